@@ -1,0 +1,76 @@
+// Device ProxADMM solver (reference: src/epsilon/algorithms/prox_admm.{h,cc}).
+#pragma once
+#include "kkt.h"
+#include "problem.h"
+#include "prox.cuh"
+
+namespace eps {
+
+enum StageKind { ST_ELEM = 0, ST_NORM2 = 1, ST_TV = 2, ST_KKT = 3 };
+
+// One f_i after Init.
+struct ProxOp {
+  int type = 0;
+  std::vector<int> vars;        // variable indices, ordered by variable id (expression_util.cc:5-31)
+  std::vector<int64_t> var_off; // offset of each inside x_i
+  int64_t n = 0;                // total variable entries
+  int64_t x_off = 0;            // into the x arena
+  int64_t span_lo = 0, span_len = 0;  // rows of u this operator touches (contiguous cover)
+  int64_t y_off = 0;            // into each y arena
+  BlockOp A;                    // span_len x n, rows relative to span_lo
+  bool simple_scalar = false;   // A = a*I on exactly the span
+  double a = 0;
+  std::unique_ptr<KktSolver> kkt;
+  ElemSeg seg;                  // elementwise / block / tv operators
+};
+
+struct Stage {
+  int kind = ST_ELEM;
+  int type = 0;
+  std::vector<int> members;     // indices into ops
+  bool scalar_a = false;        // every member has a simple scalar A block
+  // device tables
+  DevBuf<ElemSeg> segs;
+  DevBuf<SegPair> pairs;
+  std::vector<SegPair> pairs_host;
+  DevBuf<int64_t> prefix;
+  int64_t total = 0;
+  int max_len = 0;
+  DevBuf<double> tv_work;
+};
+
+}  // namespace eps
+
+struct eps_solver {
+  eps::Ctx* ctx = nullptr;
+  eps_params params;
+  std::vector<eps::VarInfo> vars;
+  std::vector<int> var_owner;                 // prox index owning each variable (-1 none)
+  std::vector<int64_t> var_x_off;             // absolute offset in the x arena
+  std::vector<eps::ProxOp> ops;
+  std::vector<std::unique_ptr<eps::Stage>> stages;
+  int64_t m_total = 0;   // A_.m()
+  int64_t n_total = 0;   // A_.n()
+  int N = 0;
+  bool has_b = false;
+  double b_norm = 0;
+  eps::DevBuf<double> u, b, x, consts, ybuf[2], tmp_m, diff_m, tmp_n, rhs_n, resid;
+  double* h_resid = nullptr;  // pinned
+  int parity = 0;             // ybuf[parity] holds the current y
+  int iter = 0;               // next iteration index (iter_ of the reference)
+  bool started = false;
+  eps_status status;
+  std::string description;
+  // graphs
+  cudaGraphExec_t graph_exec[2] = {nullptr, nullptr};
+  int64_t graph_nodes[2] = {0, 0};
+  bool graph_ok = false;
+  int eager_done[2] = {0, 0};
+
+  ~eps_solver();
+  void Init(const eps_problem& p);
+  void Iteration();          // one ADMM iteration, eager launches
+  void RunIteration();       // graph replay when available
+  void ComputeResiduals();
+  void ResetVariables();
+};

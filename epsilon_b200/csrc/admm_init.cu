@@ -1,0 +1,402 @@
+// ProxADMMSolver::Init on the device side (reference: src/epsilon/algorithms/prox_admm.cc:25-129).
+//   InitConstraints  (:25-43)  -> flat u-space, one contiguous row block per constraint
+//   InitProxOperators(:45-94)  -> per f_i: H (args), A (its columns of A_), operator object
+//   InitVariables    (:96-108) -> u = 0, x and y empty (= zero slabs)
+#include <algorithm>
+#include <chrono>
+#include <numeric>
+
+#include "admm.h"
+
+namespace eps {
+
+namespace {
+
+std::shared_ptr<MapData> IdentityMap(Ctx* ctx, int n) {
+  auto d = std::make_shared<MapData>();
+  d->ctx = ctx; d->kind = MK_SCALAR; d->m = n; d->n = n; d->alpha = 1.0;
+  return d;
+}
+
+Blk TermBlk(Ctx* ctx, const Term& t, int rows, int row_off, int col_off) {
+  Blk b;
+  b.row_off = row_off;
+  b.col_off = col_off;
+  b.map = t.map ? t.map : IdentityMap(ctx, rows);
+  b.trans = t.map ? t.trans : false;
+  b.scale = 1.0;
+  return b;
+}
+
+// Sum of the constant terms of an affine expression (affine.cc:51-69), on the host.
+bool EvalConstants(Ctx* ctx, const AffineExpr& e, std::vector<double>* out) {
+  out->assign(e.rows, 0.0);
+  bool any = false;
+  for (const Term& t : e.terms) {
+    if (t.var >= 0) continue;
+    any = true;
+    if (!t.map) {
+      for (int i = 0; i < e.rows; i++) (*out)[i] += t.constant[i];
+    } else if (t.map->kind == MK_SCALAR) {
+      for (int i = 0; i < e.rows; i++) (*out)[i] += t.map->alpha * t.constant[i];
+    } else {
+      const int n_in = (int)t.constant.size();
+      DevBuf<double> cin(ctx, n_in), cout(ctx, e.rows);
+      cin.upload(t.constant.data(), n_in);
+      MapApply(ctx, *t.map, t.trans, 1.0, cin.p, 0.0, cout.p);
+      std::vector<double> tmp(e.rows);
+      cout.download(tmp.data(), e.rows);
+      for (int i = 0; i < e.rows; i++) (*out)[i] += tmp[i];
+    }
+  }
+  return any;
+}
+
+bool IsKktType(int t) { return t == EPS_PROX_SUM_SQUARE || t == EPS_PROX_AFFINE || t == EPS_PROX_CONSTANT; }
+bool IsElemType(int t) {
+  return t == EPS_PROX_NORM_1 || t == EPS_PROX_SUM_HINGE || t == EPS_PROX_SUM_DEADZONE ||
+         t == EPS_PROX_SUM_QUANTILE || t == EPS_PROX_NON_NEGATIVE || t == EPS_PROX_SUM_LOGISTIC;
+}
+
+const char* TypeName(int t) {
+  switch (t) {
+    case EPS_PROX_AFFINE: return "AFFINE";
+    case EPS_PROX_CONSTANT: return "CONSTANT";
+    case EPS_PROX_ZERO: return "ZERO";
+    case EPS_PROX_SUM_SQUARE: return "SUM_SQUARE";
+    case EPS_PROX_NON_NEGATIVE: return "NON_NEGATIVE";
+    case EPS_PROX_NORM_1: return "NORM_1";
+    case EPS_PROX_SUM_DEADZONE: return "SUM_DEADZONE";
+    case EPS_PROX_SUM_HINGE: return "SUM_HINGE";
+    case EPS_PROX_SUM_LOGISTIC: return "SUM_LOGISTIC";
+    case EPS_PROX_SUM_QUANTILE: return "SUM_QUANTILE";
+    case EPS_PROX_NORM_2: return "NORM_2";
+    case EPS_PROX_TOTAL_VARIATION_1D: return "TOTAL_VARIATION_1D";
+    default: return "?";
+  }
+}
+
+}  // namespace
+}  // namespace eps
+
+using namespace eps;
+
+void eps_solver::Init(const eps_problem& p) {
+  ctx = p.ctx;
+  vars = p.vars;
+  N = (int)p.prox.size();
+  EPS_CHECK(params.rho == 1.0, "rho = %g (the reference requires rho == 1, prox_admm.cc:50)", params.rho);
+  EPS_CHECK(N > 0, "no prox functions");
+
+  // ---- InitConstraints: row offsets, b ----
+  std::vector<int64_t> coff(p.constraints.size() + 1, 0);
+  for (size_t c = 0; c < p.constraints.size(); c++) coff[c + 1] = coff[c] + p.constraints[c].rows;
+  m_total = coff.back();
+  std::vector<double> b_host(m_total, 0.0);
+  std::vector<char> var_in_constraint(vars.size(), 0);
+  for (size_t c = 0; c < p.constraints.size(); c++) {
+    std::vector<double> bc;
+    if (EvalConstants(ctx, p.constraints[c], &bc)) {
+      has_b = true;
+      std::copy(bc.begin(), bc.end(), b_host.begin() + coff[c]);
+    }
+    for (const Term& t : p.constraints[c].terms)
+      if (t.var >= 0) var_in_constraint[t.var] = 1;
+  }
+  n_total = 0;
+  for (size_t v = 0; v < vars.size(); v++)
+    if (var_in_constraint[v]) n_total += vars[v].size;
+  b_norm = 0;
+  for (double v : b_host) b_norm += v * v;
+  b_norm = std::sqrt(b_norm);
+
+  // ---- variable ownership ----
+  var_owner.assign(vars.size(), -1);
+  for (int i = 0; i < N; i++)
+    for (const AffineExpr& a : p.prox[i].args)
+      for (const Term& t : a.terms)
+        if (t.var >= 0) {
+          EPS_CHECK(var_owner[t.var] < 0 || var_owner[t.var] == i,
+                    "variable %s appears in prox %d and %d (problem is not separable)",
+                    vars[t.var].id.c_str(), var_owner[t.var], i);
+          var_owner[t.var] = i;
+        }
+  for (size_t v = 0; v < vars.size(); v++)
+    EPS_CHECK(!var_in_constraint[v] || var_owner[v] >= 0,
+              "variable %s appears in constraints but in no prox function", vars[v].id.c_str());
+
+  // ---- per-operator layout ----
+  ops.resize(N);
+  var_x_off.assign(vars.size(), -1);
+  int64_t x_total = 0, y_total = 0, max_n = 1;
+  std::vector<double> consts_host;
+  std::vector<std::vector<double>> g_hosts(N);
+  std::vector<BlockOp> Hs(N);
+  std::vector<int64_t> rows_h(N, 0);
+  std::vector<char> h_sharded(N, 0);
+  for (int i = 0; i < N; i++) {
+    ProxOp& op = ops[i];
+    const ProxFn& f = p.prox[i];
+    op.type = f.type;
+    EPS_CHECK(!f.epigraph, "epigraph operators are outside the configured hot path (prox %d)", i);
+    for (size_t v = 0; v < vars.size(); v++)
+      if (var_owner[v] == i) op.vars.push_back((int)v);
+    std::sort(op.vars.begin(), op.vars.end(),
+              [&](int a, int b) { return vars[a].id < vars[b].id; });
+    std::map<int, int64_t> voff;
+    op.n = 0;
+    for (int v : op.vars) {
+      voff[v] = op.n;
+      op.var_off.push_back(op.n);
+      var_x_off[v] = x_total + op.n;
+      op.n += vars[v].size;
+    }
+    op.x_off = x_total;
+    x_total += op.n;
+    max_n = std::max(max_n, op.n);
+
+    // H, g
+    BlockOp& H = Hs[i];
+    H.ctx = ctx;
+    std::vector<double>& g = g_hosts[i];
+    bool any_g = false;
+    int64_t hoff = 0;
+    for (const AffineExpr& a : f.args) {
+      std::vector<double> ga;
+      any_g = EvalConstants(ctx, a, &ga) || any_g;
+      g.insert(g.end(), ga.begin(), ga.end());
+      for (const Term& t : a.terms)
+        if (t.var >= 0) H.blks.push_back(TermBlk(ctx, t, a.rows, (int)hoff, (int)voff[t.var]));
+      if (a.global_rows > 0 && ctx->n_ranks > 1) h_sharded[i] = 1;
+      hoff += a.rows;
+    }
+    if (!any_g) g.clear();
+    rows_h[i] = hoff;
+    H.rows = hoff;
+    H.cols = op.n;
+
+    // A restricted to this operator's variables, span
+    int64_t lo = m_total, hi = 0;
+    for (size_t c = 0; c < p.constraints.size(); c++)
+      for (const Term& t : p.constraints[c].terms)
+        if (t.var >= 0 && var_owner[t.var] == i) {
+          lo = std::min(lo, coff[c]);
+          hi = std::max(hi, coff[c + 1]);
+        }
+    if (hi <= lo) { lo = 0; hi = 0; }
+    op.span_lo = lo;
+    op.span_len = hi - lo;
+    op.y_off = y_total;
+    y_total += op.span_len;
+    op.A.ctx = ctx;
+    op.A.rows = op.span_len;
+    op.A.cols = op.n;
+    for (size_t c = 0; c < p.constraints.size(); c++)
+      for (const Term& t : p.constraints[c].terms)
+        if (t.var >= 0 && var_owner[t.var] == i)
+          op.A.blks.push_back(TermBlk(ctx, t, p.constraints[c].rows, (int)(coff[c] - lo), (int)voff[t.var]));
+    op.A.Compile();
+    op.simple_scalar = op.A.simple_scalar && op.A.simple_row_off == 0 && op.span_len == op.n;
+    op.a = op.simple_scalar ? op.A.simple_alpha : 0.0;
+  }
+
+  // ---- operators ----
+  for (int i = 0; i < N; i++) {
+    ProxOp& op = ops[i];
+    const ProxFn& f = p.prox[i];
+    if (IsKktType(f.type)) {
+      auto k = std::make_unique<KktSolver>();
+      k->ctx = ctx;
+      k->mode = params.kkt_mode;
+      k->n = op.n;
+      k->cg_tol = params.cg_tol;
+      k->cg_max_iter = params.cg_max_iterations;
+      k->gram_max_n = params.gram_max_n;
+      k->rows_a = op.span_len;
+      k->A.ctx = ctx; k->A.rows = op.A.rows; k->A.cols = op.A.cols; k->A.blks = op.A.blks;
+      std::vector<double> c_host;
+      if (f.type == EPS_PROX_SUM_SQUARE) {
+        k->alpha2 = 2.0 * f.alpha;
+        k->H.ctx = ctx; k->H.rows = Hs[i].rows; k->H.cols = Hs[i].cols; k->H.blks = Hs[i].blks;
+        k->rows_h = rows_h[i];
+        k->h_sharded = h_sharded[i] != 0;
+        k->Init(g_hosts[i], c_host);
+      } else {
+        k->alpha2 = 0.0;
+        k->H.ctx = ctx; k->H.rows = 0; k->H.cols = op.n;
+        k->rows_h = 0;
+        if (f.type == EPS_PROX_AFFINE) {
+          // c = alpha * (1 x n linear map)'   (affine.cc:8-17,26-28)
+          EPS_CHECK(rows_h[i] == 1, "AFFINE prox expects a 1 x n argument, got %lld rows", (long long)rows_h[i]);
+          Hs[i].Compile();
+          DevBuf<double> one(ctx, 1), cdev(ctx, op.n);
+          VecFill(ctx, 1, f.alpha, one.p);
+          Hs[i].ApplyT(one.p, cdev.p);
+          c_host.resize(op.n);
+          cdev.download(c_host.data(), op.n);
+        }
+        k->Init(std::vector<double>(), c_host);
+      }
+      description += Format("prox %d %s vars=%lld span=[%lld,+%lld) %s\n", i, TypeName(f.type),
+                            (long long)op.n, (long long)op.span_lo, (long long)op.span_len,
+                            k->description.c_str());
+      op.kkt = std::move(k);
+    } else if (IsElemType(f.type) || f.type == EPS_PROX_NORM_2 || f.type == EPS_PROX_TOTAL_VARIATION_1D) {
+      // VectorProx::InitScalar (vector_prox.cc:51-70) for scalar H and A blocks.
+      const BlockOp& H = Hs[i];
+      EPS_CHECK(f.args.size() == 1 && op.vars.size() == 1,
+                "prox %d (%s): one argument over one variable expected", i, TypeName(f.type));
+      EPS_CHECK(H.blks.size() == 1 && H.blks[0].map->kind == MK_SCALAR && H.rows == op.n,
+                "prox %d (%s): argument must be a scalar multiple of its variable "
+                "(diagonal / general H is not supported on the device path)", i, TypeName(f.type));
+      EPS_CHECK(op.simple_scalar,
+                "prox %d (%s): the variable must enter exactly one constraint through a scalar map", i,
+                TypeName(f.type));
+      const double h = H.blks[0].scale * H.blks[0].map->alpha;
+      const double a = op.a;
+      const double beta = h * h;
+      const double gamma = ((h * a) * a) * h;
+      EPS_CHECK(gamma > 0, "prox %d: H A'A H' = %g", i, gamma);
+      ElemSeg& s = op.seg;
+      s.u_off = op.span_lo;
+      s.y_off = op.y_off;
+      s.x_off = op.x_off;
+      s.len = (int32_t)op.n;
+      s.type = f.type;
+      s.Bs = ((beta / gamma) * h) * a;
+      s.Cs = (1 / beta) * h;
+      s.As = a;
+      s.lam = f.alpha * beta * beta / gamma;
+      EPS_CHECK(s.lam >= 0, "lambda = %g < 0", s.lam);
+      s.g_off = -1;
+      if (!g_hosts[i].empty()) {
+        s.g_off = (int64_t)consts_host.size();
+        consts_host.insert(consts_host.end(), g_hosts[i].begin(), g_hosts[i].end());
+      }
+      s.q_off = -1;
+      s.zone_m = 0; s.zone_alpha = 1; s.zone_beta = 1;
+      if (f.type == EPS_PROX_SUM_DEADZONE) s.zone_m = f.zone_m;
+      if (f.type == EPS_PROX_SUM_HINGE) s.zone_beta = 0;
+      if (f.type == EPS_PROX_SUM_QUANTILE) {
+        EPS_CHECK(!f.q_alpha.empty(), "SUM_QUANTILE without alpha/beta");
+        if (f.q_alpha.size() == 1) {
+          s.zone_alpha = f.q_alpha[0];
+          s.zone_beta = f.q_beta[0];
+        } else {
+          EPS_CHECK((int64_t)f.q_alpha.size() == op.n, "quantile vectors have %zu entries, need %lld",
+                    f.q_alpha.size(), (long long)op.n);
+          s.q_off = (int64_t)consts_host.size();
+          consts_host.insert(consts_host.end(), f.q_alpha.begin(), f.q_alpha.end());
+          consts_host.insert(consts_host.end(), f.q_beta.begin(), f.q_beta.end());
+        }
+      }
+      description += Format("prox %d %s n=%lld rows=[%lld,+%lld) lambda=%.6g B=%g C=%g A=%g\n", i,
+                            TypeName(f.type), (long long)op.n, (long long)op.span_lo,
+                            (long long)op.span_len, s.lam, s.Bs, s.Cs, s.As);
+    } else {
+      throw Error(EPS_ERR_INVALID, Format("prox %d: type %d (%s) has no device operator", i, f.type, TypeName(f.type)));
+    }
+  }
+
+  // ---- stages: consecutive same-type elementwise/block operators on disjoint rows ----
+  for (int i = 0; i < N; i++) {
+    const ProxOp& op = ops[i];
+    int kind = ST_KKT;
+    if (IsElemType(op.type)) kind = ST_ELEM;
+    else if (op.type == EPS_PROX_NORM_2) kind = ST_NORM2;
+    else if (op.type == EPS_PROX_TOTAL_VARIATION_1D) kind = ST_TV;
+    bool merged = false;
+    if ((kind == ST_ELEM || kind == ST_NORM2) && !stages.empty()) {
+      Stage& last = *stages.back();
+      if (last.kind == kind && last.type == op.type) {
+        bool disjoint = true;
+        for (int j : last.members) {
+          const ProxOp& o = ops[j];
+          if (op.span_lo < o.span_lo + o.span_len && o.span_lo < op.span_lo + op.span_len) disjoint = false;
+        }
+        if (disjoint) { last.members.push_back(i); merged = true; }
+      }
+    }
+    if (!merged) {
+      auto st = std::make_unique<Stage>();
+      st->kind = kind;
+      st->type = op.type;
+      st->members.push_back(i);
+      stages.push_back(std::move(st));
+    }
+  }
+  for (auto& stp : stages) {
+    Stage& st = *stp;
+    std::vector<ElemSeg> segs;
+    std::vector<int64_t> prefix(1, 0);
+    st.scalar_a = true;
+    for (int j : st.members) {
+      const ProxOp& op = ops[j];
+      segs.push_back(op.seg);
+      SegPair pr;
+      pr.a_off = op.span_lo;
+      pr.b_off = op.y_off;
+      pr.len = (int32_t)op.span_len;
+      pr.coef = op.a * op.a;
+      st.pairs_host.push_back(pr);
+      prefix.push_back(prefix.back() + op.span_len);
+      st.max_len = std::max<int>(st.max_len, (int)op.span_len);
+      if (!op.simple_scalar) st.scalar_a = false;
+    }
+    st.total = prefix.back();
+    st.segs.alloc(ctx, segs.size());
+    st.segs.upload(segs.data(), segs.size());
+    st.pairs.alloc(ctx, st.pairs_host.size());
+    st.pairs.upload(st.pairs_host.data(), st.pairs_host.size());
+    st.prefix.alloc(ctx, prefix.size());
+    st.prefix.upload(prefix.data(), prefix.size());
+    if (st.kind == ST_TV) st.tv_work.alloc(ctx, Tv1dWorkDoubles(ops[st.members[0]].n));
+    CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+  }
+
+  // ---- slabs ----
+  u.alloc(ctx, std::max<int64_t>(m_total, 1));
+  b.alloc(ctx, std::max<int64_t>(m_total, 1));
+  b.upload(b_host.data(), m_total);
+  x.alloc(ctx, std::max<int64_t>(x_total, 1));
+  ybuf[0].alloc(ctx, std::max<int64_t>(y_total, 1));
+  ybuf[1].alloc(ctx, std::max<int64_t>(y_total, 1));
+  tmp_m.alloc(ctx, std::max<int64_t>(m_total, 1));
+  diff_m.alloc(ctx, std::max<int64_t>(m_total, 1));
+  tmp_n.alloc(ctx, max_n);
+  rhs_n.alloc(ctx, max_n);
+  resid.alloc(ctx, 8);
+  consts.alloc(ctx, std::max<size_t>(consts_host.size(), 1));
+  consts.upload(consts_host.data(), consts_host.size());
+  CUDA_CHECK(cudaMallocHost(&h_resid, 8 * sizeof(double)));
+  CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+  ResetVariables();
+
+  graph_ok = params.use_graph && !params.profile;
+  for (auto& op : ops)
+    if (op.kkt && op.kkt->mode == EPS_KKT_CG) graph_ok = false;  // host-checked inner loop
+  memset(&status, 0, sizeof(status));
+  status.state = EPS_NOT_STARTED;
+  status.m = (int32_t)m_total;
+  status.n = (int32_t)n_total;
+  status.N = N;
+  description = Format("ProxADMM m=%lld n=%lld N=%d stages=%zu graph=%d\n", (long long)m_total,
+                       (long long)n_total, N, stages.size(), graph_ok ? 1 : 0) + description;
+}
+
+void eps_solver::ResetVariables() {
+  u.zero();
+  x.zero();
+  ybuf[0].zero();
+  ybuf[1].zero();
+  parity = 0;
+  iter = 0;
+  started = false;
+  CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+}
+
+eps_solver::~eps_solver() {
+  for (int i = 0; i < 2; i++)
+    if (graph_exec[i]) cudaGraphExecDestroy(graph_exec[i]);
+  if (h_resid) cudaFreeHost(h_resid);
+}

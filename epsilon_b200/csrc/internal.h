@@ -1,0 +1,260 @@
+// Internal declarations of libepsgpu (host side, C++17).  Not installed.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <memory>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "../../include/epsgpu.h"
+
+namespace eps {
+
+// ---- errors -------------------------------------------------------------------
+struct Error : std::runtime_error {
+  int code;
+  Error(int c, const std::string& m) : std::runtime_error(m), code(c) {}
+};
+std::string Format(const char* fmt, ...);
+void SetLastError(const std::string& msg);
+
+#define EPS_CHECK(cond, ...)                                                     \
+  do {                                                                           \
+    if (!(cond))                                                                 \
+      throw ::eps::Error(EPS_ERR_INVALID, std::string("check failed: " #cond " ") + \
+                                              ::eps::Format(__VA_ARGS__));       \
+  } while (0)
+
+#define CUDA_CHECK(expr)                                                         \
+  do {                                                                           \
+    cudaError_t e_ = (expr);                                                     \
+    if (e_ != cudaSuccess)                                                       \
+      throw ::eps::Error(EPS_ERR_CUDA, ::eps::Format("%s:%d %s: %s", __FILE__,   \
+                                                     __LINE__, #expr,            \
+                                                     cudaGetErrorString(e_)));   \
+  } while (0)
+
+struct Ctx;
+
+// ---- device memory ----------------------------------------------------------------
+template <typename T>
+struct DevBuf {
+  T* p = nullptr;
+  size_t n = 0;
+  Ctx* ctx = nullptr;
+  DevBuf() {}
+  DevBuf(Ctx* c, size_t count) { alloc(c, count); }
+  DevBuf(const DevBuf&) = delete;
+  DevBuf& operator=(const DevBuf&) = delete;
+  DevBuf(DevBuf&& o) noexcept { *this = std::move(o); }
+  DevBuf& operator=(DevBuf&& o) noexcept {
+    if (this != &o) { release(); p = o.p; n = o.n; ctx = o.ctx; o.p = nullptr; o.n = 0; }
+    return *this;
+  }
+  ~DevBuf() { release(); }
+  void alloc(Ctx* c, size_t count) {
+    release();
+    ctx = c; n = count;
+    if (count == 0) return;
+    CUDA_CHECK(cudaMalloc(&p, count * sizeof(T)));
+    ctx->bytes_allocated += count * sizeof(T);
+  }
+  void release() {
+    if (p) { cudaFree(p); if (ctx) ctx->bytes_allocated -= n * sizeof(T); }
+    p = nullptr; n = 0;
+  }
+  void zero() { if (n) CUDA_CHECK(cudaMemsetAsync(p, 0, n * sizeof(T), ctx->stream)); }
+  void upload(const T* host, size_t count) {
+    if (count) CUDA_CHECK(cudaMemcpyAsync(p, host, count * sizeof(T), cudaMemcpyHostToDevice, ctx->stream));
+  }
+  void download(T* host, size_t count) const {
+    if (count) CUDA_CHECK(cudaMemcpyAsync(host, p, count * sizeof(T), cudaMemcpyDeviceToHost, ctx->stream));
+    CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+  }
+};
+
+// ---- context --------------------------------------------------------------------
+struct Comm;  // NCCL (dlopen'ed), comm.cu
+
+// Kernel classes for the profile mode (CUDA events around each launch).
+enum KClass {
+  KC_SPMV_N = 0, KC_SPMV_T, KC_GEMV_N, KC_GEMV_T, KC_PROX, KC_VEC, KC_REDUCE,
+  KC_KKT_DENSE, KC_TV, KC_ALLREDUCE, KC_OTHER, KC_COUNT
+};
+extern const char* const kKClassNames[KC_COUNT];
+
+struct Ctx {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  bool own_stream = false;
+  int sm_count = 148;
+  int64_t launches = 0;        // kernels launched outside graphs + graph-node replays
+  int64_t bytes_allocated = 0;
+  bool capturing = false;      // inside stream capture: launches counted per capture
+  int64_t capture_launches = 0;
+  Comm* comm = nullptr;
+  int n_ranks = 1, rank = 0;
+  // profile mode
+  bool profile = false;
+  struct Prof { int64_t launches = 0; double ms = 0, bytes = 0; };
+  Prof prof[KC_COUNT];
+  cudaEvent_t prof_ev[2] = {nullptr, nullptr};
+  // scratch owned by the context (grown on demand, never during graph capture)
+  DevBuf<double> split_scratch, seg_scratch, red_partials;
+  DevBuf<unsigned int> red_counter;
+  int64_t scratch_generation = 0;
+  ~Ctx();
+  void count_launch(int n = 1) {
+    if (capturing) capture_launches += n; else launches += n;
+  }
+};
+
+// Brackets one kernel launch for the profile mode; no-op otherwise.
+struct ProfScope {
+  Ctx* ctx; int kc; double bytes;
+  ProfScope(Ctx* c, int k, double b);
+  ~ProfScope();
+};
+
+// ---- atomic linear maps (LinearMapImpl types, linear/linear_map.h:17-26) -----------
+enum MapKind { MK_DENSE = 0, MK_SPARSE = 1, MK_DIAGONAL = 2, MK_SCALAR = 3, MK_KRONECKER = 4 };
+
+// CSR on the device.  rowptr int64 when nnz does not fit int32.
+struct Csr {
+  int m = 0, n = 0;
+  int64_t nnz = 0;
+  DevBuf<int32_t> rowptr;  // m+1 (nnz < 2^31 per map / per shard is enforced)
+  DevBuf<int32_t> col;
+  DevBuf<double> val;
+  int max_row_nnz = 0;
+};
+
+struct MapData {
+  Ctx* ctx = nullptr;
+  int kind = MK_SCALAR;
+  int m = 0, n = 0;       // of the stored (untransposed) matrix
+  // dense: column-major m x n
+  DevBuf<double> dense;
+  // sparse: CSR of A and CSR of A' (= the CSC wire layout)
+  Csr csr, csr_t;
+  // small host copy of the CSC arrays for block merging (only when nnz is small)
+  std::vector<int32_t> h_colptr, h_rowidx;
+  std::vector<double> h_vals;
+  bool has_host = false;
+  // diagonal
+  DevBuf<double> diag;
+  std::vector<double> h_diag;
+  // scalar
+  double alpha = 1.0;
+  // kronecker
+  std::shared_ptr<MapData> ka, kb;
+  bool ka_trans = false, kb_trans = false;
+};
+
+}  // namespace eps
+
+// Handle types of the C ABI.
+struct eps_ctx { eps::Ctx c; };
+struct eps_map {
+  std::shared_ptr<eps::MapData> d;
+  bool trans = false;
+  int m() const { return trans ? d->n : d->m; }
+  int n() const { return trans ? d->m : d->n; }
+};
+
+namespace eps {
+
+// ---- kernels: maps.cu ---------------------------------------------------------------
+// y = beta*y + alpha * op(A) x  for one atomic map.
+void MapApply(Ctx* ctx, const MapData& A, bool trans, double alpha, const double* x,
+              double beta, double* y);
+double MapAlgorithmicBytes(const MapData& A, bool trans);
+void CsrApply(Ctx* ctx, const Csr& A, double alpha, const double* x, double beta, double* y,
+              int kclass);
+void BuildCsrFromHost(Ctx* ctx, int m, int n, int64_t nnz, const int64_t* rowptr,
+                      const int32_t* col, const double* val, Csr* out);
+void DenseGemv(Ctx* ctx, const double* A, int lda, int m, int n, bool trans, double alpha,
+               const double* x, double beta, double* y, int tri = 0);
+
+// ---- vector kernels: vecops.cu --------------------------------------------------------
+void VecAxpby(Ctx* ctx, int64_t n, double a, const double* x, double b, const double* y, double* out);  // out = a x + b y
+void VecScale(Ctx* ctx, int64_t n, double a, const double* x, double* out);                              // out = a x
+void VecMulAdd(Ctx* ctx, int64_t n, const double* d, const double* x, double b, const double* y, double* out);  // out = d.*x + b y
+void VecFill(Ctx* ctx, int64_t n, double a, double* out);
+void VecCopy(Ctx* ctx, int64_t n, const double* x, double* out);
+// out[0] (+)= sum x_i y_i  (deterministic two-stage reduction; out on device)
+void VecDot(Ctx* ctx, int64_t n, const double* x, const double* y, double* out_dev, bool accumulate);
+// scratch for two-stage reductions
+struct ReduceScratch {
+  DevBuf<double>& partials;
+  DevBuf<unsigned int>& counter;
+};
+ReduceScratch* GetReduceScratch(Ctx* ctx);
+double* GrowScratch(Ctx* ctx, DevBuf<double>* buf, size_t count);
+
+// ---- composite block operator (BlockMatrix, vector/block_matrix.h) --------------------
+struct Blk {
+  int row_off = 0, col_off = 0;
+  std::shared_ptr<MapData> map;
+  bool trans = false;
+  double scale = 1.0;
+  int m() const { return trans ? map->n : map->m; }
+  int n() const { return trans ? map->m : map->n; }
+  bool diag_like() const { return map->kind == MK_SCALAR || map->kind == MK_DIAGONAL; }
+};
+
+struct BlockOp {
+  Ctx* ctx = nullptr;
+  int64_t rows = 0, cols = 0;
+  std::vector<Blk> blks;
+  // compiled form
+  bool compiled = false;
+  bool is_zero = false;
+  // "simple scalar": exactly one scalar block covering [row_off, row_off+cols)
+  bool simple_scalar = false;
+  double simple_alpha = 0;
+  int64_t simple_row_off = 0;
+  // merged sparse-like blocks (CSR over rows x cols) and its transpose
+  bool has_merged = false;
+  Csr merged, merged_t;
+  std::vector<Blk> heavy;  // blocks applied one by one (dense, large sparse, kronecker)
+  void Compile();
+  // y[0..rows) = op * x[0..cols)   (accumulate: y += )
+  void Apply(const double* x, double* y, bool accumulate = false) const;
+  // x[0..cols) = op' * y[0..rows)
+  void ApplyT(const double* y, double* x, bool accumulate = false) const;
+  // diag(op' op) when op' op is diagonal; false otherwise
+  bool GramDiagonal(std::vector<double>* d) const;
+  int64_t heavy_nnz() const;
+};
+
+// ---- dense factorisation kernels: dense.cu ---------------------------------------------
+// C(n x n, ldc) (+)= alpha * A' A, A m x n column-major (lda).  fp64 tensor cores (DMMA).
+void DenseGramTN(Ctx* ctx, const double* A, int64_t lda, int64_t m, int n, double alpha,
+                 double* C, int64_t ldc, bool accumulate);
+// C(m x m) (+)= alpha * A diag(w) A', A m x n column-major; w may be null (ones).
+void DenseGramNT(Ctx* ctx, const double* A, int64_t lda, int m, int64_t n, const double* w,
+                 double alpha, double* C, int64_t ldc, bool accumulate);
+// M (n x n SPD, lower part read, destroyed) -> W = inv(chol(M)), lower triangular with an
+// explicit zero upper part, so that inv(M) = W' W.  Throws Error(EPS_ERR_NUMERIC) when a
+// pivot is not positive.
+void DenseCholInverseFactor(Ctx* ctx, double* M, int64_t ld, int n, double* W);
+void DenseAddDiagonal(Ctx* ctx, double* M, int64_t ld, int n, const double* d, double alpha_scalar);
+// Gram of a CSR block: M[col_off.., col_off..] += alpha * A' A
+void CsrGramAtomic(Ctx* ctx, const Csr& A, double alpha, double* M, int64_t ld, int col_off);
+void CsrDensify(Ctx* ctx, const Csr& A, double scale, double* out, int64_t ld, int row_off, int col_off, bool trans);
+
+// ---- communication: comm.cu ---------------------------------------------------------------
+void CommInit(Ctx* ctx, int n_ranks, int rank, const void* unique_id);
+void CommUniqueId(void* out128);
+void CommDestroy(Ctx* ctx);
+void AllReduceSum(Ctx* ctx, double* buf, int64_t n);
+
+}  // namespace eps

@@ -1,0 +1,349 @@
+// KKT prox solve object: DIAGONAL / WOODBURY / GRAM / CG.  See kkt.h.
+#include <algorithm>
+
+#include "device.cuh"
+#include "kkt.h"
+#include "prox.cuh"
+
+namespace eps {
+
+void AddBlock(Ctx* ctx, int nb, const double* G, int64_t ldg, double* M, int64_t ldm);
+
+namespace {
+
+constexpr int kBlock = 256;
+constexpr int kUnroll = 4;
+
+// r = rhs - w; p = r; out = r.r
+__global__ void __launch_bounds__(kBlock)
+CgInitKernel(int64_t n, const double* __restrict__ rhs, const double* __restrict__ w,
+             double* __restrict__ r, double* __restrict__ p, double* partials, unsigned* counter,
+             double* out) {
+  __shared__ double smem[32];
+  double acc[1] = {0.0};
+  const int64_t stride = (int64_t)gridDim.x * kBlock;
+  for (int64_t i = (int64_t)blockIdx.x * kBlock + threadIdx.x; i < n; i += stride) {
+    const double t = rhs[i] - w[i];
+    r[i] = t;
+    p[i] = t;
+    acc[0] += t * t;
+  }
+  GridSumFinish<1>(acc, smem, partials, counter, out, 0);
+}
+
+// a = rr/pw; x += a p; r -= a w; out = r.r
+__global__ void __launch_bounds__(kBlock)
+CgUpdateXRKernel(int64_t n, const double* rr, const double* pw, const double* __restrict__ p,
+                 const double* __restrict__ w, double* __restrict__ x, double* __restrict__ r,
+                 double* partials, unsigned* counter, double* out) {
+  __shared__ double smem[32];
+  const double denom = *pw;
+  const double a = denom != 0.0 ? *rr / denom : 0.0;
+  double acc[1] = {0.0};
+  const int64_t stride = (int64_t)gridDim.x * kBlock;
+  for (int64_t i = (int64_t)blockIdx.x * kBlock + threadIdx.x; i < n; i += stride) {
+    x[i] += a * p[i];
+    const double t = r[i] - a * w[i];
+    r[i] = t;
+    acc[0] += t * t;
+  }
+  GridSumFinish<1>(acc, smem, partials, counter, out, 0);
+}
+
+// b = rr_new/rr_old; p = r + b p
+__global__ void __launch_bounds__(kBlock)
+CgUpdatePKernel(int64_t n, const double* rr_new, const double* rr_old, const double* __restrict__ r,
+                double* __restrict__ p) {
+  const double d = *rr_old;
+  const double b = d != 0.0 ? *rr_new / d : 0.0;
+  const int64_t stride = (int64_t)gridDim.x * kBlock;
+  for (int64_t i = (int64_t)blockIdx.x * kBlock + threadIdx.x; i < n; i += stride)
+    p[i] = r[i] + b * p[i];
+}
+
+__global__ void InvertKernel(int64_t n, const double* __restrict__ d, double* __restrict__ out, int* bad) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double v = d[i];
+  if (!(v > 0.0)) atomicExch(bad, 1);
+  out[i] = 1.0 / v;
+}
+
+bool RowDisjoint(const BlockOp& op) {
+  std::vector<std::pair<int, int>> r;
+  for (auto& b : op.blks) r.push_back({b.row_off, b.row_off + b.m()});
+  std::sort(r.begin(), r.end());
+  for (size_t i = 1; i < r.size(); i++)
+    if (r[i].first < r[i - 1].second) return false;
+  return true;
+}
+
+// out (rows x cols, column-major) = dense copy of op
+void Densify(Ctx* ctx, const BlockOp& op, double* out) {
+  CUDA_CHECK(cudaMemsetAsync(out, 0, (size_t)op.rows * op.cols * sizeof(double), ctx->stream));
+  for (auto& b : op.blks) {
+    const MapData& M = *b.map;
+    if (M.kind == MK_SPARSE) {
+      CsrDensify(ctx, M.csr, b.scale, out, op.rows, b.row_off, b.col_off, b.trans);
+    } else {
+      // apply the block to unit vectors column by column (dense / diagonal / scalar; small only)
+      DevBuf<double> e(ctx, b.n());
+      for (int j = 0; j < b.n(); j++) {
+        e.zero();
+        VecFill(ctx, 1, 1.0, e.p + j);
+        // accumulate: several blocks may share rows
+        DevBuf<double> col(ctx, b.m());
+        MapApply(ctx, M, b.trans, b.scale, e.p, 0.0, col.p);
+        VecAxpby(ctx, b.m(), 1.0, col.p, 1.0, out + b.row_off + (size_t)(b.col_off + j) * op.rows,
+                 out + b.row_off + (size_t)(b.col_off + j) * op.rows);
+        CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+      }
+    }
+  }
+}
+
+// Mmat (n x n) += weight * op' op
+void AccumulateGram(Ctx* ctx, const BlockOp& op, double weight, double* Mmat, int64_t n) {
+  if (op.blks.empty()) return;
+  if (RowDisjoint(op)) {
+    for (auto& b : op.blks) {
+      const MapData& M = *b.map;
+      const double wgt = weight * b.scale * b.scale;
+      double* Mb = Mmat + b.col_off + (size_t)b.col_off * n;
+      if (M.kind == MK_DENSE) {
+        DevBuf<double> G(ctx, (size_t)b.n() * b.n());
+        if (!b.trans) DenseGramTN(ctx, M.dense.p, M.m, M.m, M.n, wgt, G.p, b.n(), false);
+        else DenseGramNT(ctx, M.dense.p, M.m, M.m, M.n, nullptr, wgt, G.p, b.n(), false);
+        // add G into the (col_off, col_off) block of Mmat
+        AddBlock(ctx, b.n(), G.p, b.n(), Mb, n);
+        CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+      } else if (M.kind == MK_SPARSE) {
+        CsrGramAtomic(ctx, b.trans ? M.csr_t : M.csr, wgt, Mmat, n, b.col_off);
+      } else if (M.kind == MK_SCALAR) {
+        DenseAddDiagonal(ctx, Mb, n, b.n(), nullptr, wgt * M.alpha * M.alpha);
+      } else if (M.kind == MK_DIAGONAL) {
+        std::vector<double> d2(M.n);
+        for (int i = 0; i < M.n; i++) d2[i] = wgt * M.h_diag[i] * M.h_diag[i];
+        DevBuf<double> dd(ctx, M.n);
+        dd.upload(d2.data(), M.n);
+        DenseAddDiagonal(ctx, Mb, n, b.n(), dd.p, 0.0);
+        CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+      } else {
+        throw Error(EPS_ERR_INVALID, "Gram of a Kronecker block is not supported");
+      }
+    }
+  } else {
+    EPS_CHECK((double)op.rows * op.cols < 2e9, "row-overlapping blocks too large to densify (%lld x %lld)",
+              (long long)op.rows, (long long)op.cols);
+    DevBuf<double> D(ctx, (size_t)op.rows * op.cols);
+    Densify(ctx, op, D.p);
+    DenseGramTN(ctx, D.p, op.rows, op.rows, (int)op.cols, weight, Mmat, n, true);
+    CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+  }
+}
+
+__global__ void AddBlockKernel(int nb, const double* __restrict__ G, int64_t ldg, double* M, int64_t ldm) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  int j = blockIdx.y;
+  if (i < nb && j < nb) M[i + (int64_t)j * ldm] += G[i + (int64_t)j * ldg];
+}
+
+}  // namespace
+
+void AddBlock(Ctx* ctx, int nb, const double* G, int64_t ldg, double* M, int64_t ldm) {
+  if (nb <= 0) return;
+  AddBlockKernel<<<dim3((nb + 255) / 256, nb), 256, 0, ctx->stream>>>(nb, G, ldg, M, ldm);
+  ctx->count_launch();
+}
+
+KktSolver::~KktSolver() {
+  if (h_scal) cudaFreeHost(h_scal);
+}
+
+void KktSolver::Init(const std::vector<double>& g_host, const std::vector<double>& c_host) {
+  EPS_CHECK(n > 0, "KKT prox without variables");
+  H.Compile();
+  A.Compile();
+  tn1.alloc(ctx, n);
+  tn2.alloc(ctx, n);
+  th1.alloc(ctx, std::max<int64_t>(rows_h, 1));
+  th2.alloc(ctx, std::max<int64_t>(rows_h, 1));
+  ta1.alloc(ctx, std::max<int64_t>(rows_a, 1));
+  scal.alloc(ctx, 8);
+  scal.zero();
+  CUDA_CHECK(cudaMallocHost(&h_scal, 8 * sizeof(double)));
+
+  // c0 = -2a H'g - c
+  c0.alloc(ctx, n);
+  c0.zero();
+  if (alpha2 != 0.0 && !g_host.empty() && rows_h > 0) {
+    DevBuf<double> g(ctx, rows_h);
+    g.upload(g_host.data(), rows_h);
+    H.ApplyT(g.p, c0.p);
+    if (h_sharded) AllReduceSum(ctx, c0.p, n);
+    VecScale(ctx, n, -alpha2, c0.p, c0.p);
+    CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+  }
+  if (!c_host.empty()) {
+    DevBuf<double> c(ctx, n);
+    c.upload(c_host.data(), n);
+    VecAxpby(ctx, n, 1.0, c0.p, -1.0, c.p, c0.p);
+    CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+  }
+
+  std::vector<double> dh, da;
+  const bool h_diag = (alpha2 == 0.0 || H.blks.empty()) ? (dh.assign(n, 0.0), true) : H.GramDiagonal(&dh);
+  a_diag = A.GramDiagonal(&da);
+  bool a_pos = a_diag;
+  if (a_diag) for (double v : da) if (!(v > 0.0)) { a_pos = false; break; }
+
+  if (mode == EPS_KKT_AUTO) {
+    if (h_diag && a_diag && !h_sharded) mode = EPS_KKT_DIAGONAL;
+    else if (a_pos && rows_h > 0 && rows_h < n && rows_h <= gram_max_n && !h_sharded) mode = EPS_KKT_WOODBURY;
+    else if (n <= gram_max_n) mode = EPS_KKT_GRAM;
+    else mode = EPS_KKT_CG;
+  }
+
+  if (mode == EPS_KKT_DIAGONAL) {
+    EPS_CHECK(h_diag && a_diag && !h_sharded, "DIAGONAL mode needs scalar/diagonal blocks");
+    std::vector<double> di(n);
+    for (int64_t i = 0; i < n; i++) {
+      const double d = alpha2 * dh[i] + da[i];
+      EPS_CHECK(d > 0.0, "singular diagonal KKT system at %lld", (long long)i);
+      di[i] = 1.0 / d;
+    }
+    dinv.alloc(ctx, n);
+    dinv.upload(di.data(), n);
+    CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+    description = Format("kkt=DIAGONAL n=%lld", (long long)n);
+  } else if (mode == EPS_KKT_WOODBURY) {
+    EPS_CHECK(a_pos && rows_h > 0 && !h_sharded, "WOODBURY mode needs diagonal positive A'A and an H block");
+    std::vector<double> di(n);
+    for (int64_t i = 0; i < n; i++) di[i] = 1.0 / da[i];
+    dinv.alloc(ctx, n);
+    dinv.upload(di.data(), n);
+    // S = I/(2a) + H D^-1 H'
+    DevBuf<double> S(ctx, (size_t)rows_h * rows_h);
+    const bool single_dense = H.blks.size() == 1 && H.blks[0].map->kind == MK_DENSE &&
+                              !H.blks[0].trans && H.blks[0].row_off == 0 && H.blks[0].col_off == 0 &&
+                              H.blks[0].m() == rows_h && H.blks[0].n() == n;
+    if (single_dense) {
+      const Blk& b = H.blks[0];
+      DenseGramNT(ctx, b.map->dense.p, b.map->m, (int)rows_h, n, dinv.p, b.scale * b.scale, S.p, rows_h, false);
+    } else {
+      EPS_CHECK((double)rows_h * n < 2e9, "H too large to densify for WOODBURY (%lld x %lld)",
+                (long long)rows_h, (long long)n);
+      DevBuf<double> D(ctx, (size_t)rows_h * n);
+      Densify(ctx, H, D.p);
+      DenseGramNT(ctx, D.p, rows_h, (int)rows_h, n, dinv.p, 1.0, S.p, rows_h, false);
+      CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+    }
+    DenseAddDiagonal(ctx, S.p, rows_h, (int)rows_h, nullptr, 1.0 / alpha2);
+    W.alloc(ctx, (size_t)rows_h * rows_h);
+    DenseCholInverseFactor(ctx, S.p, rows_h, (int)rows_h, W.p);
+    description = Format("kkt=WOODBURY n=%lld factor=%lldx%lld", (long long)n, (long long)rows_h, (long long)rows_h);
+  } else if (mode == EPS_KKT_GRAM) {
+    DevBuf<double> Mmat(ctx, (size_t)n * n);
+    Mmat.zero();
+    if (alpha2 != 0.0) {
+      AccumulateGram(ctx, H, alpha2, Mmat.p, n);
+      if (h_sharded) AllReduceSum(ctx, Mmat.p, n * n);
+    }
+    AccumulateGram(ctx, A, 1.0, Mmat.p, n);
+    W.alloc(ctx, (size_t)n * n);
+    DenseCholInverseFactor(ctx, Mmat.p, n, (int)n, W.p);
+    description = Format("kkt=GRAM n=%lld factor=%lldx%lld", (long long)n, (long long)n, (long long)n);
+  } else if (mode == EPS_KKT_CG) {
+    if (a_diag) {
+      ddiag.alloc(ctx, n);
+      ddiag.upload(da.data(), n);
+    }
+    cg_r.alloc(ctx, n);
+    cg_p.alloc(ctx, n);
+    cg_w.alloc(ctx, n);
+    CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+    description = Format("kkt=CG n=%lld rows_h=%lld tol=%.1e%s", (long long)n, (long long)rows_h, cg_tol,
+                         h_sharded ? " sharded" : "");
+  } else {
+    throw Error(EPS_ERR_INVALID, Format("unknown kkt mode %d", mode));
+  }
+}
+
+void KktSolver::MatVec(const double* p, double* w) {
+  bool have = false;
+  if (alpha2 != 0.0 && !H.blks.empty()) {
+    H.Apply(p, th1.p);
+    H.ApplyT(th1.p, w);
+    if (h_sharded) AllReduceSum(ctx, w, n);
+    have = true;
+  }
+  if (a_diag) {
+    if (have) VecMulAdd(ctx, n, ddiag.p, p, alpha2, w, w);
+    else VecMulAdd(ctx, n, ddiag.p, p, 0.0, nullptr, w);
+  } else {
+    if (have) VecScale(ctx, n, alpha2, w, w);
+    A.Apply(p, ta1.p);
+    A.ApplyT(ta1.p, w, have);
+  }
+}
+
+void KktSolver::Solve(const double* rhs, double* x) {
+  switch (mode) {
+    case EPS_KKT_DIAGONAL:
+      KktDiagSolve(ctx, n, dinv.p, rhs, x);
+      break;
+    case EPS_KKT_WOODBURY: {
+      // x = D^-1 r - D^-1 H' S^-1 H D^-1 r,  S^-1 = W'W
+      KktDiagSolve(ctx, n, dinv.p, rhs, tn1.p);
+      H.Apply(tn1.p, th1.p);
+      DenseGemv(ctx, W.p, (int)rows_h, (int)rows_h, (int)rows_h, false, 1.0, th1.p, 0.0, th2.p, 1);
+      DenseGemv(ctx, W.p, (int)rows_h, (int)rows_h, (int)rows_h, true, 1.0, th2.p, 0.0, th1.p, 1);
+      H.ApplyT(th1.p, tn2.p);
+      VecMulAdd(ctx, n, dinv.p, tn2.p, -1.0, tn1.p, tn2.p);  // tn2 = dinv.*(H'z) - tn1 = -x
+      VecScale(ctx, n, -1.0, tn2.p, x);
+      break;
+    }
+    case EPS_KKT_GRAM:
+      DenseGemv(ctx, W.p, (int)n, (int)n, (int)n, false, 1.0, rhs, 0.0, tn1.p, 1);
+      DenseGemv(ctx, W.p, (int)n, (int)n, (int)n, true, 1.0, tn1.p, 0.0, x, 1);
+      break;
+    case EPS_KKT_CG: {
+      ReduceScratch* rs = GetReduceScratch(ctx);
+      const int grid = std::min(1024, GridFor(n, kBlock, kUnroll, ctx->sm_count, 4));
+      double* rr0 = scal.p;       // ping-pong rr[0], rr[1]
+      double* pw = scal.p + 2;
+      double* bb = scal.p + 3;
+      VecDot(ctx, n, rhs, rhs, bb, false);
+      MatVec(x, cg_w.p);
+      CgInitKernel<<<grid, kBlock, 0, ctx->stream>>>(n, rhs, cg_w.p, cg_r.p, cg_p.p, rs->partials.p,
+                                                      rs->counter.p, rr0);
+      ctx->count_launch();
+      CUDA_CHECK(cudaMemcpyAsync(h_scal, scal.p, 4 * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+      CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+      const double bnorm = std::sqrt(h_scal[3]);
+      double rr = h_scal[0];
+      const double thresh = cg_tol * bnorm;
+      int it = 0;
+      while (std::sqrt(rr) > thresh && it < cg_max_iter) {
+        const int cur = it & 1;
+        MatVec(cg_p.p, cg_w.p);
+        VecDot(ctx, n, cg_p.p, cg_w.p, pw, false);
+        CgUpdateXRKernel<<<grid, kBlock, 0, ctx->stream>>>(n, rr0 + cur, pw, cg_p.p, cg_w.p, x, cg_r.p,
+                                                            rs->partials.p, rs->counter.p, rr0 + (cur ^ 1));
+        ctx->count_launch();
+        CUDA_CHECK(cudaMemcpyAsync(h_scal, rr0 + (cur ^ 1), sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+        CgUpdatePKernel<<<grid, kBlock, 0, ctx->stream>>>(n, rr0 + (cur ^ 1), rr0 + cur, cg_r.p, cg_p.p);
+        ctx->count_launch();
+        CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+        rr = h_scal[0];
+        it++;
+      }
+      cg_iters_total += it;
+      break;
+    }
+    default:
+      throw Error(EPS_ERR_INVALID, "KKT solver not initialised");
+  }
+}
+
+}  // namespace eps

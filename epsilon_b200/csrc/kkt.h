@@ -1,0 +1,46 @@
+// Linear-equality (KKT) prox: SumSquareProx / AffineProx of the reference.
+#pragma once
+#include "internal.h"
+
+namespace eps {
+
+// Solves  (2a H'H + A'A) x = A'v + c0,   c0 = -2a H'g - c
+// which is what chol_.Solve(b_ + v).Select(var_keys_) returns for
+//   SumSquareProx (src/epsilon/prox/sum_square.cc:10-40; alpha' = sqrt(2*alpha) scales H and g)
+//   AffineProx    (src/epsilon/prox/affine.cc:19-49;  a = 0, c = alpha * linear term)
+// The reference eliminates the KKT blocks with BlockCholesky
+// (src/epsilon/vector/block_cholesky.cc:119-137); which Schur complement that produces
+// (rows(H)^2 or n^2) is the WOODBURY / GRAM distinction here.
+struct KktSolver {
+  Ctx* ctx = nullptr;
+  int mode = EPS_KKT_AUTO;
+  int64_t n = 0, rows_h = 0, rows_a = 0;
+  double alpha2 = 0;  // 2*alpha (0: no H term)
+  bool h_sharded = false;
+  BlockOp H, A;
+  DevBuf<double> c0;
+  // factors
+  DevBuf<double> dinv;   // DIAGONAL: 1/diag(M); WOODBURY: 1/diag(A'A)
+  DevBuf<double> ddiag;  // CG: diag(A'A) when A'A is diagonal
+  bool a_diag = false;
+  DevBuf<double> W;      // WOODBURY: rows_h^2, GRAM: n^2; lower-triangular inv(chol)
+  // work vectors
+  DevBuf<double> tn1, tn2, th1, th2, ta1;
+  DevBuf<double> cg_r, cg_p, cg_w;
+  DevBuf<double> scal;   // device scalars of the CG recurrences
+  double* h_scal = nullptr;  // pinned mirror
+  double cg_tol = 1e-12;
+  int cg_max_iter = 500;
+  int64_t cg_iters_total = 0;
+  int64_t gram_max_n = 60000;
+  std::string description;
+
+  ~KktSolver();
+  // g: rows_h constants of the argument (may be empty = 0); c: n linear term (may be null)
+  void Init(const std::vector<double>& g_host, const std::vector<double>& c_host);
+  // x <- solution for rhs (both device, n).  x holds the warm start on entry (CG).
+  void Solve(const double* rhs, double* x);
+  void MatVec(const double* p, double* w);  // w = (2a H'H + A'A) p
+};
+
+}  // namespace eps

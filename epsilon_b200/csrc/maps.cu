@@ -1,0 +1,548 @@
+// Linear operators on the device: dense GEMV (N/T), CSR SpMV (A and A'), diagonal,
+// scalar.  These back LinearMapImpl::Apply of the reference:
+//   DenseMatrixImpl::Apply   src/epsilon/linear/dense_matrix_impl.cc:55-67 (dgemv_)
+//   SparseMatrixImpl::Apply  src/epsilon/linear/sparse_matrix_impl.h:24    (Eigen CSC * x)
+//   DiagonalMatrixImpl::Apply diagonal_matrix_impl.h:23, ScalarMatrixImpl::Apply scalar_matrix_impl.h:24
+// All arithmetic is fp64 (LinearMapImpl::Scalar = double, linear_map.h:35); indices int32.
+#include <cub/cub.cuh>
+
+#include "device.cuh"
+#include "internal.h"
+
+namespace eps {
+
+// =====================================================================================
+// Dense GEMV, column-major.  HBM-bound: 8*m*n bytes of A per launch.
+// =====================================================================================
+namespace {
+
+constexpr int kGemvBlock = 256;
+
+// y_part[s][i] = sum_{j in split s} A[i,j] x[j].  Each thread owns ROWS consecutive-by-
+// blockDim rows (coalesced across the warp), x chunk staged in shared memory.
+constexpr int kGemvNChunk = 512;  // columns of x staged per pass
+constexpr int kGemvNRows = 2;     // rows per thread
+__global__ void __launch_bounds__(kGemvBlock)
+GemvNKernel(const double* __restrict__ A, int64_t lda, int m, int n, int cols_per_split,
+            const double* __restrict__ x, double* __restrict__ out, int64_t out_stride, int tri) {
+  __shared__ double xs[kGemvNChunk];
+  const int split = blockIdx.y;
+  const int j0 = split * cols_per_split;
+  int j1 = min(n, j0 + cols_per_split);
+  // lower-triangular A: columns beyond this CTA's last row hold zeros
+  if (tri) j1 = min(j1, (int)min((int64_t)m, (int64_t)(blockIdx.x + 1) * (kGemvBlock * kGemvNRows)));
+  const int row0 = blockIdx.x * (kGemvBlock * kGemvNRows) + threadIdx.x;
+  double acc[kGemvNRows];
+#pragma unroll
+  for (int r = 0; r < kGemvNRows; r++) acc[r] = 0.0;
+  for (int jc = j0; jc < j1; jc += kGemvNChunk) {
+    const int nc = min(kGemvNChunk, j1 - jc);
+    __syncthreads();
+    for (int t = threadIdx.x; t < nc; t += kGemvBlock) xs[t] = x[jc + t];
+    __syncthreads();
+    const double* Ac = A + (int64_t)jc * lda;
+    int j = 0;
+    for (; j + 8 <= nc; j += 8) {
+      double a[kGemvNRows][8];
+#pragma unroll
+      for (int r = 0; r < kGemvNRows; r++) {
+        const int row = row0 + r * kGemvBlock;
+#pragma unroll
+        for (int u = 0; u < 8; u++)
+          a[r][u] = row < m ? LdStream(Ac + (int64_t)(j + u) * lda + row) : 0.0;
+      }
+#pragma unroll
+      for (int r = 0; r < kGemvNRows; r++)
+#pragma unroll
+        for (int u = 0; u < 8; u++) acc[r] += a[r][u] * xs[j + u];
+    }
+    for (; j < nc; j++) {
+#pragma unroll
+      for (int r = 0; r < kGemvNRows; r++) {
+        const int row = row0 + r * kGemvBlock;
+        if (row < m) acc[r] += LdStream(Ac + (int64_t)j * lda + row) * xs[j];
+      }
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < kGemvNRows; r++) {
+    const int row = row0 + r * kGemvBlock;
+    if (row < m) out[(int64_t)split * out_stride + row] = acc[r];
+  }
+}
+
+// y_part[s][j] = sum_{i in split s} A[i,j] x[i]  for a group of CG columns per CTA.
+constexpr int kGemvTCols = 8;
+__global__ void __launch_bounds__(kGemvBlock)
+GemvTKernel(const double* __restrict__ A, int64_t lda, int m, int n, int rows_per_split,
+            const double* __restrict__ x, double* __restrict__ out, int64_t out_stride, int tri) {
+  __shared__ double smem[kGemvTCols * 32];
+  const int jg = blockIdx.x * kGemvTCols;
+  const int split = blockIdx.y;
+  int i0 = split * rows_per_split;
+  const int i1 = min(m, i0 + rows_per_split);
+  if (tri) i0 = max(i0, jg);  // lower-triangular A: rows above the column group are zero
+  double acc[kGemvTCols];
+#pragma unroll
+  for (int c = 0; c < kGemvTCols; c++) acc[c] = 0.0;
+  const int ncol = min(kGemvTCols, n - jg);
+  if (ncol == kGemvTCols) {
+    for (int i = i0 + threadIdx.x; i < i1; i += kGemvBlock * 2) {
+      const int i2 = i + kGemvBlock;
+      const bool v2 = i2 < i1;
+      double a0[kGemvTCols], a1[kGemvTCols];
+      const double xv0 = x[i];
+      const double xv1 = v2 ? x[i2] : 0.0;
+#pragma unroll
+      for (int c = 0; c < kGemvTCols; c++) {
+        const double* col = A + (int64_t)(jg + c) * lda;
+        a0[c] = LdStream(col + i);
+        a1[c] = v2 ? LdStream(col + i2) : 0.0;
+      }
+#pragma unroll
+      for (int c = 0; c < kGemvTCols; c++) acc[c] += a0[c] * xv0 + a1[c] * xv1;
+    }
+  } else {
+    for (int i = i0 + threadIdx.x; i < i1; i += kGemvBlock) {
+      const double xv = x[i];
+      for (int c = 0; c < ncol; c++) acc[c] += A[(int64_t)(jg + c) * lda + i] * xv;
+    }
+  }
+  BlockSum<kGemvTCols>(acc, smem);
+  if (threadIdx.x == 0) {
+    for (int c = 0; c < ncol; c++) out[(int64_t)split * out_stride + jg + c] = acc[c];
+  }
+}
+
+// y = beta*y + alpha * sum_s part[s]
+__global__ void __launch_bounds__(256)
+SplitReduceKernel(int len, int splits, const double* __restrict__ part, int64_t stride,
+                  double alpha, double beta, double* __restrict__ y) {
+  int i = blockIdx.x * 256 + threadIdx.x;
+  if (i >= len) return;
+  double s = 0.0;
+  for (int k = 0; k < splits; k++) s += part[(int64_t)k * stride + i];
+  y[i] = (beta == 0.0 ? 0.0 : beta * y[i]) + alpha * s;
+}
+
+double* SplitScratch(Ctx* ctx, size_t count) { return GrowScratch(ctx, &ctx->split_scratch, count); }
+
+}  // namespace
+
+void DenseGemv(Ctx* ctx, const double* A, int lda, int m, int n, bool trans, double alpha,
+               const double* x, double beta, double* y, int tri) {
+  if (m == 0 || n == 0) return;
+  const int target = ctx->sm_count * 4;
+  const double bytes = (tri ? 4.0 : 8.0) * m * n + 8.0 * m + 8.0 * n;
+  if (!trans) {
+    const int rb = (m + kGemvBlock * kGemvNRows - 1) / (kGemvBlock * kGemvNRows);
+    int splits = std::max(1, std::min((n + 63) / 64, target / rb));
+    int cps = (n + splits - 1) / splits;
+    cps = (cps + 7) / 8 * 8;
+    splits = (n + cps - 1) / cps;
+    double* part = SplitScratch(ctx, (size_t)splits * m);
+    {
+      ProfScope ps(ctx, KC_GEMV_N, bytes);
+      GemvNKernel<<<dim3(rb, splits), kGemvBlock, 0, ctx->stream>>>(A, lda, m, n, cps, x, part, m, tri);
+      ctx->count_launch();
+    }
+    ProfScope ps(ctx, KC_VEC, 8.0 * splits * m);
+    SplitReduceKernel<<<(m + 255) / 256, 256, 0, ctx->stream>>>(m, splits, part, m, alpha, beta, y);
+    ctx->count_launch();
+  } else {
+    const int cg = (n + kGemvTCols - 1) / kGemvTCols;
+    int splits = std::max(1, std::min((m + 2047) / 2048, target / cg));
+    int rps = (m + splits - 1) / splits;
+    splits = (m + rps - 1) / rps;
+    double* part = SplitScratch(ctx, (size_t)splits * n);
+    {
+      ProfScope ps(ctx, KC_GEMV_T, bytes);
+      GemvTKernel<<<dim3(cg, splits), kGemvBlock, 0, ctx->stream>>>(A, lda, m, n, rps, x, part, n, tri);
+      ctx->count_launch();
+    }
+    ProfScope ps(ctx, KC_VEC, 8.0 * splits * n);
+    SplitReduceKernel<<<(n + 255) / 256, 256, 0, ctx->stream>>>(n, splits, part, n, alpha, beta, y);
+    ctx->count_launch();
+  }
+}
+
+// =====================================================================================
+// CSR SpMV: y = beta*y + alpha*A x.  T lanes cooperate on one row; 128-bit-friendly
+// streaming loads of (col,val), x gathered through L1/L2.
+// Algorithmic bytes: 12*nnz + 4*(m+1) + 8*n + 8*m   (SURVEY section 8d).
+// =====================================================================================
+namespace {
+
+constexpr int kSpmvBlock = 256;
+
+template <int T>
+__global__ void __launch_bounds__(kSpmvBlock)
+CsrSpmvKernel(int m, const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col,
+              const double* __restrict__ val, const double* __restrict__ x, double alpha,
+              double beta, double* __restrict__ y) {
+  constexpr int kRowsPerBlock = kSpmvBlock / T;
+  const int lane = threadIdx.x % T;
+  const int grp = threadIdx.x / T;
+  for (int row = blockIdx.x * kRowsPerBlock + grp; row < m; row += gridDim.x * kRowsPerBlock) {
+    const int start = __ldg(rowptr + row);
+    const int end = __ldg(rowptr + row + 1);
+    double acc = 0.0;
+    int k = start + lane;
+    // 4-way unrolled: indices and values first, then the dependent gathers.
+    for (; k + 3 * T < end; k += 4 * T) {
+      const int c0 = LdStreamI(col + k), c1 = LdStreamI(col + k + T);
+      const int c2 = LdStreamI(col + k + 2 * T), c3 = LdStreamI(col + k + 3 * T);
+      const double v0 = LdStream(val + k), v1 = LdStream(val + k + T);
+      const double v2 = LdStream(val + k + 2 * T), v3 = LdStream(val + k + 3 * T);
+      const double x0 = __ldg(x + c0), x1 = __ldg(x + c1), x2 = __ldg(x + c2), x3 = __ldg(x + c3);
+      acc += v0 * x0;
+      acc += v1 * x1;
+      acc += v2 * x2;
+      acc += v3 * x3;
+    }
+    for (; k < end; k += T) acc += LdStream(val + k) * __ldg(x + LdStreamI(col + k));
+    acc = GroupSum<T>(acc);
+    if (lane == 0) y[row] = (beta == 0.0 ? 0.0 : beta * y[row]) + alpha * acc;
+  }
+}
+
+template <int T>
+void LaunchCsr(Ctx* ctx, const Csr& A, double alpha, const double* x, double beta, double* y) {
+  constexpr int rows_per_block = kSpmvBlock / T;
+  int64_t blocks = ((int64_t)A.m + rows_per_block - 1) / rows_per_block;
+  int64_t cap = (int64_t)ctx->sm_count * 8 * 4;
+  int grid = (int)std::max<int64_t>(1, std::min(blocks, cap));
+  CsrSpmvKernel<T><<<grid, kSpmvBlock, 0, ctx->stream>>>(A.m, A.rowptr.p, A.col.p, A.val.p, x,
+                                                         alpha, beta, y);
+  ctx->count_launch();
+}
+
+__global__ void ExpandColIdKernel(int n, int64_t nnz, const int32_t* __restrict__ colptr,
+                                  int32_t* __restrict__ colid, int32_t* __restrict__ perm) {
+  int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= nnz) return;
+  int lo = 0, hi = n;  // find j with colptr[j] <= k < colptr[j+1]
+  while (hi - lo > 1) {
+    int mid = (lo + hi) >> 1;
+    if ((int64_t)colptr[mid] <= k) lo = mid; else hi = mid;
+  }
+  colid[k] = lo;
+  perm[k] = (int32_t)k;
+}
+
+__global__ void RowCountKernel(int64_t nnz, const int32_t* __restrict__ rowidx, int32_t* counts) {
+  int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k < nnz) atomicAdd(&counts[rowidx[k]], 1);
+}
+
+__global__ void GatherKernel(int64_t nnz, const int32_t* __restrict__ perm,
+                             const int32_t* __restrict__ colid, const double* __restrict__ vals,
+                             int32_t* __restrict__ col_out, double* __restrict__ val_out) {
+  int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= nnz) return;
+  int p = perm[k];
+  col_out[k] = colid[p];
+  val_out[k] = vals[p];
+}
+
+__global__ void DiagScaleKernel(int n, const double* __restrict__ d, double alpha,
+                                const double* __restrict__ x, double beta, double* __restrict__ y) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) y[i] = (beta == 0.0 ? 0.0 : beta * y[i]) + alpha * (d ? d[i] : 1.0) * x[i];
+}
+
+}  // namespace
+
+void CsrApply(Ctx* ctx, const Csr& A, double alpha, const double* x, double beta, double* y,
+              int kclass) {
+  if (A.m == 0) return;
+  ProfScope ps(ctx, kclass, 12.0 * A.nnz + 4.0 * (A.m + 1) + 8.0 * A.n + 8.0 * A.m);
+  double avg = A.m ? (double)A.nnz / A.m : 0;
+  if (avg <= 3) LaunchCsr<2>(ctx, A, alpha, x, beta, y);
+  else if (avg <= 8) LaunchCsr<4>(ctx, A, alpha, x, beta, y);
+  else if (avg <= 24) LaunchCsr<8>(ctx, A, alpha, x, beta, y);
+  else if (avg <= 64) LaunchCsr<16>(ctx, A, alpha, x, beta, y);
+  else LaunchCsr<32>(ctx, A, alpha, x, beta, y);
+}
+
+void BuildCsrFromHost(Ctx* ctx, int m, int n, int64_t nnz, const int64_t* rowptr,
+                      const int32_t* col, const double* val, Csr* out) {
+  EPS_CHECK(nnz < (int64_t)2147483647, "nnz %lld does not fit int32 offsets", (long long)nnz);
+  out->m = m; out->n = n; out->nnz = nnz;
+  std::vector<int32_t> rp(m + 1);
+  int maxr = 0;
+  for (int i = 0; i <= m; i++) rp[i] = (int32_t)rowptr[i];
+  for (int i = 0; i < m; i++) maxr = std::max(maxr, rp[i + 1] - rp[i]);
+  out->max_row_nnz = maxr;
+  out->rowptr.alloc(ctx, m + 1);
+  out->col.alloc(ctx, nnz);
+  out->val.alloc(ctx, nnz);
+  out->rowptr.upload(rp.data(), m + 1);
+  out->col.upload(col, nnz);
+  out->val.upload(val, nnz);
+  CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+}
+
+// CSC (= CSR of A') on the device -> CSR of A, by a stable radix sort on the row index
+// (deterministic: within a row the columns stay ascending).
+static void TransposeCsrOnDevice(Ctx* ctx, const Csr& At, Csr* A) {
+  const int m = At.n, n = At.m;
+  const int64_t nnz = At.nnz;
+  A->m = m; A->n = n; A->nnz = nnz;
+  A->rowptr.alloc(ctx, m + 1);
+  A->col.alloc(ctx, nnz);
+  A->val.alloc(ctx, nnz);
+  A->rowptr.zero();
+  if (nnz == 0) return;
+  DevBuf<int32_t> colid(ctx, nnz), perm_in(ctx, nnz), perm_out(ctx, nnz), keys_out(ctx, nnz);
+  const int tb = 256;
+  const unsigned gb = (unsigned)((nnz + tb - 1) / tb);
+  ExpandColIdKernel<<<gb, tb, 0, ctx->stream>>>(n, nnz, At.rowptr.p, colid.p, perm_in.p);
+  int end_bit = 1;
+  while ((1ll << end_bit) < (long long)m) end_bit++;
+  size_t tmp_bytes = 0;
+  CUDA_CHECK(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, At.col.p, keys_out.p, perm_in.p,
+                                             perm_out.p, (int)nnz, 0, end_bit, ctx->stream));
+  DevBuf<char> tmp(ctx, tmp_bytes);
+  CUDA_CHECK(cub::DeviceRadixSort::SortPairs(tmp.p, tmp_bytes, At.col.p, keys_out.p, perm_in.p,
+                                             perm_out.p, (int)nnz, 0, end_bit, ctx->stream));
+  GatherKernel<<<gb, tb, 0, ctx->stream>>>(nnz, perm_out.p, colid.p, At.val.p, A->col.p, A->val.p);
+  // row pointer: counts -> exclusive scan
+  DevBuf<int32_t> counts(ctx, m + 1);
+  counts.zero();
+  RowCountKernel<<<gb, tb, 0, ctx->stream>>>(nnz, At.col.p, counts.p);
+  size_t scan_bytes = 0;
+  CUDA_CHECK(cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, counts.p, A->rowptr.p, m + 1, ctx->stream));
+  DevBuf<char> tmp2(ctx, scan_bytes);
+  CUDA_CHECK(cub::DeviceScan::ExclusiveSum(tmp2.p, scan_bytes, counts.p, A->rowptr.p, m + 1, ctx->stream));
+  CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+  CUDA_CHECK(cudaGetLastError());
+}
+
+double MapAlgorithmicBytes(const MapData& A, bool trans) {
+  switch (A.kind) {
+    case MK_DENSE: return 8.0 * A.m * A.n + 8.0 * A.m + 8.0 * A.n;
+    case MK_SPARSE: {
+      const Csr& c = trans ? A.csr_t : A.csr;
+      return 12.0 * c.nnz + 4.0 * (c.m + 1) + 8.0 * c.n + 8.0 * c.m;
+    }
+    case MK_DIAGONAL: return 24.0 * A.n;
+    default: return 16.0 * A.n;
+  }
+}
+
+void MapApply(Ctx* ctx, const MapData& A, bool trans, double alpha, const double* x, double beta,
+              double* y) {
+  switch (A.kind) {
+    case MK_DENSE:
+      DenseGemv(ctx, A.dense.p, A.m, A.m, A.n, trans, alpha, x, beta, y);
+      break;
+    case MK_SPARSE:
+      CsrApply(ctx, trans ? A.csr_t : A.csr, alpha, x, beta, y, trans ? KC_SPMV_T : KC_SPMV_N);
+      break;
+    case MK_DIAGONAL:
+    case MK_SCALAR: {
+      if (A.n == 0) break;
+      ProfScope ps(ctx, KC_VEC, 24.0 * A.n);
+      const double a = A.kind == MK_SCALAR ? alpha * A.alpha : alpha;
+      DiagScaleKernel<<<(A.n + 255) / 256, 256, 0, ctx->stream>>>(
+          A.n, A.kind == MK_DIAGONAL ? A.diag.p : nullptr, a, x, beta, y);
+      ctx->count_launch();
+      break;
+    }
+    default:
+      throw Error(EPS_ERR_INVALID, "map kind not applicable on device");
+  }
+}
+
+}  // namespace eps
+
+// =====================================================================================
+// C ABI
+// =====================================================================================
+using namespace eps;
+
+#define EPS_API_BEGIN try {
+#define EPS_API_END                                  \
+    return EPS_OK;                                   \
+  } catch (const eps::Error& e) {                    \
+    eps::SetLastError(e.what());                     \
+    return e.code;                                   \
+  } catch (const std::exception& e) {                \
+    eps::SetLastError(e.what());                     \
+    return EPS_ERR_INVALID;                          \
+  }
+
+extern "C" {
+
+int eps_map_dense(eps_ctx* ctx, int m, int n, const double* colmajor, eps_map** out) {
+  EPS_API_BEGIN
+  EPS_CHECK(ctx && out && m >= 0 && n >= 0, "eps_map_dense arguments");
+  CUDA_CHECK(cudaSetDevice(ctx->c.device));
+  auto d = std::make_shared<MapData>();
+  d->ctx = &ctx->c; d->kind = MK_DENSE; d->m = m; d->n = n;
+  d->dense.alloc(&ctx->c, (size_t)m * n);
+  // chunked upload keeps the pageable staging bounded for 80 GB matrices
+  const size_t total = (size_t)m * n, chunk = (size_t)1 << 27;
+  for (size_t off = 0; off < total; off += chunk) {
+    size_t cnt = std::min(chunk, total - off);
+    CUDA_CHECK(cudaMemcpyAsync(d->dense.p + off, colmajor + off, cnt * sizeof(double),
+                               cudaMemcpyHostToDevice, ctx->c.stream));
+  }
+  CUDA_CHECK(cudaStreamSynchronize(ctx->c.stream));
+  auto* h = new eps_map();
+  h->d = d;
+  *out = h;
+  EPS_API_END
+}
+
+int eps_map_csc(eps_ctx* ctx, int m, int n, int64_t nnz, const int32_t* colptr,
+                const int32_t* rowidx, const double* vals, eps_map** out) {
+  EPS_API_BEGIN
+  EPS_CHECK(ctx && out && m >= 0 && n >= 0 && nnz >= 0, "eps_map_csc arguments");
+  EPS_CHECK(nnz < (int64_t)2147483647, "nnz %lld does not fit int32 offsets (shard the rows)",
+            (long long)nnz);
+  EPS_CHECK(colptr[0] == 0 && colptr[n] == nnz, "colptr[0]=%d colptr[n]=%d nnz=%lld", colptr[0],
+            colptr[n], (long long)nnz);
+  CUDA_CHECK(cudaSetDevice(ctx->c.device));
+  auto d = std::make_shared<MapData>();
+  d->ctx = &ctx->c; d->kind = MK_SPARSE; d->m = m; d->n = n;
+  // CSR of A' is the wire layout itself.
+  Csr& t = d->csr_t;
+  t.m = n; t.n = m; t.nnz = nnz;
+  t.rowptr.alloc(&ctx->c, n + 1);
+  t.col.alloc(&ctx->c, nnz);
+  t.val.alloc(&ctx->c, nnz);
+  t.rowptr.upload(colptr, n + 1);
+  t.col.upload(rowidx, nnz);
+  t.val.upload(vals, nnz);
+  CUDA_CHECK(cudaStreamSynchronize(ctx->c.stream));
+  TransposeCsrOnDevice(&ctx->c, t, &d->csr);
+  if (nnz <= (int64_t)4 << 20) {
+    d->h_colptr.assign(colptr, colptr + n + 1);
+    d->h_rowidx.assign(rowidx, rowidx + nnz);
+    d->h_vals.assign(vals, vals + nnz);
+    d->has_host = true;
+  }
+  auto* h = new eps_map();
+  h->d = d;
+  *out = h;
+  EPS_API_END
+}
+
+int eps_map_diagonal(eps_ctx* ctx, int n, const double* dvals, eps_map** out) {
+  EPS_API_BEGIN
+  EPS_CHECK(ctx && out && n >= 0, "eps_map_diagonal arguments");
+  CUDA_CHECK(cudaSetDevice(ctx->c.device));
+  auto d = std::make_shared<MapData>();
+  d->ctx = &ctx->c; d->kind = MK_DIAGONAL; d->m = n; d->n = n;
+  d->diag.alloc(&ctx->c, n);
+  d->diag.upload(dvals, n);
+  d->h_diag.assign(dvals, dvals + n);
+  CUDA_CHECK(cudaStreamSynchronize(ctx->c.stream));
+  auto* h = new eps_map();
+  h->d = d;
+  *out = h;
+  EPS_API_END
+}
+
+int eps_map_scalar(eps_ctx* ctx, int n, double alpha, eps_map** out) {
+  EPS_API_BEGIN
+  EPS_CHECK(ctx && out && n >= 0, "eps_map_scalar arguments");
+  auto d = std::make_shared<MapData>();
+  d->ctx = &ctx->c; d->kind = MK_SCALAR; d->m = n; d->n = n; d->alpha = alpha;
+  auto* h = new eps_map();
+  h->d = d;
+  *out = h;
+  EPS_API_END
+}
+
+int eps_map_kronecker(eps_ctx* ctx, eps_map* a, eps_map* b, eps_map** out) {
+  EPS_API_BEGIN
+  EPS_CHECK(ctx && a && b && out, "eps_map_kronecker arguments");
+  auto d = std::make_shared<MapData>();
+  d->ctx = &ctx->c; d->kind = MK_KRONECKER;
+  d->ka = a->d; d->kb = b->d; d->ka_trans = a->trans; d->kb_trans = b->trans;
+  d->m = a->m() * b->m();
+  d->n = a->n() * b->n();
+  auto* h = new eps_map();
+  h->d = d;
+  *out = h;
+  EPS_API_END
+}
+
+int eps_map_transpose(eps_map* map, eps_map** out) {
+  EPS_API_BEGIN
+  EPS_CHECK(map && out, "eps_map_transpose arguments");
+  auto* h = new eps_map();
+  h->d = map->d;
+  h->trans = !map->trans;
+  *out = h;
+  EPS_API_END
+}
+
+int eps_map_dims(const eps_map* map, int* m, int* n) {
+  EPS_API_BEGIN
+  EPS_CHECK(map, "null map");
+  if (m) *m = map->m();
+  if (n) *n = map->n();
+  EPS_API_END
+}
+
+namespace eps {
+void KroneckerApply(Ctx* ctx, const MapData& K, bool trans, const double* x, double* y);
+}
+
+int eps_map_apply_dev(eps_map* map, const double* x_dev, double* y_dev) {
+  EPS_API_BEGIN
+  EPS_CHECK(map && x_dev && y_dev, "eps_map_apply_dev arguments");
+  Ctx* ctx = map->d->ctx;
+  CUDA_CHECK(cudaSetDevice(ctx->device));
+  if (map->d->kind == MK_KRONECKER) KroneckerApply(ctx, *map->d, map->trans, x_dev, y_dev);
+  else MapApply(ctx, *map->d, map->trans, 1.0, x_dev, 0.0, y_dev);
+  CUDA_CHECK(cudaGetLastError());
+  EPS_API_END
+}
+
+int eps_map_apply(eps_map* map, const double* x, double* y) {
+  EPS_API_BEGIN
+  EPS_CHECK(map && x && y, "eps_map_apply arguments");
+  Ctx* ctx = map->d->ctx;
+  CUDA_CHECK(cudaSetDevice(ctx->device));
+  DevBuf<double> dx(ctx, map->n()), dy(ctx, map->m());
+  dx.upload(x, map->n());
+  if (map->d->kind == MK_KRONECKER) KroneckerApply(ctx, *map->d, map->trans, dx.p, dy.p);
+  else MapApply(ctx, *map->d, map->trans, 1.0, dx.p, 0.0, dy.p);
+  CUDA_CHECK(cudaGetLastError());
+  dy.download(y, map->m());
+  EPS_API_END
+}
+
+int eps_map_time(eps_map* map, int reps, float* ms_per_apply, double* algorithmic_bytes) {
+  EPS_API_BEGIN
+  EPS_CHECK(map && reps > 0, "eps_map_time arguments");
+  Ctx* ctx = map->d->ctx;
+  CUDA_CHECK(cudaSetDevice(ctx->device));
+  DevBuf<double> dx(ctx, map->n()), dy(ctx, map->m());
+  VecFill(ctx, map->n(), 1.0, dx.p);
+  for (int i = 0; i < 3; i++) MapApply(ctx, *map->d, map->trans, 1.0, dx.p, 0.0, dy.p);
+  cudaEvent_t e0, e1;
+  CUDA_CHECK(cudaEventCreate(&e0));
+  CUDA_CHECK(cudaEventCreate(&e1));
+  CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+  CUDA_CHECK(cudaEventRecord(e0, ctx->stream));
+  for (int i = 0; i < reps; i++) MapApply(ctx, *map->d, map->trans, 1.0, dx.p, 0.0, dy.p);
+  CUDA_CHECK(cudaEventRecord(e1, ctx->stream));
+  CUDA_CHECK(cudaEventSynchronize(e1));
+  float ms = 0;
+  CUDA_CHECK(cudaEventElapsedTime(&ms, e0, e1));
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  if (ms_per_apply) *ms_per_apply = ms / reps;
+  if (algorithmic_bytes) *algorithmic_bytes = MapAlgorithmicBytes(*map->d, map->trans);
+  EPS_API_END
+}
+
+void eps_map_destroy(eps_map* map) { delete map; }
+
+}  // extern "C"

@@ -1,0 +1,62 @@
+// Host-visible declarations of the fused prox kernels (prox_elem.cu).
+#pragma once
+#include "internal.h"
+
+namespace eps {
+
+// One prox function of an elementwise / block stage after the VectorProx reduction
+// (reference: VectorProx::InitScalar, src/epsilon/prox/vector_prox.cc:51-70):
+//   w  = u + y_old            (prox_admm.cc:142  u_ += y_[i])
+//   v  = Bs*w + g             (vector_prox.cc:131 PreProcessInput, B = (beta/gamma) H A')
+//   x' = prox_{lam f}(v)      (ApplyVector)
+//   x  = Cs*(x' - g)          (vector_prox.cc:135 PostProcessOutput, C = (1/beta) H')
+//   y  = As*x                 (prox_admm.cc:144  y_[i] = A_*x_[i])
+//   u  = w - y                (prox_admm.cc:145)
+struct ElemSeg {
+  int64_t u_off;   // first row of the constraint block in u (and of the span of y)
+  int64_t y_off;   // offset of y_i in the y arena
+  int64_t x_off;   // offset of x_i in the x arena
+  int64_t g_off;   // offset of g in the constant arena, -1 when absent
+  int64_t q_off;   // SUM_QUANTILE: alpha at q_off, beta at q_off + len; -1 otherwise
+  int32_t len;
+  int32_t type;    // eps_prox_type
+  double lam, Bs, Cs, As;
+  double zone_m, zone_alpha, zone_beta;  // scaled_zone.cc:34-76
+};
+
+struct SegPair {
+  int64_t a_off, b_off;
+  int32_t len;
+  double coef;
+};
+
+// Fused elementwise step over the segments of one stage.
+void ElemProxStep(Ctx* ctx, const ElemSeg* segs_dev, const int64_t* prefix_dev, int nseg,
+                  int64_t total, int type, const double* consts, double* u, const double* y_old,
+                  double* y_new, double* x);
+// NORM_2 block soft threshold, one warp (len <= 1024) or one CTA per segment.
+void Norm2ProxStep(Ctx* ctx, const ElemSeg* segs_dev, int nseg, int max_len, const double* consts,
+                   double* u, const double* y_old, double* y_new, double* x);
+// TOTAL_VARIATION_1D for one segment (host copy of the segment passed by value).
+void Tv1dProxStep(Ctx* ctx, const ElemSeg& seg, const double* consts, double* u, const double* y_old,
+                  double* y_new, double* x, double* work /* 9*len doubles */);
+size_t Tv1dWorkDoubles(int64_t len);
+
+// dst[a_off + j] += c1*src1[b_off + j] + c2*src2[b_off + j]   (src2 may be null)
+void SegAxpy(Ctx* ctx, const SegPair* pairs_dev, const int64_t* prefix_dev, int nseg, int64_t total,
+             double* dst, const double* src1, double c1, const double* src2, double c2);
+// out[0] += sum_seg coef_seg * sum_j v[a_off + j]^2 ; out[1] = max(out[1], max_seg sum_j w[b_off+j]^2)
+// (either part may be skipped by passing null)
+void SegSumSq(Ctx* ctx, const SegPair* pairs_dev, const SegPair* pairs_host, int nseg,
+              const double* v, double* out_sum, const double* w, double* out_max);
+
+// KKT prox with a simple scalar constraint block A = a*I:
+//   pre : w = u + y_old (stored in u), rhs = a*w + c0
+//   post: y_new = a*x, u = w - y_new
+void KktScalarPre(Ctx* ctx, int64_t n, double a, const double* c0, double* u, const double* y_old,
+                  double* rhs);
+void KktScalarPost(Ctx* ctx, int64_t n, double a, const double* x, double* u, double* y_new);
+// x = dinv .* rhs
+void KktDiagSolve(Ctx* ctx, int64_t n, const double* dinv, const double* rhs, double* x);
+
+}  // namespace eps

@@ -1,0 +1,148 @@
+// Fused prox kernels: prox + y = A x + dual update in one pass over HBM.
+// Compiled with -fmad=false so that the elementwise arithmetic rounds exactly like the
+// reference's x86-64 build (no FMA contraction).
+//
+// Reference operators restated here (each on the reduced form of VectorProx,
+// src/epsilon/prox/vector_prox.cc:51-70,131-137):
+//   ScaledZoneProx   src/epsilon/prox/scaled_zone.cc:78-104  (NORM_1, SUM_HINGE, SUM_DEADZONE, SUM_QUANTILE)
+//   NonNegativeProx  src/epsilon/prox/non_negative.cc:5-9
+//   Norm2Prox        src/epsilon/prox/norm_2.cc:6-17
+//   NewtonProx+Logistic  src/epsilon/prox/newton.cc:47-91, sum_logistic.cc:8-32
+//   TotalVariation1DProx src/epsilon/prox/total_variation_1d.cc:12-24 -> Johnson's DP (glmgen tf_dp.c:43-170)
+#include "device.cuh"
+#include "prox.cuh"
+
+namespace eps {
+
+namespace {
+
+constexpr int kBlock = 256;
+constexpr int kUnroll = 4;
+
+__device__ __forceinline__ int FindSeg(const int64_t* __restrict__ prefix, int nseg, int64_t e) {
+  int lo = 0, hi = nseg;  // prefix[lo] <= e < prefix[lo+1]
+  while (hi - lo > 1) {
+    int mid = (lo + hi) >> 1;
+    if (prefix[mid] <= e) lo = mid; else hi = mid;
+  }
+  return lo;
+}
+
+// scaled_zone.cc:78-104 with C = 0.
+__device__ __forceinline__ double ScaledZone(double x, double lam, double M, double a, double b) {
+  if (fabs(x) <= M) return x;
+  if (x > M + lam * a) return x - lam * a;
+  if (x < -M - lam * b) return x + lam * b;
+  return x > 0 ? M : -M;
+}
+
+// Solve x - v + lam*sigma(x) = 0 (newton.cc:10-16 ProxResidual with Logistic::gradf),
+// damped Newton from x = v with the reference's backtracking constants (newton.cc:63-77).
+// All lanes of the warp iterate together and leave when every lane has converged.
+__device__ __forceinline__ double LogisticProx(double v, double lam, bool active) {
+  double x = v;
+  auto sigma = [](double t) {
+    if (t >= 0) { double e = exp(-t); return 1.0 / (1.0 + e); }
+    double e = exp(t);
+    return e / (1.0 + e);
+  };
+  double s = sigma(x);
+  double g = x - v + lam * s;
+  bool done = !active;
+  for (int it = 0; it < 100; it++) {
+    if (__all_sync(kFull, done)) break;
+    if (!done) {
+      const double h = s * (1.0 - s);
+      const double dx = g / (1.0 + lam * h);
+      double theta = 1.0;
+      bool moved = false;
+      while (theta > 1e-12) {
+        const double nx = x - theta * dx;
+        const double ns = sigma(nx);
+        const double ng = nx - v + lam * ns;
+        if (fabs(ng) <= (1.0 - 0.001 * theta) * fabs(g)) {
+          x = nx; s = ns; g = ng; moved = true;
+          break;
+        }
+        theta *= 0.5;
+      }
+      // converged to working precision, or no further decrease is representable
+      if (!moved || fabs(g) <= 2.3e-16 * fmax(1.0, fabs(v))) done = true;
+    }
+  }
+  return x;
+}
+
+template <int TYPE>
+__global__ void __launch_bounds__(kBlock)
+ElemProxKernel(const ElemSeg* __restrict__ segs, const int64_t* __restrict__ prefix, int nseg,
+               int64_t total, const double* __restrict__ consts, double* __restrict__ u,
+               const double* __restrict__ y_old, double* __restrict__ y_new, double* __restrict__ x) {
+  const int64_t stride = (int64_t)gridDim.x * kBlock * kUnroll;
+  for (int64_t base = (int64_t)blockIdx.x * kBlock * kUnroll + threadIdx.x;
+       base - threadIdx.x < total; base += stride) {
+#pragma unroll
+    for (int k = 0; k < kUnroll; k++) {
+      const int64_t e = base + (int64_t)k * kBlock;
+      const bool active = e < total;
+      double w = 0, v = 0, g = 0, lam = 0, xo = 0;
+      int64_t j = 0;
+      ElemSeg sg;
+      if (active) {
+        const int si = nseg == 1 ? 0 : FindSeg(prefix, nseg, e);
+        sg = segs[si];
+        j = e - prefix[si];
+        w = u[sg.u_off + j] + y_old[sg.y_off + j];
+        g = sg.g_off >= 0 ? consts[sg.g_off + j] : 0.0;
+        v = sg.Bs * w + g;
+        lam = sg.lam;
+      }
+      if (TYPE == EPS_PROX_SUM_LOGISTIC) {
+        xo = LogisticProx(v, lam, active);  // warp-cooperative: every lane takes part
+      } else if (active) {
+        if (TYPE == EPS_PROX_NON_NEGATIVE) {
+          xo = fmax(v, 0.0);
+        } else if (TYPE == EPS_PROX_SUM_QUANTILE) {
+          const double a = sg.q_off >= 0 ? consts[sg.q_off + j] : sg.zone_alpha;
+          const double b = sg.q_off >= 0 ? consts[sg.q_off + sg.len + j] : sg.zone_beta;
+          xo = ScaledZone(v, lam, 0.0, a, b);
+        } else {
+          xo = ScaledZone(v, lam, sg.zone_m, sg.zone_alpha, sg.zone_beta);
+        }
+      }
+      if (active) {
+        const double xv = sg.Cs * (xo - g);
+        const double yn = sg.As * xv;
+        x[sg.x_off + j] = xv;
+        y_new[sg.y_off + j] = yn;
+        u[sg.u_off + j] = w - yn;
+      }
+    }
+  }
+}
+
+}  // namespace
+
+void ElemProxStep(Ctx* ctx, const ElemSeg* segs, const int64_t* prefix, int nseg, int64_t total,
+                  int type, const double* consts, double* u, const double* y_old, double* y_new,
+                  double* x) {
+  if (total <= 0) return;
+  ProfScope ps(ctx, KC_PROX, 40.0 * total);
+  const int grid = GridFor(total, kBlock, kUnroll, ctx->sm_count);
+#define LAUNCH(T)                                                                              \
+  ElemProxKernel<T><<<grid, kBlock, 0, ctx->stream>>>(segs, prefix, nseg, total, consts, u, y_old, \
+                                                      y_new, x)
+  switch (type) {
+    case EPS_PROX_NON_NEGATIVE: LAUNCH(EPS_PROX_NON_NEGATIVE); break;
+    case EPS_PROX_SUM_QUANTILE: LAUNCH(EPS_PROX_SUM_QUANTILE); break;
+    case EPS_PROX_SUM_LOGISTIC: LAUNCH(EPS_PROX_SUM_LOGISTIC); break;
+    case EPS_PROX_NORM_1:
+    case EPS_PROX_SUM_HINGE:
+    case EPS_PROX_SUM_DEADZONE: LAUNCH(EPS_PROX_NORM_1); break;
+    default: throw Error(EPS_ERR_INVALID, Format("prox type %d is not elementwise", type));
+  }
+#undef LAUNCH
+  ctx->count_launch();
+}
+
+}  // namespace eps
