@@ -55,15 +55,13 @@ ProfScope::~ProfScope() {
   ctx->prof[kc].bytes += bytes;
 }
 
-ReduceScratch* GetReduceScratch(Ctx* ctx) {
-  static thread_local std::unique_ptr<ReduceScratch> view;
+ReduceScratch GetReduceScratch(Ctx* ctx) {
   if (ctx->red_partials.n == 0) {
     ctx->red_partials.alloc(ctx, 4096);
     ctx->red_counter.alloc(ctx, 16);
     ctx->red_counter.zero();
   }
-  view.reset(new ReduceScratch{ctx->red_partials, ctx->red_counter});
-  return view.get();
+  return ReduceScratch{ctx->red_partials.p, ctx->red_counter.p};
 }
 
 double* GrowScratch(Ctx* ctx, DevBuf<double>* buf, size_t count) {

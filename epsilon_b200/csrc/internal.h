@@ -176,6 +176,7 @@ namespace eps {
 void MapApply(Ctx* ctx, const MapData& A, bool trans, double alpha, const double* x,
               double beta, double* y);
 double MapAlgorithmicBytes(const MapData& A, bool trans);
+void KroneckerApply(Ctx* ctx, const MapData& K, bool trans, const double* x, double* y);
 void CsrApply(Ctx* ctx, const Csr& A, double alpha, const double* x, double beta, double* y,
               int kclass);
 void BuildCsrFromHost(Ctx* ctx, int m, int n, int64_t nnz, const int64_t* rowptr,
@@ -193,10 +194,10 @@ void VecCopy(Ctx* ctx, int64_t n, const double* x, double* out);
 void VecDot(Ctx* ctx, int64_t n, const double* x, const double* y, double* out_dev, bool accumulate);
 // scratch for two-stage reductions
 struct ReduceScratch {
-  DevBuf<double>& partials;
-  DevBuf<unsigned int>& counter;
+  double* partials;
+  unsigned int* counter;
 };
-ReduceScratch* GetReduceScratch(Ctx* ctx);
+ReduceScratch GetReduceScratch(Ctx* ctx);
 double* GrowScratch(Ctx* ctx, DevBuf<double>* buf, size_t count);
 
 // ---- composite block operator (BlockMatrix, vector/block_matrix.h) --------------------

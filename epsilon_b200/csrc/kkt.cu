@@ -308,15 +308,15 @@ void KktSolver::Solve(const double* rhs, double* x) {
       DenseGemv(ctx, W.p, (int)n, (int)n, (int)n, true, 1.0, tn1.p, 0.0, x, 1);
       break;
     case EPS_KKT_CG: {
-      ReduceScratch* rs = GetReduceScratch(ctx);
+      ReduceScratch rs = GetReduceScratch(ctx);
       const int grid = std::min(1024, GridFor(n, kBlock, kUnroll, ctx->sm_count, 4));
       double* rr0 = scal.p;       // ping-pong rr[0], rr[1]
       double* pw = scal.p + 2;
       double* bb = scal.p + 3;
       VecDot(ctx, n, rhs, rhs, bb, false);
       MatVec(x, cg_w.p);
-      CgInitKernel<<<grid, kBlock, 0, ctx->stream>>>(n, rhs, cg_w.p, cg_r.p, cg_p.p, rs->partials.p,
-                                                      rs->counter.p, rr0);
+      CgInitKernel<<<grid, kBlock, 0, ctx->stream>>>(n, rhs, cg_w.p, cg_r.p, cg_p.p, rs.partials,
+                                                      rs.counter, rr0);
       ctx->count_launch();
       CUDA_CHECK(cudaMemcpyAsync(h_scal, scal.p, 4 * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
       CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
@@ -329,7 +329,7 @@ void KktSolver::Solve(const double* rhs, double* x) {
         MatVec(cg_p.p, cg_w.p);
         VecDot(ctx, n, cg_p.p, cg_w.p, pw, false);
         CgUpdateXRKernel<<<grid, kBlock, 0, ctx->stream>>>(n, rr0 + cur, pw, cg_p.p, cg_w.p, x, cg_r.p,
-                                                            rs->partials.p, rs->counter.p, rr0 + (cur ^ 1));
+                                                            rs.partials, rs.counter, rr0 + (cur ^ 1));
         ctx->count_launch();
         CUDA_CHECK(cudaMemcpyAsync(h_scal, rr0 + (cur ^ 1), sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
         CgUpdatePKernel<<<grid, kBlock, 0, ctx->stream>>>(n, rr0 + (cur ^ 1), rr0 + cur, cg_r.p, cg_p.p);

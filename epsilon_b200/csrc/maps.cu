@@ -489,10 +489,6 @@ int eps_map_dims(const eps_map* map, int* m, int* n) {
   EPS_API_END
 }
 
-namespace eps {
-void KroneckerApply(Ctx* ctx, const MapData& K, bool trans, const double* x, double* y);
-}
-
 int eps_map_apply_dev(eps_map* map, const double* x_dev, double* y_dev) {
   EPS_API_BEGIN
   EPS_CHECK(map && x_dev && y_dev, "eps_map_apply_dev arguments");

@@ -80,11 +80,11 @@ void VecCopy(Ctx* ctx, int64_t n, const double* x, double* out) {
 }
 
 void VecDot(Ctx* ctx, int64_t n, const double* x, const double* y, double* out_dev, bool accumulate) {
-  ReduceScratch* rs = GetReduceScratch(ctx);
+  ReduceScratch rs = GetReduceScratch(ctx);
   int grid = GridFor(n > 0 ? n : 1, kBlock, kUnroll, ctx->sm_count, 4);
   if (grid > 1024) grid = 1024;
   ProfScope ps(ctx, KC_REDUCE, 16.0 * n);
-  DotKernel<<<grid, kBlock, 0, ctx->stream>>>(n, x, y, rs->partials.p, rs->counter.p, out_dev,
+  DotKernel<<<grid, kBlock, 0, ctx->stream>>>(n, x, y, rs.partials, rs.counter, out_dev,
                                               accumulate ? 1 : 0);
   ctx->count_launch();
 }

@@ -1,0 +1,64 @@
+"""LinearMapImpl::Apply parity (reference tests: src/epsilon/linear/dense_matrix_impl_test.cc:24-29,
+linear_map_test.cc, kronecker_product_impl_test.cc:9-20; tolerance 1e-8 there, tighter here)."""
+import numpy as np
+import pytest
+import scipy.sparse as sp
+
+from epsilon_b200.problem import LinearMapSpec
+from epsilon_b200.solver import LinearMap
+
+pytestmark = pytest.mark.gpu
+
+
+def _check(ctx, spec, rng, tol=1e-12):
+    lm = LinearMap(ctx, spec)
+    m, n = lm.shape
+    assert (m, n) == (spec.m, spec.n)
+    x = rng.standard_normal(n)
+    y = lm.apply(x)
+    ref = spec.apply(x)
+    scale = max(1.0, np.abs(ref).max())
+    assert np.abs(y - ref).max() <= tol * scale * max(1, n) ** 0.5
+    yt = rng.standard_normal(m)
+    t = lm.transpose()
+    assert t.shape == (n, m)
+    xt = t.apply(yt)
+    reft = np.asarray(spec.to_scipy().T @ yt).ravel()
+    scale = max(1.0, np.abs(reft).max())
+    assert np.abs(xt - reft).max() <= tol * scale * max(1, m) ** 0.5
+
+
+@pytest.mark.parametrize("m,n", [(1, 1), (3, 5), (64, 64), (1000, 37), (37, 1000), (513, 2049), (4096, 300)])
+def test_dense(ctx, m, n):
+    rng = np.random.default_rng(m * 1000 + n)
+    _check(ctx, LinearMapSpec.Dense(rng.standard_normal((m, n))), rng)
+
+
+@pytest.mark.parametrize("m,n,d", [(5, 7, 0.5), (100, 50, 0.1), (2000, 300, 0.01), (300, 2000, 0.05),
+                                   (1000, 1000, 0.3), (50, 40, 0.0)])
+def test_sparse(ctx, m, n, d):
+    rng = np.random.default_rng(m + n)
+    a = sp.random(m, n, density=d, random_state=np.random.RandomState(1), format="csc")
+    _check(ctx, LinearMapSpec.Sparse(a), rng)
+
+
+def test_sparse_ragged_rows(ctx):
+    rng = np.random.default_rng(3)
+    a = sp.lil_matrix((200, 300))
+    a[0, :] = rng.standard_normal(300)          # one full row
+    a[5, 3] = 2.0                               # one singleton
+    a[100:150, 10] = rng.standard_normal((50, 1))  # one full column segment; many empty rows
+    _check(ctx, LinearMapSpec.Sparse(a.tocsc()), rng)
+
+
+def test_diagonal_scalar(ctx):
+    rng = np.random.default_rng(0)
+    _check(ctx, LinearMapSpec.Diagonal(rng.standard_normal(777)), rng)
+    _check(ctx, LinearMapSpec.Scalar(-2.5, 1234), rng)
+
+
+def test_kronecker(ctx):
+    rng = np.random.default_rng(1)
+    a = LinearMapSpec.Dense(rng.standard_normal((3, 4)))
+    b = LinearMapSpec.Sparse(sp.random(5, 6, density=0.5, random_state=np.random.RandomState(2)))
+    _check(ctx, LinearMapSpec.Kronecker(a, b), rng)
