@@ -30,6 +30,7 @@ Ctx::~Ctx() {
     if (prof_ev[i]) cudaEventDestroy(prof_ev[i]);
   split_scratch.release();
   seg_scratch.release();
+  sell_scratch.release();
   red_partials.release();
   red_counter.release();
   if (own_stream && stream) cudaStreamDestroy(stream);

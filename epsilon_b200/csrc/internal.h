@@ -107,7 +107,7 @@ struct Ctx {
   Prof prof[KC_COUNT];
   cudaEvent_t prof_ev[2] = {nullptr, nullptr};
   // scratch owned by the context (grown on demand, never during graph capture)
-  DevBuf<double> split_scratch, seg_scratch, red_partials;
+  DevBuf<double> split_scratch, seg_scratch, red_partials, sell_scratch;
   DevBuf<unsigned int> red_counter;
   int64_t scratch_generation = 0;
   ~Ctx();
@@ -136,6 +136,17 @@ struct Csr {
   int max_row_nnz = 0;
 };
 
+// Column-tiled SELL-32 storage (sell.cu).
+struct Sell {
+  bool built = false;
+  int R = 0, Cn = 0, T = 0, TW = 0, RR = 0, rows_per = 0, n_slices = 0;
+  int64_t nnz = 0, n_val = 0, n_idx = 0;
+  DevBuf<int32_t> sl_len, rowid;
+  DevBuf<int64_t> voff, ioff;
+  DevBuf<double> val;
+  DevBuf<uint16_t> idx;
+};
+
 struct MapData {
   Ctx* ctx = nullptr;
   int kind = MK_SCALAR;
@@ -144,6 +155,7 @@ struct MapData {
   DevBuf<double> dense;
   // sparse: CSR of A and CSR of A' (= the CSC wire layout)
   Csr csr, csr_t;
+  Sell sell, sell_t;  // built for large matrices; used by Apply instead of the CSR kernel
   // small host copy of the CSC arrays for block merging (only when nnz is small)
   std::vector<int32_t> h_colptr, h_rowidx;
   std::vector<double> h_vals;
@@ -181,6 +193,8 @@ void CsrApply(Ctx* ctx, const Csr& A, double alpha, const double* x, double beta
               int kclass);
 void BuildCsrFromHost(Ctx* ctx, int m, int n, int64_t nnz, const int64_t* rowptr,
                       const int32_t* col, const double* val, Csr* out);
+void BuildSell(Ctx* ctx, const Csr& A, Sell* S);
+void SellApply(Ctx* ctx, const Sell& S, double alpha, const double* x, double beta, double* y, int kclass);
 void DenseGemv(Ctx* ctx, const double* A, int lda, int m, int n, bool trans, double alpha,
                const double* x, double beta, double* y, int tri = 0);
 

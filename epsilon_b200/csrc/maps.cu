@@ -337,9 +337,12 @@ void MapApply(Ctx* ctx, const MapData& A, bool trans, double alpha, const double
     case MK_DENSE:
       DenseGemv(ctx, A.dense.p, A.m, A.m, A.n, trans, alpha, x, beta, y);
       break;
-    case MK_SPARSE:
-      CsrApply(ctx, trans ? A.csr_t : A.csr, alpha, x, beta, y, trans ? KC_SPMV_T : KC_SPMV_N);
+    case MK_SPARSE: {
+      const Sell& S = trans ? A.sell_t : A.sell;
+      if (S.built) SellApply(ctx, S, alpha, x, beta, y, trans ? KC_SPMV_T : KC_SPMV_N);
+      else CsrApply(ctx, trans ? A.csr_t : A.csr, alpha, x, beta, y, trans ? KC_SPMV_T : KC_SPMV_N);
       break;
+    }
     case MK_DIAGONAL:
     case MK_SCALAR: {
       if (A.n == 0) break;
@@ -418,6 +421,12 @@ int eps_map_csc(eps_ctx* ctx, int m, int n, int64_t nnz, const int32_t* colptr,
   t.val.upload(vals, nnz);
   CUDA_CHECK(cudaStreamSynchronize(ctx->c.stream));
   TransposeCsrOnDevice(&ctx->c, t, &d->csr);
+  const char* fmt = getenv("EPS_SPARSE_FORMAT");  // "csr" forces the plain CSR kernel
+  const bool want_sell = fmt ? strcmp(fmt, "csr") != 0 : true;
+  if (want_sell && (nnz >= ((int64_t)1 << 18) || (fmt && strcmp(fmt, "sell") == 0)) && m > 0 && n > 0) {
+    BuildSell(&ctx->c, d->csr, &d->sell);
+    BuildSell(&ctx->c, d->csr_t, &d->sell_t);
+  }
   if (nnz <= (int64_t)4 << 20) {
     d->h_colptr.assign(colptr, colptr + n + 1);
     d->h_rowidx.assign(rowidx, rowidx + nnz);

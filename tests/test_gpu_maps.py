@@ -62,3 +62,24 @@ def test_kronecker(ctx):
     a = LinearMapSpec.Dense(rng.standard_normal((3, 4)))
     b = LinearMapSpec.Sparse(sp.random(5, 6, density=0.5, random_state=np.random.RandomState(2)))
     _check(ctx, LinearMapSpec.Kronecker(a, b), rng)
+
+
+@pytest.mark.parametrize("m,n,d", [(3000, 2000, 0.05), (70000, 30001, 0.0005), (301, 60000, 0.02),
+                                   (60001, 257, 0.02)])
+def test_sparse_sell(ctx, m, n, d, monkeypatch):
+    """Column-tiled SELL path (large matrices; forced here for small ones as well)."""
+    monkeypatch.setenv("EPS_SPARSE_FORMAT", "sell")
+    rng = np.random.default_rng(m + n)
+    a = sp.random(m, n, density=d, random_state=np.random.RandomState(5), format="csc")
+    a.data = rng.standard_normal(a.nnz)
+    _check(ctx, LinearMapSpec.Sparse(a), rng)
+
+
+def test_sparse_sell_ragged(ctx, monkeypatch):
+    monkeypatch.setenv("EPS_SPARSE_FORMAT", "sell")
+    rng = np.random.default_rng(11)
+    a = sp.lil_matrix((500, 70000))
+    a[0, :] = rng.standard_normal(70000)            # a row longer than one tile
+    a[7, 69999] = 3.0
+    a[100:400, 25600] = rng.standard_normal((300, 1))  # first column of the second tile
+    _check(ctx, LinearMapSpec.Sparse(a.tocsc()), rng)
