@@ -132,3 +132,417 @@ def newton_logistic(v: np.ndarray, lam: np.ndarray) -> np.ndarray:
         if x_res < eps:                                         # :81-83
             break
     return x
+
+
+# ---------------------------------------------------------------------------
+# 1-D total variation (C restatement in oracle/tv1d_dp.c; pure Python for small n)
+# ---------------------------------------------------------------------------
+
+_LIB_PATH = os.path.join(HERE, "_build", "liboracle.so")
+_lib = None
+
+
+def build_c(force: bool = False) -> str:
+    """gcc the C part of the oracle into oracle/_build/liboracle.so."""
+    src = os.path.join(HERE, "tv1d_dp.c")
+    if force or not os.path.exists(_LIB_PATH) or os.path.getmtime(_LIB_PATH) < os.path.getmtime(src):
+        os.makedirs(os.path.dirname(_LIB_PATH), exist_ok=True)
+        subprocess.run(["gcc", "-O2", "-fPIC", "-shared", "-ffp-contract=off", "-o", _LIB_PATH, src],
+                       check=True)
+    return _LIB_PATH
+
+
+def _c_lib():
+    global _lib
+    if _lib is None:
+        try:
+            lib = ctypes.CDLL(build_c())
+            lib.oracle_tv1d.restype = ctypes.c_int
+            lib.oracle_tv1d.argtypes = [ctypes.c_int, ctypes.c_void_p, ctypes.c_double, ctypes.c_void_p]
+            _lib = lib
+        except Exception:
+            _lib = False
+    return _lib or None
+
+
+def tv1d_py(y: np.ndarray, lam: float) -> np.ndarray:
+    """Same dynamic program as oracle/tv1d_dp.c in plain Python (small n only)."""
+    n = y.size
+    if n <= 1 or lam == 0:
+        return y.astype(np.float64).copy()
+    pos, da, db = [0.0] * (2 * n), [0.0] * (2 * n), [0.0] * (2 * n)
+    clo, chi = [0.0] * (n - 1), [0.0] * (n - 1)
+    head, tail = n - 1, n
+    clo[0], chi[0] = -lam + y[0], lam + y[0]
+    pos[head], da[head], db[head] = clo[0], 1.0, -y[0] + lam
+    pos[tail], da[tail], db[tail] = chi[0], -1.0, y[0] + lam
+    al, bl, ar, br = 1.0, -y[1] - lam, -1.0, y[1] - lam
+    for k in range(1, n - 1):
+        a_lo, b_lo, lo = al, bl, head
+        while lo <= tail:
+            if a_lo * pos[lo] + b_lo > -lam:
+                break
+            a_lo += da[lo]; b_lo += db[lo]; lo += 1
+        a_hi, b_hi, hi = ar, br, tail
+        while hi >= lo:
+            if -a_hi * pos[hi] - b_hi < lam:
+                break
+            a_hi += da[hi]; b_hi += db[hi]; hi -= 1
+        clo[k] = (-lam - b_lo) / a_lo
+        head = lo - 1
+        pos[head] = clo[k]
+        chi[k] = (lam + b_hi) / (-a_hi)
+        tail = hi + 1
+        pos[tail] = chi[k]
+        da[head], db[head] = a_lo, b_lo + lam
+        da[tail], db[tail] = a_hi, b_hi + lam
+        al, bl, ar, br = 1.0, -y[k + 1] - lam, -1.0, y[k + 1] - lam
+    a_lo, b_lo, lo = al, bl, head
+    while lo <= tail:
+        if a_lo * pos[lo] + b_lo > 0:
+            break
+        a_lo += da[lo]; b_lo += db[lo]; lo += 1
+    out = np.empty(n)
+    out[n - 1] = -b_lo / a_lo
+    for k in range(n - 2, -1, -1):
+        nxt = out[k + 1]
+        out[k] = chi[k] if nxt > chi[k] else (clo[k] if nxt < clo[k] else nxt)
+    return out
+
+
+def tv1d(y: np.ndarray, lam: float) -> np.ndarray:
+    """TotalVariation1DProx::ApplyVector, total_variation_1d.cc:12-24."""
+    y = np.ascontiguousarray(y, dtype=np.float64)
+    lib = _c_lib()
+    if lib is None:
+        return tv1d_py(y, float(lam))
+    out = np.empty_like(y)
+    rc = lib.oracle_tv1d(int(y.size), y.ctypes.data, float(lam), out.ctypes.data)
+    assert rc == 0
+    return out
+
+
+# ---------------------------------------------------------------------------
+# flattening (what affine::BuildAffineOperator produces, affine.cc:22-129)
+# ---------------------------------------------------------------------------
+
+def _term_matrix(t, rows: int):
+    """The sparse matrix of one term's linear map (identity when map is None)."""
+    if t.map is None:
+        return sp.identity(rows, format="csr")
+    return sp.csr_matrix(t.map.to_scipy())
+
+
+def _affine_blocks(aff, var_cols: Dict[str, slice], ncols: int):
+    """(matrix over the given column layout, constant vector) of one affine expression."""
+    A = sp.csr_matrix((aff.rows, ncols))
+    b = np.zeros(aff.rows)
+    for t in aff.terms:
+        if hasattr(t.operand, "var_id"):
+            vid = t.operand.var_id
+            if vid not in var_cols:
+                continue
+            sl = var_cols[vid]
+            M = _term_matrix(t, aff.rows)
+            E = sp.csr_matrix((np.ones(sl.stop - sl.start), (np.arange(sl.stop - sl.start),
+                                                             np.arange(sl.start, sl.stop))),
+                              shape=(sl.stop - sl.start, ncols))
+            A = A + M @ E
+        else:
+            c = np.asarray(t.operand, dtype=np.float64).ravel()
+            b += c if t.map is None else np.asarray(t.map.to_scipy() @ c).ravel()
+    return sp.csr_matrix(A), b
+
+
+def _diag_if_diagonal(M) -> Optional[np.ndarray]:
+    M = sp.coo_matrix(M)
+    if np.any(M.row != M.col):
+        off = M.data[M.row != M.col]
+        if np.any(off != 0):
+            return None
+    return np.asarray(sp.csr_matrix(M).diagonal()).ravel()
+
+
+# ---------------------------------------------------------------------------
+# operators
+# ---------------------------------------------------------------------------
+
+class _KktProx:
+    """SumSquareProx (sum_square.cc:10-40) and AffineProx (affine.cc:19-49).
+
+    Both assemble a symmetric block KKT matrix and eliminate it with BlockCholesky
+    (block_cholesky.cc:119-137); the variables' part of chol_.Solve(b_ + v) is
+        x = (2a H'H + A'A)^-1 (A'v - 2a H'g - c)
+    (a = ProxFunction.alpha, entering as sqrt(2a) scaling of H and g, sum_square.cc:16,23,27;
+    a = 0 for AFFINE / CONSTANT whose c = alpha * (1 x n map)', affine.cc:8-17,26-28).
+    The elimination order NextKey picks only decides WHICH Schur complement is inverted
+    (rows(H)^2 when rows(H) < n: the Woodbury side; else n^2) -- restated here by the same
+    size test, with a dense Cholesky of that complement.
+    """
+
+    def __init__(self, f, H, g, A):
+        self.A = sp.csr_matrix(A)
+        n = A.shape[1]
+        a2 = 2.0 * f.alpha if f.type == "SUM_SQUARE" else 0.0
+        self.c0 = np.zeros(n)
+        if f.type == "SUM_SQUARE":
+            self.c0 = -a2 * np.asarray(H.T @ g).ravel()
+        elif f.type == "AFFINE":
+            assert H.shape[0] == 1
+            self.c0 = -f.alpha * np.asarray(H.todense()).ravel()
+        AtA = (self.A.T @ self.A).tocsc()
+        d = _diag_if_diagonal(AtA)
+        rows_h = H.shape[0] if a2 != 0 else 0
+        self.woodbury = bool(a2 != 0 and d is not None and np.all(d > 0) and 0 < rows_h < n)
+        if self.woodbury:
+            # (D + 2a H'H)^-1 = D^-1 - D^-1 H' (I/(2a) + H D^-1 H')^-1 H D^-1
+            self.dinv = 1.0 / d
+            self.H = sp.csr_matrix(H)
+            Hd = self.H.toarray() if rows_h * n <= 5e7 else None
+            if Hd is not None:
+                S = (Hd * self.dinv) @ Hd.T
+            else:
+                S = (self.H @ sp.diags(self.dinv) @ self.H.T).toarray()
+            S[np.diag_indices_from(S)] += 1.0 / a2
+            self.chol = sla.cho_factor(S, lower=True)
+        else:
+            Msp = AtA + (a2 * (sp.csr_matrix(H).T @ sp.csr_matrix(H)) if a2 != 0 else 0 * AtA)
+            self.mdiag = _diag_if_diagonal(Msp)      # every block scalar/diagonal: elementwise
+            if self.mdiag is None:
+                self.chol = sla.cho_factor(Msp.toarray(), lower=True)
+
+    def apply(self, v: np.ndarray) -> np.ndarray:
+        rhs = np.asarray(self.A.T @ v).ravel() + self.c0
+        if not self.woodbury:
+            return rhs / self.mdiag if self.mdiag is not None else sla.cho_solve(self.chol, rhs)
+        t = self.dinv * rhs
+        z = sla.cho_solve(self.chol, np.asarray(self.H @ t).ravel())
+        return t - self.dinv * np.asarray(self.H.T @ z).ravel()
+
+
+class _VectorProx:
+    """VectorProx::{Init,Apply} (vector_prox.cc:51-183): reduce
+    argmin_x f(Hx + g) + 1/2||Ax - v||^2 to a plain prox when H'H and H A'A H' are scalar
+    (InitScalar :51-70) or diagonal (InitDiagonal :72-116)."""
+
+    def __init__(self, f, H, g, A):
+        self.f = f
+        H, A = sp.csr_matrix(H), sp.csr_matrix(A)
+        n = H.shape[0]
+        beta = _diag_if_diagonal(H.T @ H)
+        gamma = _diag_if_diagonal(H @ A.T @ A @ H.T)
+        assert beta is not None and gamma is not None, "Affine transformation is not scalar or diagonal"
+        scalar = np.all(beta == beta[0]) and np.all(gamma == gamma[0]) and gamma[0] != 0
+        self.g = g
+        self.D = None
+        if scalar:                                                     # :59-67
+            b0, g0 = float(beta[0]), float(gamma[0])
+            self.B = ((b0 / g0) * H) @ A.T
+            self.C = (1 / b0) * H.T
+            self.lam = np.full(n, f.alpha * b0 * b0 / g0)
+            assert self.lam[0] >= 0
+        else:                                                          # :84-115
+            assert H.shape[0] == H.shape[1], "diagonal reduction restated for square H only"
+            beta, gamma = beta.copy(), gamma.copy()
+            lam, delta = np.zeros(n), np.zeros(n)
+            for i in range(n):
+                if gamma[i]:
+                    lam[i] = f.alpha * beta[i] * beta[i] / gamma[i]
+                else:
+                    beta[i], gamma[i], delta[i] = 1.0, 1.0, 1.0
+            self.B = H @ sp.diags(beta / gamma) @ A.T
+            self.C = sp.diags(1.0 / beta) @ H.T
+            AtA = _diag_if_diagonal(A.T @ A)
+            assert AtA is not None
+            inv = np.where(AtA != 0, 1.0 / np.where(AtA != 0, AtA, 1.0), 0.0)   # zero-safe Inverse
+            self.D = sp.diags(inv) @ sp.diags(delta) @ A.T
+            self.lam = lam
+        self.scalar = scalar
+
+    def _apply_vector(self, v: np.ndarray) -> np.ndarray:
+        t = self.f.type
+        if t in ZONE_TYPES:
+            al, be, M = zone_params(self.f, v.size)
+            return scaled_zone(v, self.lam, al, be, M)
+        if t == "NON_NEGATIVE":
+            return np.maximum(v, 0.0)                                   # non_negative.cc:5-9
+        if t == "NORM_2":
+            assert self.scalar
+            return norm2_block(v, float(self.lam[0]))
+        if t == "SUM_LOGISTIC":
+            return newton_logistic(v, self.lam)
+        if t == "TOTAL_VARIATION_1D":
+            assert self.scalar
+            return tv1d(v, float(self.lam[0]))
+        raise ValueError("no restatement for prox type %s" % t)
+
+    def apply(self, v: np.ndarray) -> np.ndarray:
+        vin = np.asarray(self.B @ v).ravel() + self.g                   # PreProcessInput :139-141
+        x = self._apply_vector(vin)
+        out = np.asarray(self.C @ (x - self.g)).ravel()                 # PostProcessOutput :143-145
+        if self.D is not None:
+            out = out + np.asarray(self.D @ v).ravel()
+        return out
+
+
+def _make_operator(f, H, g, A):
+    if f.type in KKT_TYPES:
+        return _KktProx(f, H, g, A)
+    return _VectorProx(f, H, g, A)
+
+
+# ---------------------------------------------------------------------------
+# ProxADMMSolver
+# ---------------------------------------------------------------------------
+
+class ProxADMM:
+    """ProxADMMSolver (prox_admm.cc).  `problem` is an epsilon_b200.problem.ProxAffineProblem
+    (the flattened prox-affine form both sides of the boundary share)."""
+
+    def __init__(self, problem, params: Optional[dict] = None):
+        self.problem = problem
+        self.params = dict(DEFAULT_PARAMS)
+        self.params.update(params or {})
+        assert self.params["rho"] == 1.0, "CHECK_EQ(1, rho), prox_admm.cc:50"
+        self._init()
+
+    # InitConstraints (:25-43) + InitProxOperators (:45-94) + InitVariables (:96-108)
+    def _init(self):
+        p = self.problem
+        sizes = p.variables()
+        self.N = len(p.prox)
+        self.prox_vars: List[List[str]] = [p.prox_variables(i) for i in range(self.N)]
+        owner = {}
+        for i, vs in enumerate(self.prox_vars):
+            for v in vs:
+                assert v not in owner, "variable %s in two prox functions" % v
+                owner[v] = i
+        coff = np.concatenate([[0], np.cumsum([c.rows for c in p.constraints])]).astype(int)
+        self.m = int(coff[-1])                                         # A_.m()
+        in_constraint = set()
+        for c in p.constraints:
+            for t in c.terms:
+                if hasattr(t.operand, "var_id"):
+                    in_constraint.add(t.operand.var_id)
+        self.n = int(sum(sizes[v] for v in in_constraint))             # A_.n()
+        self.b = np.zeros(self.m)
+        self.Ai, self.ops, self.cols = [], [], []
+        for i, f in enumerate(p.prox):
+            cols, off = {}, 0
+            for v in self.prox_vars[i]:
+                cols[v] = slice(off, off + sizes[v])
+                off += sizes[v]
+            self.cols.append(cols)
+            # H, g: the arguments stacked (keys arg:0, arg:1, ...)
+            Hs, gs = [], []
+            for a in f.args:
+                Ha, ga = _affine_blocks(a, cols, off)
+                Hs.append(Ha)
+                gs.append(ga)
+            H = sp.vstack(Hs, format="csr") if Hs else sp.csr_matrix((0, off))
+            g = np.concatenate(gs) if gs else np.zeros(0)
+            # A_i: columns of A_ that belong to f_i's variables, times sqrt(rho) (:68-79)
+            in_c = {v: s for v, s in cols.items() if v in in_constraint}
+            rows = []
+            for c in p.constraints:
+                Ac, _ = _affine_blocks(c, in_c, off)
+                rows.append(Ac)
+            A = sp.vstack(rows, format="csr") if rows else sp.csr_matrix((0, off))
+            self.Ai.append(A)
+            self.ops.append(_make_operator(f, H, g, A))
+        for k, c in enumerate(p.constraints):
+            _, bc = _affine_blocks(c, {}, 0)
+            self.b[coff[k]:coff[k + 1]] = bc
+        self.reset()
+
+    def reset(self):
+        self.u = np.zeros(self.m)
+        self.x = [np.zeros(A.shape[1]) for A in self.Ai]
+        self.y = [np.zeros(self.m) for _ in range(self.N)]             # empty BlockVector = 0
+        self.y_prev = [np.zeros(self.m) for _ in range(self.N)]
+        self.iter = 0
+        self.status = {"state": 0, "num_iterations": 0}
+
+    def iteration(self):
+        """One pass of prox_admm.cc:135-147."""
+        self.y_prev = [yi.copy() for yi in self.y]
+        self.u = self.u - self.b
+        for i in range(self.N):
+            self.u = self.u - self.y[i]
+        for i in range(self.N):
+            self.u = self.u + self.y[i]
+            self.x[i] = self.ops[i].apply(self.u)
+            self.y[i] = np.asarray(self.Ai[i] @ self.x[i]).ravel()
+            self.u = self.u - self.y[i]
+
+    def compute_residuals(self) -> dict:
+        """prox_admm.cc:178-217."""
+        abs_tol, rel_tol, rho = self.params["abs_tol"], self.params["rel_tol"], self.params["rho"]
+        ax_b = self.b.copy()
+        max_ax = float(np.linalg.norm(self.b))
+        for i in range(self.N):
+            ai_xi = np.asarray(self.Ai[i] @ self.x[i]).ravel()
+            max_ax = max(max_ax, float(np.linalg.norm(ai_xi)))
+            ax_b += ai_xi
+        s2 = 0.0
+        diff = np.zeros(self.m)
+        for i in range(self.N - 2, -1, -1):
+            diff = diff + (self.y[i + 1] - self.y_prev[i + 1])
+            si = float(np.linalg.norm(self.Ai[i].T @ diff))
+            s2 += si * si
+        atu2 = sum(float(np.sum(np.asarray(A.T @ self.u) ** 2)) for A in self.Ai)
+        st = {
+            "r_norm": float(np.linalg.norm(ax_b)),
+            "s_norm": rho * float(np.sqrt(s2)),
+            "epsilon_primal": abs_tol * np.sqrt(self.m) + rel_tol * max_ax,
+            "epsilon_dual": abs_tol * np.sqrt(self.n) + rel_tol * rho * float(np.sqrt(atu2)),
+        }
+        ok = st["r_norm"] <= st["epsilon_primal"] and st["s_norm"] <= st["epsilon_dual"]
+        st["state"] = STATE_OPTIMAL if ok else STATE_RUNNING
+        st["num_iterations"] = self.iter
+        self.status = st
+        return st
+
+    def solution(self) -> Dict[str, np.ndarray]:
+        """GetSolution, prox_admm.cc:171-176."""
+        out = {}
+        for i in range(self.N):
+            for v, sl in self.cols[i].items():
+                out[v] = self.x[i][sl].copy()
+        return out
+
+    def solve(self) -> dict:
+        """ProxADMMSolver::Solve, prox_admm.cc:131-169.  Returns status, per-epoch trace, x."""
+        self.reset()
+        trace = []
+        max_it, epoch = int(self.params["max_iterations"]), int(self.params["epoch_iterations"])
+        self.iter = 0
+        while self.iter < max_it:
+            self.iteration()
+            if self.iter % epoch == 0:
+                trace.append(dict(self.compute_residuals()))
+                if self.status["state"] == STATE_OPTIMAL:
+                    break
+            self.iter += 1
+        if self.iter == max_it:
+            self.compute_residuals()
+            self.status["state"] = STATE_MAX_ITERATIONS
+            trace.append(dict(self.status))
+        return {"status": dict(self.status), "trace": trace, "x": self.solution(),
+                "m": self.m, "n": self.n, "N": self.N}
+
+
+def eval_prox(f, lam: float, v: Dict[str, np.ndarray]) -> Dict[str, np.ndarray]:
+    """EvalProx, python/epopt/solvemodule.cc:189-242: A = (1/sqrt(lam)) I per variable,
+    v <- A v, one Apply."""
+    from epsilon_b200.problem import Affine, LinearMapSpec, ProxAffineProblem, Term, Variable
+    prob = ProxAffineProblem([f], [])
+    sizes = prob.variables()
+    a = 1.0 / np.sqrt(lam)
+    order = sorted(sizes)
+    cons = [Affine(sizes[k], [Term(Variable(k, sizes[k]), LinearMapSpec.Scalar(a, sizes[k]))])
+            for k in order]
+    s = ProxADMM(ProxAffineProblem([f], cons))
+    u = np.concatenate([a * np.asarray(v[k], dtype=np.float64).ravel() for k in order])
+    x = s.ops[0].apply(u)
+    return {k: x[sl].copy() for k, sl in s.cols[0].items()}

@@ -1,0 +1,168 @@
+#!/usr/bin/env python
+"""Generate tests/golden/*.npz by running the UNMODIFIED reference solver.
+
+Run in the build container (needs oracle/_ref/epsilon_ref, i.e. /root/reference + `make -C
+oracle`):   python tests/golden/make_golden.py
+
+Each fixture records, for one seeded problem of epsilon_b200.problems (the same bytes go to
+the reference and, in the tests, to the numpy oracle and the CUDA path):
+  * a SHA-256 over the generated input buffers (guards against generator drift),
+  * the reference's per-epoch residual trace, final status, m/n/N and the solution x,
+and for single operators (the harness' `prox` mode = EvalProx, solvemodule.cc:189-242) the
+input v, lambda and the reference's output.
+The reference holds no golden vectors of its own for this path; these
+outputs of the reference itself are what pins the oracle.
+"""
+from __future__ import annotations
+
+import hashlib
+import json
+import os
+import sys
+
+import numpy as np
+import scipy.sparse as sp
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+
+from epsilon_b200 import problems  # noqa: E402
+from epsilon_b200.problem import Affine, LinearMapSpec, ProxFunction, Term, Variable  # noqa: E402
+
+# name -> (generator, args, kwargs, solver params)
+SOLVE_CASES = {
+    "lasso_dense_100x500": ("lasso", (100, 500), {}, {}),
+    "lasso_dense_tall_600x150": ("lasso", (600, 150), {"seed": 2}, {}),
+    "lasso_dense_60x200": ("lasso", (60, 200), {"seed": 1}, {}),
+    "lasso_config1_1000x5000": ("lasso", (1000, 5000), {}, {}),
+    "lasso_sparse_4000x400": ("lasso", (4000, 400), {"density": 0.02, "seed": 3}, {}),
+    "lasso_sparse_30000x3000": ("lasso", (30000, 3000), {"density": 0.001, "seed": 8}, {}),
+    "logreg_l1_2000x200": ("logreg_l1", (2000, 200), {"density": 0.05, "seed": 4}, {"max_iterations": 200}),
+    "logreg_l1_dense_500x80": ("logreg_l1", (500, 80), {"seed": 9}, {"max_iterations": 200}),
+    "hinge_l2_1500x100": ("hinge_l2", (1500, 100), {"seed": 5}, {"max_iterations": 300}),
+    "hinge_l2_sparse_5000x300": ("hinge_l2", (5000, 300), {"density": 0.02, "seed": 10}, {"max_iterations": 300}),
+    "group_lasso_400x10x12": ("group_lasso", (400, 10, 12), {"seed": 6}, {"max_iterations": 300}),
+    "tv_1d_5000": ("tv_1d", (5000,), {"seed": 7}, {"max_iterations": 300}),
+    "tv_1d_200000": ("tv_1d", (200000,), {"seed": 11}, {"max_iterations": 100}),
+    # stop by max_iterations (not a multiple of the epoch): MAX_ITERATIONS_REACHED path
+    "lasso_maxiter_17": ("lasso", (80, 120), {"seed": 12}, {"max_iterations": 17}),
+}
+
+
+def problem_digest(prob) -> str:
+    """SHA-256 over every constant and matrix buffer of the problem, in traversal order."""
+    h = hashlib.sha256()
+
+    def feed_map(m):
+        if m is None:
+            return
+        if m.dense is not None:
+            h.update(np.asfortranarray(m.dense).tobytes(order="F"))
+        if m.sparse is not None:
+            a = sp.csc_matrix(m.sparse)
+            h.update(a.indptr.astype(np.int32).tobytes())
+            h.update(a.indices.astype(np.int32).tobytes())
+            h.update(a.data.astype(np.float64).tobytes())
+        if m.diag is not None:
+            h.update(np.asarray(m.diag, dtype=np.float64).tobytes())
+        h.update(np.float64(m.scalar).tobytes())
+        for k in (m.kron or ()):
+            feed_map(k)
+
+    for aff in [a for f in prob.prox for a in f.args] + list(prob.constraints):
+        for t in aff.terms:
+            feed_map(t.map)
+            if not isinstance(t.operand, Variable):
+                h.update(np.asarray(t.operand, dtype=np.float64).tobytes())
+    for f in prob.prox:
+        h.update(np.float64(f.alpha).tobytes())
+    return h.hexdigest()
+
+
+def make_problem(name):
+    gen, args, kw, params = SOLVE_CASES[name]
+    prob, info = getattr(problems, gen)(*args, **kw)
+    return prob, info, params
+
+
+TRACE_KEYS = ("state", "num_iterations", "r_norm", "s_norm", "epsilon_primal", "epsilon_dual")
+
+
+# ---- single operators ------------------------------------------------------------------
+def prox_cases():
+    """name -> (ProxFunction, lambda, {var: v})."""
+    rng = np.random.default_rng(1234)
+    out = {}
+
+    def simple(ptype, n, alpha=1.0, scale=1.0, **kw):
+        x = Variable("x", n)
+        args = [Affine(n, [Term(x) if scale == 1.0 else Term(x, LinearMapSpec.Scalar(scale, n))])]
+        return ProxFunction(ptype, args=args, alpha=alpha, **kw)
+
+    n = 2000
+    out["norm_1"] = (simple("NORM_1", n, alpha=0.7), 1.3, {"x": rng.standard_normal(n) * 2})
+    out["norm_1_scaled_arg"] = (simple("NORM_1", n, alpha=0.4, scale=-2.5), 0.6, {"x": rng.standard_normal(n)})
+    out["sum_hinge"] = (simple("SUM_HINGE", n), 0.8, {"x": rng.standard_normal(n) * 2})
+    out["sum_deadzone"] = (simple("SUM_DEADZONE", n, alpha=1.5, zone_m=0.5), 0.9, {"x": rng.standard_normal(n) * 2})
+    out["sum_quantile_vec"] = (simple("SUM_QUANTILE", n, quantile_alpha=rng.random(n),
+                                      quantile_beta=rng.random(n)), 1.1, {"x": rng.standard_normal(n) * 2})
+    out["sum_quantile_scalar"] = (simple("SUM_QUANTILE", n, quantile_alpha=np.array([0.3]),
+                                         quantile_beta=np.array([0.7])), 2.0, {"x": rng.standard_normal(n) * 2})
+    out["non_negative"] = (simple("NON_NEGATIVE", n), 1.0, {"x": rng.standard_normal(n)})
+    out["norm_2_shrink"] = (simple("NORM_2", 300, alpha=2.0), 1.5, {"x": rng.standard_normal(300)})
+    out["norm_2_zero"] = (simple("NORM_2", 50, alpha=100.0), 1.0, {"x": rng.standard_normal(50)})
+    out["sum_logistic"] = (simple("SUM_LOGISTIC", n), 1.7, {"x": rng.standard_normal(n) * 4})
+    out["sum_logistic_large_lambda"] = (simple("SUM_LOGISTIC", 500, alpha=3.0), 25.0,
+                                        {"x": rng.standard_normal(500) * 10})
+    out["tv_1d"] = (simple("TOTAL_VARIATION_1D", n, alpha=2.0), 1.5,
+                    {"x": np.repeat(rng.standard_normal(20) * 3, 100) + rng.standard_normal(n)})
+    out["tv_1d_len2"] = (simple("TOTAL_VARIATION_1D", 2, alpha=0.1), 1.0, {"x": np.array([1.0, -2.0])})
+    out["tv_1d_len1"] = (simple("TOTAL_VARIATION_1D", 1, alpha=0.1), 1.0, {"x": np.array([3.0])})
+    # SUM_SQUARE with a dense argument (least squares), wide and tall
+    for nm, (m, nn) in {"sum_square_wide": (30, 80), "sum_square_tall": (120, 40)}.items():
+        a = rng.standard_normal((m, nn))
+        b = rng.standard_normal(m)
+        x = Variable("x", nn)
+        f = ProxFunction("SUM_SQUARE", alpha=0.5, args=[Affine(m, [
+            Term(x, LinearMapSpec.Dense(a, name="A")), Term(b, LinearMapSpec.Scalar(-1.0, m), name="b")])])
+        out[nm] = (f, 0.7, {"x": rng.standard_normal(nn)})
+    return out
+
+
+def main():
+    from oracle import ref_runner
+    assert ref_runner.available(), "build oracle/_ref first: make -C oracle"
+    index = {"solve": {}, "prox": {}}
+    for name in SOLVE_CASES:
+        prob, info, params = make_problem(name)
+        r = ref_runner.run(prob, params=params, mode="trace")
+        stock = ref_runner.run(prob, params=params, mode="solve")
+        # the stepped run must end exactly where the stock Solve() ends
+        for k in TRACE_KEYS:
+            assert r["status"][k] == stock["status"][k], (name, k, r["status"], stock["status"])
+        trace = np.array([[t[k] for k in TRACE_KEYS] for t in r["trace"]], dtype=np.float64)
+        v = info["solution_var"]
+        np.savez_compressed(
+            os.path.join(HERE, name + ".npz"), trace=trace,
+            status=np.array([r["status"][k] for k in TRACE_KEYS], dtype=np.float64),
+            mnN=np.array([r["m"], r["n"], r["N"]], dtype=np.int64),
+            x=r["x"][v].astype(np.float64), objective=np.float64(info["objective"](r["x"])))
+        index["solve"][name] = {"digest": problem_digest(prob), "solution_var": v,
+                                "epochs": int(trace.shape[0]),
+                                "num_iterations": int(r["status"]["num_iterations"]),
+                                "state": int(r["status"]["state"])}
+        print(name, index["solve"][name])
+    for name, (f, lam, v) in prox_cases().items():
+        x = ref_runner.run_prox(f, lam, v)
+        np.savez_compressed(os.path.join(HERE, "prox_" + name + ".npz"), lam=np.float64(lam),
+                            **{"v_" + k: val for k, val in v.items()},
+                            **{"x_" + k: val for k, val in x.items() if k in v})
+        index["prox"][name] = {"type": f.type, "n": int(sum(val.size for val in v.values()))}
+        print("prox", name, index["prox"][name])
+    with open(os.path.join(HERE, "index.json"), "w") as fh:
+        json.dump(index, fh, indent=1, sort_keys=True)
+
+
+if __name__ == "__main__":
+    main()
