@@ -42,7 +42,7 @@ def _read_vectors(path: str) -> Dict[str, np.ndarray]:
 def run(problem, params: Optional[dict] = None, mode: str = "trace", dump_iter: int = -1,
         workdir: Optional[str] = None, timeout: float = 3600.0) -> dict:
     """mode 'solve' = stock ProxADMMSolver::Solve(); 'trace' = stepped, per-epoch residuals."""
-    from epsilon_b200.problem import write_reference_problem
+    from oracle.ref_format import write_reference_problem
     assert available(), "oracle/_ref/epsilon_ref missing: run `make -C oracle`"
     tmp = workdir or tempfile.mkdtemp(prefix="epsref_")
     try:
@@ -73,7 +73,7 @@ def run(problem, params: Optional[dict] = None, mode: str = "trace", dump_iter: 
 
 def run_prox(f, lam: float, v: Dict[str, np.ndarray], workdir: Optional[str] = None) -> Dict[str, np.ndarray]:
     """Single operator through the EvalProx statement sequence (solvemodule.cc:189-242)."""
-    from epsilon_b200.problem import write_reference_prox
+    from oracle.ref_format import write_reference_prox
     assert available(), "oracle/_ref/epsilon_ref missing: run `make -C oracle`"
     tmp = workdir or tempfile.mkdtemp(prefix="epsref_")
     try:
