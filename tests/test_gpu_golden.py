@@ -42,11 +42,35 @@ def _cases():
             yield name, mode
 
 
+_EXPECTED = {}
+
+
+def _expected(name, prob, info, params):
+    """The committed output of the reference for this case.  The fixtures hold outputs, not the
+    (up to 40 MB) inputs; should the seeded generator produce different bytes on this host
+    (numpy build differences), the pinned CPU oracle is run on the bytes at hand instead --
+    the stop decision sits on a 0.3 % margin and only means something on identical inputs."""
+    if name in _EXPECTED:
+        return _EXPECTED[name]
+    if make_golden.problem_digest(prob) == INDEX["solve"][name]["digest"]:
+        gold = dict(np.load(os.path.join(GOLDEN, name + ".npz")))
+    else:
+        import warnings
+        warnings.warn("generator drift for %s: checking against the CPU oracle" % name)
+        o = onp.ProxADMM(prob, params).solve()
+        gold = {"trace": np.array([[t[k] for k in TRACE_KEYS] for t in o["trace"]], dtype=np.float64),
+                "status": np.array([o["status"][k] for k in TRACE_KEYS], dtype=np.float64),
+                "mnN": np.array([o["m"], o["n"], o["N"]]),
+                "x": o["x"][INDEX["solve"][name]["solution_var"]],
+                "objective": np.float64(info["objective"](o["x"]))}
+    _EXPECTED[name] = gold
+    return gold
+
+
 @pytest.mark.parametrize("name,mode", list(_cases()))
 def test_admm_matches_reference_golden(ctx, name, mode):
     prob, info, params = make_golden.make_problem(name)
-    assert make_golden.problem_digest(prob) == INDEX["solve"][name]["digest"]
-    gold = np.load(os.path.join(GOLDEN, name + ".npz"))
+    gold = _expected(name, prob, info, params)
     p = dict(params, kkt_mode=mode)
     with ProxADMMSolver(prob, p, ctx=ctx) as s:
         x = s.solve()
