@@ -250,7 +250,7 @@ def main_ours(args):
     ms = s.iterate(args.steps)
     clocks = sampler.stop() if rank == 0 else None
     launches = ctx.kernel_launches - launches0
-    cg_iters = s.status.cg_iterations
+    cg_iters = s.residuals()["cg_iterations"]   # inner CG iterations of the timed iterate() call
     ms = max_over_ranks(ms)
     value = args.steps / (ms / 1e3)
 
@@ -279,11 +279,27 @@ def main_ours(args):
     spmv_launches = sum(prof[k]["launches"] for k in ("spmv_n", "spmv_t") if k in prof)
     achieved = spmv_bytes / (spmv_ms / 1e3) / 1e9 if spmv_ms > 0 else None
     total_prof_ms = sum(v["ms"] for v in prof.values())
+    traffic = None  # dram__bytes_read.sum + dram__bytes_write.sum per launch, ncu --set full (1-GPU shape)
+    try:
+        if world == 1 and args.m == 1_000_000 and args.n == 100_000:
+            import csv
+            rd = wr = 0.0
+            for row in csv.reader(open(os.path.join(ROOT, "profiles", "r01_ncu_full_SellSpmvKernel.csv"))):
+                if row and row[0] in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+                    scale = {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0}[row[1]]
+                    v = 0.5 * (float(row[2]) + float(row[3])) * scale   # mean of the A' and A launches
+                    rd, wr = (v, wr) if "read" in row[0] else (rd, v)
+            traffic = rd + wr if rd else None
+    except Exception:
+        traffic = None
+    sell = os.environ.get("EPS_SPARSE_FORMAT", "sell") != "csr"
     roofline = {
-        "bound": "hbm", "kernel": "CsrSpmvKernel (A and A' passes of the CG matvec)",
+        "bound": "hbm",
+        "kernel": ("SellSpmvKernel" if sell else "CsrSpmvKernel") + " (A and A' passes of the CG matvec)",
         "achieved": achieved, "peak": peak,
         "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "6650 GB/s (of fallback)",
-        "unit": "GB/s", "frac": achieved / peak if achieved else None, "traffic": None,
+        "unit": "GB/s", "frac": achieved / peak if achieved else None, "traffic": traffic,
+        "traffic_source": "profiles/r01_ncu_full_SellSpmvKernel.csv (ncu --set full, mean of one A and one A' launch)" if traffic else None,
         "launches": spmv_launches, "ms_per_launch": spmv_ms / max(spmv_launches, 1),
         "algorithmic_bytes_per_launch": spmv_bytes / max(spmv_launches, 1),
         "share_of_step": spmv_ms / total_prof_ms if total_prof_ms else None,
