@@ -80,6 +80,40 @@ __device__ __forceinline__ void GridSumFinish(double (&v)[NV], double* smem, dou
   }
 }
 
+// Like GridSumFinish but leaves the totals in v[] of thread 0 of the LAST CTA to arrive and
+// returns true there (false everywhere else), so that the caller can append scalar work.
+template <int NV>
+__device__ __forceinline__ bool GridSumLast(double (&v)[NV], double* smem, double* partials,
+                                            unsigned* counter) {
+  BlockSum<NV>(v, smem);
+  __shared__ bool is_last_;
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int k = 0; k < NV; k++) partials[k * gridDim.x + blockIdx.x] = v[k];
+    __threadfence();
+    unsigned prev = atomicAdd(counter, 1u);
+    is_last_ = (prev == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!is_last_) return false;
+  __threadfence();
+  double acc[NV];
+#pragma unroll
+  for (int k = 0; k < NV; k++) {
+    double t = 0;
+    for (int i = threadIdx.x; i < gridDim.x; i += blockDim.x) t += __ldcg(&partials[k * gridDim.x + i]);
+    acc[k] = t;
+  }
+  BlockSum<NV>(acc, smem);
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int k = 0; k < NV; k++) v[k] = acc[k];
+    *counter = 0;
+    return true;
+  }
+  return false;
+}
+
 // Streaming 128-bit loads that do not pollute L1 (data read exactly once).
 __device__ __forceinline__ double2 LdStream2(const double* p) {
   double2 r;

@@ -194,7 +194,14 @@ void CsrApply(Ctx* ctx, const Csr& A, double alpha, const double* x, double beta
 void BuildCsrFromHost(Ctx* ctx, int m, int n, int64_t nnz, const int64_t* rowptr,
                       const int32_t* col, const double* val, Csr* out);
 void BuildSell(Ctx* ctx, const Csr& A, Sell* S);
-void SellApply(Ctx* ctx, const Sell& S, double alpha, const double* x, double beta, double* y, int kclass);
+// Optional fusions of a sparse apply (used by the CG loop of kkt.cu).
+struct SpmvExtra {
+  const int* skip = nullptr;      // device flag: when non-zero the kernels return at once
+  const double* ep_d = nullptr;   // y += ep_d .* ep_p after the alpha/beta update
+  const double* ep_p = nullptr;
+};
+void SellApply(Ctx* ctx, const Sell& S, double alpha, const double* x, double beta, double* y, int kclass,
+               const SpmvExtra* ex = nullptr);
 void DenseGemv(Ctx* ctx, const double* A, int lda, int m, int n, bool trans, double alpha,
                const double* x, double beta, double* y, int tri = 0);
 

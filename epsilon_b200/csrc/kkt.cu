@@ -1,6 +1,8 @@
 // KKT prox solve object: DIAGONAL / WOODBURY / GRAM / CG.  See kkt.h.
 #include <algorithm>
 
+#include <cooperative_groups.h>
+
 #include "device.cuh"
 #include "kkt.h"
 #include "prox.cuh"
@@ -14,51 +16,99 @@ namespace {
 constexpr int kBlock = 256;
 constexpr int kUnroll = 4;
 
-// r = rhs - w; p = r; out = r.r
+constexpr int kCgRing = 64;
+constexpr int kTailBlock = 512;
+
+// Sum of `count` per-CTA partials in a fixed order; identical in every CTA.
+__device__ __forceinline__ double SumPartials(const double* partials, int count, double* smem) {
+  double v[1] = {0.0};
+  for (int i = threadIdx.x; i < count; i += blockDim.x) v[0] += __ldcg(&partials[i]);
+  BlockSum<1>(v, smem);
+  __shared__ double total_;
+  __syncthreads();
+  if (threadIdx.x == 0) total_ = v[0];
+  __syncthreads();
+  return total_;
+}
+
+// r = rhs - w; p = r; rr = r.r; thresh = tol*sqrt(rhs.rhs); publishes result `seq`.
+// scal: [0] rr  [1] thresh
 __global__ void __launch_bounds__(kBlock)
-CgInitKernel(int64_t n, const double* __restrict__ rhs, const double* __restrict__ w,
-             double* __restrict__ r, double* __restrict__ p, double* partials, unsigned* counter,
-             double* out) {
-  __shared__ double smem[32];
-  double acc[1] = {0.0};
+CgStartKernel(int64_t n, const double* __restrict__ rhs, const double* __restrict__ w,
+              double* __restrict__ r, double* __restrict__ p, double tol, double* scal,
+              double* partials, unsigned* counter, int* done, KktSolver::CgResult* ring,
+              long long seq) {
+  __shared__ double smem[64];
+  double acc[2] = {0.0, 0.0};
   const int64_t stride = (int64_t)gridDim.x * kBlock;
   for (int64_t i = (int64_t)blockIdx.x * kBlock + threadIdx.x; i < n; i += stride) {
-    const double t = rhs[i] - w[i];
+    const double b = rhs[i];
+    const double t = b - w[i];
     r[i] = t;
     p[i] = t;
     acc[0] += t * t;
+    acc[1] += b * b;
   }
-  GridSumFinish<1>(acc, smem, partials, counter, out, 0);
+  if (GridSumLast<2>(acc, smem, partials, counter)) {
+    const double thresh = tol * sqrt(acc[1]);
+    const int conv = sqrt(acc[0]) <= thresh ? 1 : 0;
+    scal[0] = acc[0];
+    scal[1] = thresh;
+    *done = conv;
+    KktSolver::CgResult* e = &ring[seq % kCgRing];
+    e->rr = acc[0];
+    e->converged = conv;
+    __threadfence_system();
+    *reinterpret_cast<volatile long long*>(&e->seq) = seq;
+  }
 }
 
-// a = rr/pw; x += a p; r -= a w; out = r.r
-__global__ void __launch_bounds__(kBlock)
-CgUpdateXRKernel(int64_t n, const double* rr, const double* pw, const double* __restrict__ p,
-                 const double* __restrict__ w, double* __restrict__ x, double* __restrict__ r,
-                 double* partials, unsigned* counter, double* out) {
-  __shared__ double smem[32];
-  const double denom = *pw;
-  const double a = denom != 0.0 ? *rr / denom : 0.0;
-  double acc[1] = {0.0};
-  const int64_t stride = (int64_t)gridDim.x * kBlock;
-  for (int64_t i = (int64_t)blockIdx.x * kBlock + threadIdx.x; i < n; i += stride) {
+// One CG update after w = M p, as one cooperative kernel:
+//   a = rr / p.w;  x += a p;  r -= a w;  rr' = r.r;  p = r + (rr'/rr) p
+// and the publication of (rr', converged) for the host.  No-op once `done` is raised.
+__global__ void __launch_bounds__(kTailBlock)
+CgTailKernel(int64_t n, const double* __restrict__ w, double* __restrict__ p, double* __restrict__ x,
+             double* __restrict__ r, double* scal, double* partials, int* done,
+             KktSolver::CgResult* ring, long long seq) {
+  namespace cg = cooperative_groups;
+  __shared__ double smem[64];
+  if (*done) return;  // uniform: only ever written by the last phase of an earlier launch
+  cg::grid_group grid = cg::this_grid();
+  const int G = gridDim.x;
+  const int64_t stride = (int64_t)G * kTailBlock;
+  const int64_t first = (int64_t)blockIdx.x * kTailBlock + threadIdx.x;
+  const double rr = scal[0];
+  const double thresh = scal[1];
+  double v[1] = {0.0};
+  for (int64_t i = first; i < n; i += stride) v[0] += p[i] * w[i];
+  BlockSum<1>(v, smem);
+  if (threadIdx.x == 0) partials[blockIdx.x] = v[0];
+  grid.sync();
+  const double pw = SumPartials(partials, G, smem);
+  const double a = pw != 0.0 ? rr / pw : 0.0;
+  v[0] = 0.0;
+  for (int64_t i = first; i < n; i += stride) {
     x[i] += a * p[i];
     const double t = r[i] - a * w[i];
     r[i] = t;
-    acc[0] += t * t;
+    v[0] += t * t;
   }
-  GridSumFinish<1>(acc, smem, partials, counter, out, 0);
-}
-
-// b = rr_new/rr_old; p = r + b p
-__global__ void __launch_bounds__(kBlock)
-CgUpdatePKernel(int64_t n, const double* rr_new, const double* rr_old, const double* __restrict__ r,
-                double* __restrict__ p) {
-  const double d = *rr_old;
-  const double b = d != 0.0 ? *rr_new / d : 0.0;
-  const int64_t stride = (int64_t)gridDim.x * kBlock;
-  for (int64_t i = (int64_t)blockIdx.x * kBlock + threadIdx.x; i < n; i += stride)
-    p[i] = r[i] + b * p[i];
+  BlockSum<1>(v, smem);
+  if (threadIdx.x == 0) partials[G + blockIdx.x] = v[0];
+  grid.sync();
+  const double rr_new = SumPartials(partials + G, G, smem);
+  const double b = rr != 0.0 ? rr_new / rr : 0.0;
+  for (int64_t i = first; i < n; i += stride) p[i] = r[i] + b * p[i];
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    const int conv = sqrt(rr_new) <= thresh ? 1 : 0;
+    scal[0] = rr_new;
+    if (conv) *done = 1;
+    KktSolver::CgResult* e = &ring[seq % kCgRing];
+    e->rr = rr_new;
+    e->converged = conv;
+    __threadfence_system();
+    *reinterpret_cast<volatile long long*>(&e->seq) = seq;
+  }
 }
 
 __global__ void InvertKernel(int64_t n, const double* __restrict__ d, double* __restrict__ out, int* bad) {
@@ -158,6 +208,7 @@ void AddBlock(Ctx* ctx, int nb, const double* G, int64_t ldg, double* M, int64_t
 
 KktSolver::~KktSolver() {
   if (h_scal) cudaFreeHost(h_scal);
+  if (ring) cudaFreeHost(ring);
 }
 
 void KktSolver::Init(const std::vector<double>& g_host, const std::vector<double>& c_host) {
@@ -261,15 +312,48 @@ void KktSolver::Init(const std::vector<double>& g_host, const std::vector<double
     cg_r.alloc(ctx, n);
     cg_p.alloc(ctx, n);
     cg_w.alloc(ctx, n);
+    cg_done.alloc(ctx, 1);
+    cg_done.zero();
+    CUDA_CHECK(cudaHostAlloc(&ring, kCgRing * sizeof(CgResult), cudaHostAllocMapped));
+    memset(ring, 0, kCgRing * sizeof(CgResult));
+    {
+      int per_sm = 0;
+      CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, CgTailKernel, kTailBlock, 0));
+      EPS_CHECK(per_sm >= 1, "CgTailKernel does not fit an SM");
+      const int64_t want = (n + kTailBlock - 1) / kTailBlock;
+      tail_grid = (int)std::max<int64_t>(1, std::min<int64_t>(want, (int64_t)ctx->sm_count * per_sm));
+      tail_grid = std::min(tail_grid, ctx->sm_count);
+      cg_partials.alloc(ctx, 2 * (size_t)tail_grid);
+    }
+    // fused matvec: H is one SELL-packed sparse block over all of x and A'A is diagonal
+    fast_h = a_diag && alpha2 != 0.0 && H.blks.size() == 1 && H.blks[0].map->kind == MK_SPARSE &&
+             H.blks[0].row_off == 0 && H.blks[0].col_off == 0 && H.blks[0].m() == rows_h &&
+             H.blks[0].n() == n && H.blks[0].map->sell.built && H.blks[0].map->sell_t.built;
     CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
-    description = Format("kkt=CG n=%lld rows_h=%lld tol=%.1e%s", (long long)n, (long long)rows_h, cg_tol,
-                         h_sharded ? " sharded" : "");
+    description = Format("kkt=CG n=%lld rows_h=%lld tol=%.1e%s%s", (long long)n, (long long)rows_h, cg_tol,
+                         h_sharded ? " sharded" : "", fast_h ? " fused-matvec" : "");
   } else {
     throw Error(EPS_ERR_INVALID, Format("unknown kkt mode %d", mode));
   }
 }
 
-void KktSolver::MatVec(const double* p, double* w) {
+void KktSolver::MatVec(const double* p, double* w, const int* skip) {
+  if (fast_h) {
+    // w = 2a s^2 H'(H p) + d.*p with the diagonal term fused into the reduction of the second
+    // pass.  Row-sharded: every rank contributes its rows' part, rank 0 alone adds d.*p, and
+    // the all-reduce completes the sum (identical bits on every rank).
+    const Blk& b = H.blks[0];
+    const MapData& M = *b.map;
+    SpmvExtra e1, e2;
+    e1.skip = skip;
+    e2.skip = skip;
+    if (!h_sharded || ctx->rank == 0) { e2.ep_d = ddiag.p; e2.ep_p = p; }
+    SellApply(ctx, b.trans ? M.sell_t : M.sell, b.scale, p, 0.0, th1.p, b.trans ? KC_SPMV_T : KC_SPMV_N, &e1);
+    SellApply(ctx, b.trans ? M.sell : M.sell_t, alpha2 * b.scale, th1.p, 0.0, w,
+              b.trans ? KC_SPMV_N : KC_SPMV_T, &e2);
+    if (h_sharded) AllReduceSum(ctx, w, n);
+    return;
+  }
   bool have = false;
   if (alpha2 != 0.0 && !H.blks.empty()) {
     H.Apply(p, th1.p);
@@ -308,36 +392,52 @@ void KktSolver::Solve(const double* rhs, double* x) {
       DenseGemv(ctx, W.p, (int)n, (int)n, (int)n, true, 1.0, tn1.p, 0.0, x, 1);
       break;
     case EPS_KKT_CG: {
+      // Conjugate gradients, warm-started from x.  The host never waits for the iteration it
+      // has just launched: it launches iteration k, then reads the published result of
+      // iteration k-1 from the host-mapped ring, so the device always has work queued.  When
+      // that result says "converged", iteration k was already a no-op (cg_done is raised on
+      // the device by the kernel that detected convergence).
       ReduceScratch rs = GetReduceScratch(ctx);
       const int grid = std::min(1024, GridFor(n, kBlock, kUnroll, ctx->sm_count, 4));
-      double* rr0 = scal.p;       // ping-pong rr[0], rr[1]
-      double* pw = scal.p + 2;
-      double* bb = scal.p + 3;
-      VecDot(ctx, n, rhs, rhs, bb, false);
-      MatVec(x, cg_w.p);
-      CgInitKernel<<<grid, kBlock, 0, ctx->stream>>>(n, rhs, cg_w.p, cg_r.p, cg_p.p, rs.partials,
-                                                      rs.counter, rr0);
+      const long long base = cg_seq;
+      auto wait_result = [&](long long seq) -> const CgResult& {
+        volatile CgResult* e = &ring[seq % kCgRing];
+        long long spins = 0;
+        while (e->seq != seq) {
+          if ((++spins & 0xFFFFF) == 0) {  // surface device faults instead of spinning forever
+            cudaError_t q = cudaStreamQuery(ctx->stream);
+            if (q != cudaSuccess && q != cudaErrorNotReady) CUDA_CHECK(q);
+            if (q == cudaSuccess && e->seq != seq)
+              throw Error(EPS_ERR_CUDA, "CG result was never published");
+          }
+        }
+        return *const_cast<const CgResult*>(e);
+      };
+      MatVec(x, cg_w.p, nullptr);
+      CgStartKernel<<<grid, kBlock, 0, ctx->stream>>>(n, rhs, cg_w.p, cg_r.p, cg_p.p, cg_tol, scal.p,
+                                                       rs.partials, rs.counter, cg_done.p, ring, base);
       ctx->count_launch();
-      CUDA_CHECK(cudaMemcpyAsync(h_scal, scal.p, 4 * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
-      CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
-      const double bnorm = std::sqrt(h_scal[3]);
-      double rr = h_scal[0];
-      const double thresh = cg_tol * bnorm;
       int it = 0;
-      while (std::sqrt(rr) > thresh && it < cg_max_iter) {
-        const int cur = it & 1;
-        MatVec(cg_p.p, cg_w.p);
-        VecDot(ctx, n, cg_p.p, cg_w.p, pw, false);
-        CgUpdateXRKernel<<<grid, kBlock, 0, ctx->stream>>>(n, rr0 + cur, pw, cg_p.p, cg_w.p, x, cg_r.p,
-                                                            rs.partials, rs.counter, rr0 + (cur ^ 1));
-        ctx->count_launch();
-        CUDA_CHECK(cudaMemcpyAsync(h_scal, rr0 + (cur ^ 1), sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
-        CgUpdatePKernel<<<grid, kBlock, 0, ctx->stream>>>(n, rr0 + (cur ^ 1), rr0 + cur, cg_r.p, cg_p.p);
-        ctx->count_launch();
-        CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
-        rr = h_scal[0];
-        it++;
+      bool converged = false;
+      for (; it < cg_max_iter; it++) {
+        MatVec(cg_p.p, cg_w.p, cg_done.p);
+        {
+          ProfScope ps(ctx, KC_VEC, 72.0 * n);
+          int64_t nn = n;
+          const double* wp = cg_w.p;
+          double *pp = cg_p.p, *xp = x, *rp = cg_r.p, *sp = scal.p, *part = cg_partials.p;
+          int* dp = cg_done.p;
+          CgResult* rg = ring;
+          long long seq = base + it + 1;
+          void* args[] = {&nn, &wp, &pp, &xp, &rp, &sp, &part, &dp, &rg, &seq};
+          CUDA_CHECK(cudaLaunchCooperativeKernel((const void*)CgTailKernel, dim3(tail_grid),
+                                                 dim3(kTailBlock), args, 0, ctx->stream));
+          ctx->count_launch();
+        }
+        if (wait_result(base + it).converged != 0.0) { converged = true; break; }
       }
+      if (!converged) wait_result(base + it);  // it == cg_max_iter: drain the last iteration
+      cg_seq = base + cg_max_iter + 2;
       cg_iters_total += it;
       break;
     }

@@ -29,6 +29,16 @@ struct KktSolver {
   DevBuf<double> cg_r, cg_p, cg_w;
   DevBuf<double> scal;   // device scalars of the CG recurrences
   double* h_scal = nullptr;  // pinned mirror
+  // CG without a host round trip per iteration: the tail kernel of iteration k publishes
+  // (rr, converged, seq) into a host-mapped ring and raises `cg_done` on the device, which
+  // turns the speculatively launched iteration k+1 into no-ops.
+  struct CgResult { double rr; double converged; long long seq; long long pad; };
+  CgResult* ring = nullptr;      // cudaHostAlloc(mapped), kCgRing entries
+  long long cg_seq = 1;
+  DevBuf<int> cg_done;
+  DevBuf<double> cg_partials;
+  int tail_grid = 0;
+  bool fast_h = false;           // H = one SELL block, A'A diagonal: fused matvec
   double cg_tol = 1e-12;
   int cg_max_iter = 500;
   int64_t cg_iters_total = 0;
@@ -40,7 +50,7 @@ struct KktSolver {
   void Init(const std::vector<double>& g_host, const std::vector<double>& c_host);
   // x <- solution for rhs (both device, n).  x holds the warm start on entry (CG).
   void Solve(const double* rhs, double* x);
-  void MatVec(const double* p, double* w);  // w = (2a H'H + A'A) p
+  void MatVec(const double* p, double* w, const int* skip = nullptr);  // w = (2a H'H + A'A) p
 };
 
 }  // namespace eps

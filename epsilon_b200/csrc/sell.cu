@@ -115,9 +115,10 @@ SellSpmvKernel(int R, int Cn, int TW, int RR, int spi, const int32_t* __restrict
                const int64_t* __restrict__ voff, const int64_t* __restrict__ ioff,
                const double* __restrict__ val, const uint16_t* __restrict__ idx,
                const int32_t* __restrict__ rowid, const double* __restrict__ x,
-               double* __restrict__ P, int use_tma) {
+               double* __restrict__ P, int use_tma, const int* __restrict__ skip) {
   extern __shared__ __align__(128) double xs[];
   __shared__ __align__(8) unsigned long long bar;
+  if (skip && *skip) return;  // speculative launch after the CG loop converged (kkt.cu)
   const int item = blockIdx.x;
   const int t = item / RR;
   const int c0 = t * TW;
@@ -188,12 +189,16 @@ SellSpmvKernel(int R, int Cn, int TW, int RR, int spi, const int32_t* __restrict
 
 __global__ void __launch_bounds__(256)
 SellReduceKernel(int R, int T, const double* __restrict__ P, double alpha, double beta,
-                 double* __restrict__ y) {
+                 double* __restrict__ y, const int* __restrict__ skip,
+                 const double* __restrict__ ep_d, const double* __restrict__ ep_p) {
+  if (skip && *skip) return;
   const int row = blockIdx.x * 256 + threadIdx.x;
   if (row >= R) return;
   double s = 0.0;
   for (int t = 0; t < T; t++) s += P[(size_t)t * R + row];
-  y[row] = (beta == 0.0 ? 0.0 : beta * y[row]) + alpha * s;
+  double out = (beta == 0.0 ? 0.0 : beta * y[row]) + alpha * s;
+  if (ep_d) out += ep_d[row] * ep_p[row];  // fused diagonal term of the KKT operator
+  y[row] = out;
 }
 
 }  // namespace
@@ -262,7 +267,9 @@ void BuildSell(Ctx* ctx, const Csr& A, Sell* S) {
   S->built = true;
 }
 
-void SellApply(Ctx* ctx, const Sell& S, double alpha, const double* x, double beta, double* y, int kclass) {
+void SellApply(Ctx* ctx, const Sell& S, double alpha, const double* x, double beta, double* y, int kclass,
+               const SpmvExtra* ex) {
+  const int* skip = ex ? ex->skip : nullptr;
   if (S.R == 0) return;
   double* P = GrowScratch(ctx, &ctx->sell_scratch, (size_t)S.T * S.R);
   {
@@ -273,11 +280,12 @@ void SellApply(Ctx* ctx, const Sell& S, double alpha, const double* x, double be
     const int use_tma = ((reinterpret_cast<uintptr_t>(x) & 15) == 0 && last % 2 == 0) ? 1 : 0;
     SellSpmvKernel<<<S.T * S.RR, kSellThreads, (size_t)S.TW * 8 + 64, ctx->stream>>>(
         S.R, S.Cn, S.TW, S.RR, S.rows_per / 32, S.sl_len.p, S.voff.p, S.ioff.p, S.val.p, S.idx.p,
-        S.rowid.p, x, P, use_tma);
+        S.rowid.p, x, P, use_tma, skip);
     ctx->count_launch();
   }
   ProfScope ps(ctx, KC_VEC, 8.0 * S.T * S.R + 8.0 * S.R);
-  SellReduceKernel<<<(S.R + 255) / 256, 256, 0, ctx->stream>>>(S.R, S.T, P, alpha, beta, y);
+  SellReduceKernel<<<(S.R + 255) / 256, 256, 0, ctx->stream>>>(S.R, S.T, P, alpha, beta, y, skip,
+                                                                ex ? ex->ep_d : nullptr, ex ? ex->ep_p : nullptr);
   ctx->count_launch();
 }
 
