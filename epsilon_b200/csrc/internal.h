@@ -139,9 +139,9 @@ struct Csr {
 // Column-tiled SELL-32 storage (sell.cu).
 struct Sell {
   bool built = false;
-  int R = 0, Cn = 0, T = 0, TW = 0, RR = 0, rows_per = 0, n_slices = 0;
+  int R = 0, Cn = 0, T = 0, TW = 0, RR = 0, rows_per = 0, n_slices = 0, n_cta = 0;
   int64_t nnz = 0, n_val = 0, n_idx = 0;
-  DevBuf<int32_t> sl_len, rowid;
+  DevBuf<int32_t> sl_len, rowid, cta_begin;
   DevBuf<int64_t> voff, ioff;
   DevBuf<double> val;
   DevBuf<uint16_t> idx;

@@ -420,6 +420,9 @@ void KktSolver::Solve(const double* rhs, double* x) {
       int it = 0;
       bool converged = false;
       for (; it < cg_max_iter; it++) {
+        // profile mode times every launch with its own event pair: no speculation there, so
+        // that no-op launches do not enter the per-class statistics
+        if (ctx->profile && wait_result(base + it).converged != 0.0) { converged = true; break; }
         MatVec(cg_p.p, cg_w.p, cg_done.p);
         {
           ProfScope ps(ctx, KC_VEC, 72.0 * n);

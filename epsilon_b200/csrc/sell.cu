@@ -109,9 +109,13 @@ __device__ __forceinline__ uint32_t SmemAddr(const void* p) {
   return (uint32_t)__cvta_generic_to_shared(p);
 }
 
-// P[tile][row] = sum over the row's non-zeros inside the tile
+// P[tile][row] = sum over the row's non-zeros inside the tile.
+// Persistent: CTA g owns the contiguous work items [cta_begin[g], cta_begin[g+1]) -- a static
+// partition balanced by stored non-zeros at build time (deterministic, no atomics).  Items
+// are ordered tile-major, so a CTA restages its x tile only when the tile changes.
 __global__ void __launch_bounds__(kSellThreads, 1)
-SellSpmvKernel(int R, int Cn, int TW, int RR, int spi, const int32_t* __restrict__ sl_len,
+SellSpmvKernel(int R, int Cn, int TW, int RR, int spi, const int32_t* __restrict__ cta_begin,
+               const int32_t* __restrict__ sl_len,
                const int64_t* __restrict__ voff, const int64_t* __restrict__ ioff,
                const double* __restrict__ val, const uint16_t* __restrict__ idx,
                const int32_t* __restrict__ rowid, const double* __restrict__ x,
@@ -119,71 +123,81 @@ SellSpmvKernel(int R, int Cn, int TW, int RR, int spi, const int32_t* __restrict
   extern __shared__ __align__(128) double xs[];
   __shared__ __align__(8) unsigned long long bar;
   if (skip && *skip) return;  // speculative launch after the CG loop converged (kkt.cu)
-  const int item = blockIdx.x;
-  const int t = item / RR;
-  const int c0 = t * TW;
-  const int cw = min(TW, Cn - c0);
+  const int item_lo = cta_begin[blockIdx.x], item_hi = cta_begin[blockIdx.x + 1];
+  if (item_lo >= item_hi) return;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint32_t bar_a = SmemAddr(&bar);
   if (use_tma) {
-    // one TMA bulk copy of the x tile (cp.async.bulk, completion on an mbarrier)
-    const uint32_t bar_a = SmemAddr(&bar);
-    const uint32_t bytes = (uint32_t)cw * 8u;
     if (threadIdx.x == 0) {
       asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_a));
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_a), "r"(bytes) : "memory");
-      asm volatile(
-          "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-          ::"r"(SmemAddr(xs)), "l"(x + c0), "r"(bytes), "r"(bar_a) : "memory");
-    }
-    // wait (phase 0)
-    uint32_t done = 0;
-    while (!done) {
-      asm volatile(
-          "{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}\n"
-          : "=r"(done) : "r"(bar_a), "r"(0u) : "memory");
-    }
-  } else {
-    for (int i = threadIdx.x; i < cw; i += kSellThreads) xs[i] = x[c0 + i];
-    __syncthreads();
   }
-  const int s0 = item * spi;
-  double* Pt = P + (size_t)t * R;
-  for (int s = s0 + warp; s < s0 + spi; s += kSellThreads / 32) {
-    const int len = sl_len[s];
-    const int row = rowid[(size_t)s * 32 + lane];
-    const double* v = val + voff[s] + lane;
-    const uint16_t* ix = idx + ioff[s] + lane * 4;
-    double acc0 = 0.0, acc1 = 0.0;
-    int k = 0;
-    for (; k + 8 <= len; k += 8) {
-      const uint2 qa = *reinterpret_cast<const uint2*>(ix + (size_t)(k >> 2) * 128);
-      const uint2 qb = *reinterpret_cast<const uint2*>(ix + (size_t)((k >> 2) + 1) * 128);
-      const double v0 = LdStream(v + (size_t)(k + 0) * 32), v1 = LdStream(v + (size_t)(k + 1) * 32);
-      const double v2 = LdStream(v + (size_t)(k + 2) * 32), v3 = LdStream(v + (size_t)(k + 3) * 32);
-      const double v4 = LdStream(v + (size_t)(k + 4) * 32), v5 = LdStream(v + (size_t)(k + 5) * 32);
-      const double v6 = LdStream(v + (size_t)(k + 6) * 32), v7 = LdStream(v + (size_t)(k + 7) * 32);
-      acc0 += v0 * xs[qa.x & 0xFFFF];
-      acc1 += v1 * xs[qa.x >> 16];
-      acc0 += v2 * xs[qa.y & 0xFFFF];
-      acc1 += v3 * xs[qa.y >> 16];
-      acc0 += v4 * xs[qb.x & 0xFFFF];
-      acc1 += v5 * xs[qb.x >> 16];
-      acc0 += v6 * xs[qb.y & 0xFFFF];
-      acc1 += v7 * xs[qb.y >> 16];
+  int cur_t = -1;
+  uint32_t phase = 0;
+  for (int item = item_lo; item < item_hi; item++) {
+    const int t = item / RR;
+    if (t != cur_t) {
+      const int c0 = t * TW;
+      const int cw = min(TW, Cn - c0);
+      __syncthreads();  // every warp is done reading the previous tile (and sees the barrier init)
+      if (use_tma) {
+        // one TMA bulk copy of the x tile (cp.async.bulk, completion on an mbarrier)
+        const uint32_t bytes = (uint32_t)cw * 8u;
+        if (threadIdx.x == 0) {
+          asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_a), "r"(bytes) : "memory");
+          asm volatile(
+              "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+              ::"r"(SmemAddr(xs)), "l"(x + c0), "r"(bytes), "r"(bar_a) : "memory");
+        }
+        uint32_t done = 0;
+        while (!done) {
+          asm volatile(
+              "{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}\n"
+              : "=r"(done) : "r"(bar_a), "r"(phase) : "memory");
+        }
+        phase ^= 1u;
+      } else {
+        for (int i = threadIdx.x; i < cw; i += kSellThreads) xs[i] = x[c0 + i];
+        __syncthreads();
+      }
+      cur_t = t;
     }
-    for (; k < len; k += 4) {
-      const uint2 q = *reinterpret_cast<const uint2*>(ix + (size_t)(k >> 2) * 128);
-      const int rem = len - k;
-      acc0 += LdStream(v + (size_t)k * 32) * xs[q.x & 0xFFFF];
-      if (rem > 1) acc1 += LdStream(v + (size_t)(k + 1) * 32) * xs[q.x >> 16];
-      if (rem > 2) acc0 += LdStream(v + (size_t)(k + 2) * 32) * xs[q.y & 0xFFFF];
-      if (rem > 3) acc1 += LdStream(v + (size_t)(k + 3) * 32) * xs[q.y >> 16];
+    const int s0 = item * spi;
+    double* Pt = P + (size_t)t * R;
+    for (int s = s0 + warp; s < s0 + spi; s += kSellThreads / 32) {
+      const int len = sl_len[s];
+      const int row = rowid[(size_t)s * 32 + lane];
+      const double* v = val + voff[s] + lane;
+      const uint16_t* ix = idx + ioff[s] + lane * 4;
+      double acc0 = 0.0, acc1 = 0.0;
+      int k = 0;
+      for (; k + 8 <= len; k += 8) {
+        const uint2 qa = *reinterpret_cast<const uint2*>(ix + (size_t)(k >> 2) * 128);
+        const uint2 qb = *reinterpret_cast<const uint2*>(ix + (size_t)((k >> 2) + 1) * 128);
+        const double v0 = LdStream(v + (size_t)(k + 0) * 32), v1 = LdStream(v + (size_t)(k + 1) * 32);
+        const double v2 = LdStream(v + (size_t)(k + 2) * 32), v3 = LdStream(v + (size_t)(k + 3) * 32);
+        const double v4 = LdStream(v + (size_t)(k + 4) * 32), v5 = LdStream(v + (size_t)(k + 5) * 32);
+        const double v6 = LdStream(v + (size_t)(k + 6) * 32), v7 = LdStream(v + (size_t)(k + 7) * 32);
+        acc0 += v0 * xs[qa.x & 0xFFFF];
+        acc1 += v1 * xs[qa.x >> 16];
+        acc0 += v2 * xs[qa.y & 0xFFFF];
+        acc1 += v3 * xs[qa.y >> 16];
+        acc0 += v4 * xs[qb.x & 0xFFFF];
+        acc1 += v5 * xs[qb.x >> 16];
+        acc0 += v6 * xs[qb.y & 0xFFFF];
+        acc1 += v7 * xs[qb.y >> 16];
+      }
+      for (; k < len; k += 4) {
+        const uint2 q = *reinterpret_cast<const uint2*>(ix + (size_t)(k >> 2) * 128);
+        const int rem = len - k;
+        acc0 += LdStream(v + (size_t)k * 32) * xs[q.x & 0xFFFF];
+        if (rem > 1) acc1 += LdStream(v + (size_t)(k + 1) * 32) * xs[q.x >> 16];
+        if (rem > 2) acc0 += LdStream(v + (size_t)(k + 2) * 32) * xs[q.y & 0xFFFF];
+        if (rem > 3) acc1 += LdStream(v + (size_t)(k + 3) * 32) * xs[q.y >> 16];
+      }
+      if (row >= 0) Pt[row] = acc0 + acc1;
     }
-    if (row >= 0) Pt[row] = acc0 + acc1;
   }
 }
 
@@ -210,11 +224,14 @@ void BuildSell(Ctx* ctx, const Csr& A, Sell* S) {
   int TW = (Cn + T - 1) / T;
   TW = (TW + 1) / 2 * 2;  // keep tile starts 16-byte aligned for the bulk copy
   S->T = T; S->TW = TW;
-  const int target_items = ctx->sm_count * 2;
-  int RR = std::max(1, (target_items + T - 1) / T);
-  int rows_per = (R + RR - 1) / RR;
-  rows_per = std::max(32, (rows_per + 31) / 32 * 32);
-  RR = (R + rows_per - 1) / rows_per;
+  // about 8 work items per CTA so that the static partition below balances to ~1/8 of an
+  // item, but at least 1024 rows (one 32-row slice per warp) per item
+  const int64_t want_items = (int64_t)ctx->sm_count * 8;
+  int rows_per = (int)(((int64_t)R * T + want_items - 1) / want_items);
+  rows_per = std::max(1024, rows_per);
+  rows_per = std::min(rows_per, std::max(32, R));
+  rows_per = (rows_per + 31) / 32 * 32;
+  int RR = (R + rows_per - 1) / rows_per;
   S->RR = RR; S->rows_per = rows_per;
   const int spi = rows_per / 32;
   const int n_slices = T * RR * spi;
@@ -253,6 +270,37 @@ void BuildSell(Ctx* ctx, const Csr& A, Sell* S) {
   S->val.alloc(ctx, std::max<int64_t>(S->n_val, 1));
   S->idx.alloc(ctx, std::max<int64_t>(S->n_idx, 4));
   S->rowid.alloc(ctx, (size_t)n_slices * 32);
+  {
+    // static partition of the tile-major item list over the CTAs, balanced by stored bytes
+    // (10 per non-zero) plus the x-tile staging a CTA pays when it enters a new tile
+    const int items = T * RR;
+    std::vector<int64_t> hv(n_slices + 1);
+    CUDA_CHECK(cudaMemcpyAsync(hv.data(), S->voff.p, (n_slices + 1) * sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
+    CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+    std::vector<double> cost(items + 1, 0.0);
+    for (int i = 0; i < items; i++) {
+      double c = 10.0 * (double)(hv[(size_t)(i + 1) * spi] - hv[(size_t)i * spi]) + 12.0 * rows_per;
+      if (i % RR == 0) c += 8.0 * TW;
+      cost[i + 1] = cost[i] + c;
+    }
+    const int G = std::max(1, std::min(items, ctx->sm_count));
+    std::vector<int32_t> begin(G + 1, items);
+    begin[0] = 0;
+    int it = 0;
+    for (int g = 1; g < G; g++) {
+      const double target = cost[items] * g / G;
+      while (it < items && cost[it + 1] <= target) it++;
+      // closer boundary of the two around the target
+      int cut = it;
+      if (it < items && (target - cost[it]) > (cost[it + 1] - target)) cut = it + 1;
+      begin[g] = std::max(cut, begin[g - 1]);
+    }
+    begin[G] = items;
+    S->n_cta = G;
+    S->cta_begin.alloc(ctx, G + 1);
+    S->cta_begin.upload(begin.data(), G + 1);
+    CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+  }
   SellFillKernel<<<(n_slices + 7) / 8, 256, 0, ctx->stream>>>(
       R, T, RR, rows_per, TW, n_slices, vals_out.p, segstart.p, seglen.p, A.col.p, A.val.p, S->sl_len.p,
       S->voff.p, S->ioff.p, S->val.p, S->idx.p, S->rowid.p);
@@ -278,8 +326,8 @@ void SellApply(Ctx* ctx, const Sell& S, double alpha, const double* x, double be
     // pointer and the width of the last tile can break that
     const int last = S.Cn - (S.T - 1) * S.TW;
     const int use_tma = ((reinterpret_cast<uintptr_t>(x) & 15) == 0 && last % 2 == 0) ? 1 : 0;
-    SellSpmvKernel<<<S.T * S.RR, kSellThreads, (size_t)S.TW * 8 + 64, ctx->stream>>>(
-        S.R, S.Cn, S.TW, S.RR, S.rows_per / 32, S.sl_len.p, S.voff.p, S.ioff.p, S.val.p, S.idx.p,
+    SellSpmvKernel<<<S.n_cta, kSellThreads, (size_t)S.TW * 8 + 64, ctx->stream>>>(
+        S.R, S.Cn, S.TW, S.RR, S.rows_per / 32, S.cta_begin.p, S.sl_len.p, S.voff.p, S.ioff.p, S.val.p, S.idx.p,
         S.rowid.p, x, P, use_tma, skip);
     ctx->count_launch();
   }
