@@ -341,8 +341,24 @@ def main_ours(args):
         dist.destroy_process_group()
 
 
+def _only_json_on_stdout():
+    """Route everything libraries print to fd 1 (NCCL's version banner, torchrun notices) to
+    stderr; the returned file is the real stdout for the one JSON line."""
+    sys.stdout.flush()
+    real = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    return real
+
+
 if __name__ == "__main__":
     a = parse_args()
+    _REAL_STDOUT = _only_json_on_stdout()
+    _print = print
+
+    def print(*args, **kw):  # noqa: A001  (the JSON line goes to the real stdout)
+        kw.setdefault("file", _REAL_STDOUT)
+        _print(*args, **kw)
+        kw["file"].flush()
     if a.impl == "reference":
         main_reference(a)
     else:
