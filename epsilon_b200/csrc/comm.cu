@@ -15,7 +15,7 @@ typedef struct ncclComm* ncclComm_t;
 typedef struct { char internal[128]; } ncclUniqueId;
 typedef int ncclResult_t;
 enum { ncclSuccess = 0 };
-enum { ncclFloat64 = 8 };  // ncclDataType_t
+enum { ncclInt8 = 0, ncclFloat64 = 8 };  // ncclDataType_t
 enum { ncclSum = 0 };      // ncclRedOp_t
 
 struct NcclApi {
@@ -24,6 +24,7 @@ struct NcclApi {
   ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
   ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
   ncclResult_t (*AllReduce)(const void*, void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*AllGather)(const void*, void*, size_t, int, ncclComm_t, cudaStream_t) = nullptr;
   const char* (*GetErrorString)(ncclResult_t) = nullptr;
 };
 
@@ -45,6 +46,7 @@ NcclApi& Api() {
   api.CommInitRank = reinterpret_cast<decltype(api.CommInitRank)>(sym("ncclCommInitRank"));
   api.CommDestroy = reinterpret_cast<decltype(api.CommDestroy)>(sym("ncclCommDestroy"));
   api.AllReduce = reinterpret_cast<decltype(api.AllReduce)>(sym("ncclAllReduce"));
+  api.AllGather = reinterpret_cast<decltype(api.AllGather)>(sym("ncclAllGather"));
   api.GetErrorString = reinterpret_cast<decltype(api.GetErrorString)>(sym("ncclGetErrorString"));
   return api;
 }
@@ -94,6 +96,68 @@ void AllReduceSum(Ctx* ctx, double* buf, int64_t n) {
   ProfScope ps(ctx, KC_ALLREDUCE, 8.0 * n);
   NCCL_CHECK(Api().AllReduce(buf, buf, (size_t)n, ncclFloat64, ncclSum, ctx->comm->comm, ctx->stream));
   ctx->count_launch();
+}
+
+// ---- one-shot peer all-reduce: buffers mapped into every rank through CUDA IPC -------------
+// Layout of each rank's block: [flags: 2*G u64, padded to 4 KB][counter][receive: 2*G*n f64].
+void PeerSetup(Ctx* ctx, int64_t n, PeerBuf* out) {
+  out->ready = false;
+  const int G = ctx->n_ranks;
+  if (G <= 1 || G > kMaxRanks || !ctx->comm || getenv("EPS_NO_PEER")) return;
+  const size_t head = 4096;
+  const size_t bytes = head + sizeof(double) * 2 * (size_t)G * n;
+  CUDA_CHECK(cudaMalloc(&out->block, bytes));
+  ctx->bytes_allocated += bytes;
+  CUDA_CHECK(cudaMemsetAsync(out->block, 0, bytes, ctx->stream));
+  cudaIpcMemHandle_t mine;
+  int ok = cudaIpcGetMemHandle(&mine, out->block) == cudaSuccess ? 1 : 0;
+  if (!ok) cudaGetLastError();
+  // gather {ok, handle} of every rank
+  struct Rec { int ok; int pad; cudaIpcMemHandle_t h; };
+  Rec rec; memset(&rec, 0, sizeof(rec));
+  rec.ok = ok; rec.h = mine;
+  DevBuf<char> send(ctx, sizeof(Rec)), recv(ctx, sizeof(Rec) * G);
+  CUDA_CHECK(cudaMemcpyAsync(send.p, &rec, sizeof(Rec), cudaMemcpyHostToDevice, ctx->stream));
+  NCCL_CHECK(Api().AllGather(send.p, recv.p, sizeof(Rec), ncclInt8, ctx->comm->comm, ctx->stream));
+  std::vector<Rec> all(G);
+  CUDA_CHECK(cudaMemcpyAsync(all.data(), recv.p, sizeof(Rec) * G, cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+  int good = 1;
+  for (int r = 0; r < G; r++) good &= all[r].ok;
+  for (int r = 0; r < G && good; r++) {
+    if (r == ctx->rank) { out->mapped[r] = nullptr; continue; }
+    if (cudaIpcOpenMemHandle(&out->mapped[r], all[r].h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+      cudaGetLastError();
+      out->mapped[r] = nullptr;
+      good = 0;
+    }
+  }
+  // every rank must take the same decision
+  DevBuf<double> agree(ctx, 1);
+  double g = good ? 0.0 : 1.0;
+  CUDA_CHECK(cudaMemcpyAsync(agree.p, &g, sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+  NCCL_CHECK(Api().AllReduce(agree.p, agree.p, 1, ncclFloat64, ncclSum, ctx->comm->comm, ctx->stream));
+  CUDA_CHECK(cudaMemcpyAsync(&g, agree.p, sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+  if (g != 0.0) { PeerRelease(out); return; }
+  out->x.G = G;
+  out->x.rank = ctx->rank;
+  out->x.n = n;
+  for (int r = 0; r < G; r++) {
+    char* base = static_cast<char*>(r == ctx->rank ? out->block : out->mapped[r]);
+    out->x.flag[r] = reinterpret_cast<unsigned long long*>(base);
+    out->x.recv[r] = reinterpret_cast<double*>(base + head);
+  }
+  out->counter = reinterpret_cast<unsigned*>(static_cast<char*>(out->block) + 2048);
+  out->seq = 0;
+  out->ready = true;
+}
+
+void PeerRelease(PeerBuf* pb) {
+  for (int r = 0; r < kMaxRanks; r++)
+    if (pb->mapped[r]) { cudaIpcCloseMemHandle(pb->mapped[r]); pb->mapped[r] = nullptr; }
+  if (pb->block) { cudaFree(pb->block); pb->block = nullptr; }
+  pb->ready = false;
 }
 
 }  // namespace eps

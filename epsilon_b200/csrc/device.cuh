@@ -144,6 +144,15 @@ __device__ __forceinline__ int LdStreamI(const int32_t* p) {
   return r;
 }
 
+__device__ __forceinline__ unsigned long long LdAcquireSys(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void StReleaseSys(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
 inline int GridFor(int64_t n, int block, int per_thread, int sm_count, int max_waves = 8) {
   int64_t g = (n + (int64_t)block * per_thread - 1) / ((int64_t)block * per_thread);
   int64_t cap = (int64_t)sm_count * max_waves;

@@ -194,8 +194,35 @@ void CsrApply(Ctx* ctx, const Csr& A, double alpha, const double* x, double beta
 void BuildCsrFromHost(Ctx* ctx, int m, int n, int64_t nnz, const int64_t* rowptr,
                       const int32_t* col, const double* val, Csr* out);
 void BuildSell(Ctx* ctx, const Csr& A, Sell* S);
+// One-shot all-reduce over NVLink peer memory (comm.cu): every rank PUSHES its n-vector into
+// slot [parity][rank] of every peer's receive buffer and then raises flag [parity][rank] on
+// that peer; the consumer waits for its G local flags and adds the G slots in rank order, so
+// all ranks obtain bit-identical sums.  Passed to kernels by value.
+constexpr int kMaxRanks = 8;
+struct PeerXchg {
+  double* recv[kMaxRanks] = {};              // recv[r]: rank r's buffer [2][G][n], mapped here
+  unsigned long long* flag[kMaxRanks] = {};  // flag[r]: rank r's flags [2][G]
+  int G = 0, rank = 0;
+  int64_t n = 0;
+};
+struct PeerBuf {
+  bool ready = false;
+  PeerXchg x;
+  void* block = nullptr;        // local allocation (flags + receive buffer)
+  void* mapped[kMaxRanks] = {}; // peers' blocks opened through CUDA IPC
+  unsigned* counter = nullptr;  // CTA arrival counter of the publishing kernel
+  unsigned long long seq = 0;   // last sequence number handed out
+};
+// Collective over the communicator; leaves out->ready false when peer mapping is unavailable
+// (the callers then fall back to ncclAllReduce).
+void PeerSetup(Ctx* ctx, int64_t n, PeerBuf* out);
+void PeerRelease(PeerBuf* pb);
+
 // Optional fusions of a sparse apply (used by the CG loop of kkt.cu).
 struct SpmvExtra {
+  const PeerXchg* publish = nullptr;  // push the result to all ranks instead of writing y
+  unsigned long long publish_seq = 0;
+  unsigned* publish_counter = nullptr;
   const int* skip = nullptr;      // device flag: when non-zero the kernels return at once
   const double* ep_d = nullptr;   // y += ep_d .* ep_p after the alpha/beta update
   const double* ep_p = nullptr;

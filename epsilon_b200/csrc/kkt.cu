@@ -5,6 +5,7 @@
 
 #include "device.cuh"
 #include "kkt.h"
+#include "peer.cuh"
 #include "prox.cuh"
 
 namespace eps {
@@ -37,13 +38,16 @@ __global__ void __launch_bounds__(kBlock)
 CgStartKernel(int64_t n, const double* __restrict__ rhs, const double* __restrict__ w,
               double* __restrict__ r, double* __restrict__ p, double tol, double* scal,
               double* partials, unsigned* counter, int* done, KktSolver::CgResult* ring,
-              long long seq) {
+              long long seq, PeerXchg px, unsigned long long xseq, const double* __restrict__ dg,
+              const double* __restrict__ x0) {
   __shared__ double smem[64];
   double acc[2] = {0.0, 0.0};
   const int64_t stride = (int64_t)gridDim.x * kBlock;
+  if (xseq) PeerWait(px, xseq);  // w = sum over ranks of the published parts + d.*x0
   for (int64_t i = (int64_t)blockIdx.x * kBlock + threadIdx.x; i < n; i += stride) {
     const double b = rhs[i];
-    const double t = b - w[i];
+    const double wi = xseq ? PeerSum(px, xseq, i) + dg[i] * x0[i] : w[i];
+    const double t = b - wi;
     r[i] = t;
     p[i] = t;
     acc[0] += t * t;
@@ -67,12 +71,18 @@ CgStartKernel(int64_t n, const double* __restrict__ rhs, const double* __restric
 //   a = rr / p.w;  x += a p;  r -= a w;  rr' = r.r;  p = r + (rr'/rr) p
 // and the publication of (rr', converged) for the host.  No-op once `done` is raised.
 __global__ void __launch_bounds__(kTailBlock)
-CgTailKernel(int64_t n, const double* __restrict__ w, double* __restrict__ p, double* __restrict__ x,
+CgTailKernel(int64_t n, double* __restrict__ w, double* __restrict__ p, double* __restrict__ x,
              double* __restrict__ r, double* scal, double* partials, int* done,
-             KktSolver::CgResult* ring, long long seq) {
+             KktSolver::CgResult* ring, long long seq, PeerXchg px, unsigned long long xseq,
+             const double* __restrict__ dg) {
   namespace cg = cooperative_groups;
   __shared__ double smem[64];
-  if (*done) return;  // uniform: only ever written by the last phase of an earlier launch
+  if (*done) {  // uniform: only ever written by the last phase of an earlier launch
+    // the exchange of the speculative iteration is still consumed, so that a peer can never
+    // run two exchanges ahead of this rank (double-buffered slots)
+    if (xseq) PeerWait(px, xseq);
+    return;
+  }
   cg::grid_group grid = cg::this_grid();
   const int G = gridDim.x;
   const int64_t stride = (int64_t)G * kTailBlock;
@@ -80,7 +90,18 @@ CgTailKernel(int64_t n, const double* __restrict__ w, double* __restrict__ p, do
   const double rr = scal[0];
   const double thresh = scal[1];
   double v[1] = {0.0};
-  for (int64_t i = first; i < n; i += stride) v[0] += p[i] * w[i];
+  if (xseq) {
+    // fused receive side of the all-reduce: w = sum_ranks(published) + d.*p
+    PeerWait(px, xseq);
+    for (int64_t i = first; i < n; i += stride) {
+      const double pi = p[i];
+      const double wi = PeerSum(px, xseq, i) + dg[i] * pi;
+      w[i] = wi;
+      v[0] += pi * wi;
+    }
+  } else {
+    for (int64_t i = first; i < n; i += stride) v[0] += p[i] * w[i];
+  }
   BlockSum<1>(v, smem);
   if (threadIdx.x == 0) partials[blockIdx.x] = v[0];
   grid.sync();
@@ -209,6 +230,7 @@ void AddBlock(Ctx* ctx, int nb, const double* G, int64_t ldg, double* M, int64_t
 KktSolver::~KktSolver() {
   if (h_scal) cudaFreeHost(h_scal);
   if (ring) cudaFreeHost(ring);
+  PeerRelease(&peer);
 }
 
 void KktSolver::Init(const std::vector<double>& g_host, const std::vector<double>& c_host) {
@@ -329,9 +351,11 @@ void KktSolver::Init(const std::vector<double>& g_host, const std::vector<double
     fast_h = a_diag && alpha2 != 0.0 && H.blks.size() == 1 && H.blks[0].map->kind == MK_SPARSE &&
              H.blks[0].row_off == 0 && H.blks[0].col_off == 0 && H.blks[0].m() == rows_h &&
              H.blks[0].n() == n && H.blks[0].map->sell.built && H.blks[0].map->sell_t.built;
+    if (fast_h && h_sharded) PeerSetup(ctx, n, &peer);
     CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
-    description = Format("kkt=CG n=%lld rows_h=%lld tol=%.1e%s%s", (long long)n, (long long)rows_h, cg_tol,
-                         h_sharded ? " sharded" : "", fast_h ? " fused-matvec" : "");
+    description = Format("kkt=CG n=%lld rows_h=%lld tol=%.1e%s%s%s", (long long)n, (long long)rows_h, cg_tol,
+                         h_sharded ? " sharded" : "", fast_h ? " fused-matvec" : "",
+                         peer.ready ? " peer-allreduce" : "");
   } else {
     throw Error(EPS_ERR_INVALID, Format("unknown kkt mode %d", mode));
   }
@@ -347,11 +371,21 @@ void KktSolver::MatVec(const double* p, double* w, const int* skip) {
     SpmvExtra e1, e2;
     e1.skip = skip;
     e2.skip = skip;
-    if (!h_sharded || ctx->rank == 0) { e2.ep_d = ddiag.p; e2.ep_p = p; }
+    pending_seq = 0;
+    if (peer.ready) {
+      // push this rank's part to every rank; the kernel that consumes w (CgStart / CgTail)
+      // completes the sum and adds d.*p.  Never skipped: see CgTailKernel.
+      e2.publish = &peer.x;
+      e2.publish_seq = pending_seq = ++peer.seq;
+      e2.publish_counter = peer.counter;
+    } else if (!h_sharded || ctx->rank == 0) {
+      e2.ep_d = ddiag.p;
+      e2.ep_p = p;
+    }
     SellApply(ctx, b.trans ? M.sell_t : M.sell, b.scale, p, 0.0, th1.p, b.trans ? KC_SPMV_T : KC_SPMV_N, &e1);
     SellApply(ctx, b.trans ? M.sell : M.sell_t, alpha2 * b.scale, th1.p, 0.0, w,
               b.trans ? KC_SPMV_N : KC_SPMV_T, &e2);
-    if (h_sharded) AllReduceSum(ctx, w, n);
+    if (h_sharded && !peer.ready) AllReduceSum(ctx, w, n);
     return;
   }
   bool have = false;
@@ -415,7 +449,8 @@ void KktSolver::Solve(const double* rhs, double* x) {
       };
       MatVec(x, cg_w.p, nullptr);
       CgStartKernel<<<grid, kBlock, 0, ctx->stream>>>(n, rhs, cg_w.p, cg_r.p, cg_p.p, cg_tol, scal.p,
-                                                       rs.partials, rs.counter, cg_done.p, ring, base);
+                                                       rs.partials, rs.counter, cg_done.p, ring, base,
+                                                       peer.x, pending_seq, ddiag.p, x);
       ctx->count_launch();
       int it = 0;
       bool converged = false;
@@ -427,12 +462,15 @@ void KktSolver::Solve(const double* rhs, double* x) {
         {
           ProfScope ps(ctx, KC_VEC, 72.0 * n);
           int64_t nn = n;
-          const double* wp = cg_w.p;
+          double* wp = cg_w.p;
           double *pp = cg_p.p, *xp = x, *rp = cg_r.p, *sp = scal.p, *part = cg_partials.p;
           int* dp = cg_done.p;
           CgResult* rg = ring;
           long long seq = base + it + 1;
-          void* args[] = {&nn, &wp, &pp, &xp, &rp, &sp, &part, &dp, &rg, &seq};
+          PeerXchg pxv = peer.x;
+          unsigned long long xs = pending_seq;
+          const double* dgp = ddiag.p;
+          void* args[] = {&nn, &wp, &pp, &xp, &rp, &sp, &part, &dp, &rg, &seq, &pxv, &xs, &dgp};
           CUDA_CHECK(cudaLaunchCooperativeKernel((const void*)CgTailKernel, dim3(tail_grid),
                                                  dim3(kTailBlock), args, 0, ctx->stream));
           ctx->count_launch();

@@ -1,0 +1,47 @@
+// Device side of the one-shot peer all-reduce (see PeerXchg in internal.h, host side in comm.cu).
+#pragma once
+#include "device.cuh"
+#include "internal.h"
+
+namespace eps {
+
+// Publisher, called by every thread of every CTA after its last store into the peers' slots:
+// the last CTA to arrive raises flag [parity][rank] = seq on every rank.
+__device__ __forceinline__ void PeerPublishFinish(const PeerXchg& px, unsigned long long seq,
+                                                  unsigned* counter) {
+  __threadfence_system();  // this thread's remote stores are visible system-wide
+  __syncthreads();
+  __shared__ bool last_;
+  if (threadIdx.x == 0) {
+    const unsigned prev = atomicAdd(counter, 1u);
+    last_ = prev == gridDim.x - 1;
+  }
+  __syncthreads();
+  if (!last_) return;
+  __threadfence_system();
+  if (threadIdx.x < px.G) {
+    const int parity = (int)(seq & 1ull);
+    StReleaseSys(px.flag[threadIdx.x] + parity * px.G + px.rank, seq);
+  }
+  if (threadIdx.x == 0) *counter = 0;
+}
+
+// Consumer: block until all G ranks have published `seq`.  Called by every thread of the CTA.
+__device__ __forceinline__ void PeerWait(const PeerXchg& px, unsigned long long seq) {
+  if (threadIdx.x < px.G) {
+    const unsigned long long* f = px.flag[px.rank] + (int)(seq & 1ull) * px.G + threadIdx.x;
+    while (LdAcquireSys(f) < seq) {}
+  }
+  __syncthreads();
+}
+
+// Sum of the G published slots at element i, in rank order (identical on every rank).
+// __ldcg: the slots are rewritten by peers every other exchange, L1 must not serve them.
+__device__ __forceinline__ double PeerSum(const PeerXchg& px, unsigned long long seq, int64_t i) {
+  const double* base = px.recv[px.rank] + (size_t)(seq & 1ull) * px.G * px.n + i;
+  double s = 0.0;
+  for (int r = 0; r < px.G; r++) s += __ldcg(base + (size_t)r * px.n);
+  return s;
+}
+
+}  // namespace eps

@@ -16,6 +16,7 @@
 
 #include "device.cuh"
 #include "internal.h"
+#include "peer.cuh"
 
 namespace eps {
 
@@ -215,6 +216,26 @@ SellReduceKernel(int R, int T, const double* __restrict__ P, double alpha, doubl
   y[row] = out;
 }
 
+// Same reduction, but the result is this rank's contribution to a cross-GPU sum: it is
+// pushed over NVLink into slot [parity][rank] of every rank's receive buffer (P2P stores),
+// fused with the reduction so that the transfer overlaps it CTA by CTA.
+__global__ void __launch_bounds__(256)
+SellReducePublishKernel(int R, int T, const double* __restrict__ P, double alpha, PeerXchg px,
+                        unsigned long long seq, unsigned* counter) {
+  const int row = blockIdx.x * 256 + threadIdx.x;
+  if (row < R) {
+    double s = 0.0;
+    for (int t = 0; t < T; t++) s += P[(size_t)t * R + row];
+    const double out = alpha * s;
+    const size_t slot = ((size_t)(seq & 1ull) * px.G + px.rank) * px.n + row;
+    for (int k = 0; k < px.G; k++) {
+      const int r = (px.rank + k) % px.G;  // start with the local copy, spread the peers
+      px.recv[r][slot] = out;
+    }
+  }
+  PeerPublishFinish(px, seq, counter);
+}
+
 }  // namespace
 
 void BuildSell(Ctx* ctx, const Csr& A, Sell* S) {
@@ -330,6 +351,14 @@ void SellApply(Ctx* ctx, const Sell& S, double alpha, const double* x, double be
         S.R, S.Cn, S.TW, S.RR, S.rows_per / 32, S.cta_begin.p, S.sl_len.p, S.voff.p, S.ioff.p, S.val.p, S.idx.p,
         S.rowid.p, x, P, use_tma, skip);
     ctx->count_launch();
+  }
+  if (ex && ex->publish) {
+    EPS_CHECK(beta == 0.0 && ex->publish->n == S.R, "publishing apply: beta must be 0 and sizes must match");
+    ProfScope ps(ctx, KC_ALLREDUCE, 8.0 * S.T * S.R + 8.0 * S.R * ex->publish->G);
+    SellReducePublishKernel<<<(S.R + 255) / 256, 256, 0, ctx->stream>>>(S.R, S.T, P, alpha, *ex->publish,
+                                                                         ex->publish_seq, ex->publish_counter);
+    ctx->count_launch();
+    return;
   }
   ProfScope ps(ctx, KC_VEC, 8.0 * S.T * S.R + 8.0 * S.R);
   SellReduceKernel<<<(S.R + 255) / 256, 256, 0, ctx->stream>>>(S.R, S.T, P, alpha, beta, y, skip,
