@@ -81,9 +81,14 @@ void CommInit(Ctx* ctx, int n_ranks, int rank, const void* unique_id) {
   auto* c = new Comm();
   NCCL_CHECK(Api().CommInitRank(&c->comm, n_ranks, id, rank));
   ctx->comm = c;
+  // map the peer buffers now (CUDA IPC opens cost ~0.1 s per peer): communicator set-up, not
+  // solver set-up.  Grown on demand for longer vectors.
+  const char* cap = getenv("EPS_PEER_CAPACITY");
+  PeerEnsure(ctx, cap ? atoll(cap) : (int64_t)1 << 18);
 }
 
 void CommDestroy(Ctx* ctx) {
+  if (ctx->peer) { PeerRelease(ctx->peer); delete ctx->peer; ctx->peer = nullptr; }
   if (!ctx->comm) return;
   if (ctx->comm->comm) Api().CommDestroy(ctx->comm->comm);
   delete ctx->comm;
@@ -100,10 +105,9 @@ void AllReduceSum(Ctx* ctx, double* buf, int64_t n) {
 
 // ---- one-shot peer all-reduce: buffers mapped into every rank through CUDA IPC -------------
 // Layout of each rank's block: [flags: 2*G u64, padded to 4 KB][counter][receive: 2*G*n f64].
-void PeerSetup(Ctx* ctx, int64_t n, PeerBuf* out) {
+static void PeerSetup(Ctx* ctx, int64_t n, PeerBuf* out) {
   out->ready = false;
   const int G = ctx->n_ranks;
-  if (G <= 1 || G > kMaxRanks || !ctx->comm || getenv("EPS_NO_PEER")) return;
   const size_t head = 4096;
   const size_t bytes = head + sizeof(double) * 2 * (size_t)G * n;
   CUDA_CHECK(cudaMalloc(&out->block, bytes));
@@ -151,6 +155,19 @@ void PeerSetup(Ctx* ctx, int64_t n, PeerBuf* out) {
   out->counter = reinterpret_cast<unsigned*>(static_cast<char*>(out->block) + 2048);
   out->seq = 0;
   out->ready = true;
+}
+
+PeerBuf* PeerEnsure(Ctx* ctx, int64_t n) {
+  const int G = ctx->n_ranks;
+  if (G <= 1 || G > kMaxRanks || !ctx->comm || getenv("EPS_NO_PEER")) return nullptr;
+  if (ctx->peer && ctx->peer->ready && ctx->peer->x.n >= n) return ctx->peer;
+  EPS_CHECK(!ctx->capturing, "peer buffer growth during graph capture");
+  CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+  if (ctx->peer) { PeerRelease(ctx->peer); delete ctx->peer; ctx->peer = nullptr; }
+  auto* pb = new PeerBuf();
+  ctx->peer = pb;
+  PeerSetup(ctx, n, pb);
+  return pb->ready ? pb : nullptr;
 }
 
 void PeerRelease(PeerBuf* pb) {

@@ -82,6 +82,7 @@ struct DevBuf {
 
 // ---- context --------------------------------------------------------------------
 struct Comm;  // NCCL (dlopen'ed), comm.cu
+struct PeerBuf;  // NVLink peer buffers of the one-shot all-reduce, comm.cu
 
 // Kernel classes for the profile mode (CUDA events around each launch).
 enum KClass {
@@ -100,6 +101,7 @@ struct Ctx {
   bool capturing = false;      // inside stream capture: launches counted per capture
   int64_t capture_launches = 0;
   Comm* comm = nullptr;
+  PeerBuf* peer = nullptr;     // owned; created collectively by PeerEnsure
   int n_ranks = 1, rank = 0;
   // profile mode
   bool profile = false;
@@ -203,7 +205,7 @@ struct PeerXchg {
   double* recv[kMaxRanks] = {};              // recv[r]: rank r's buffer [2][G][n], mapped here
   unsigned long long* flag[kMaxRanks] = {};  // flag[r]: rank r's flags [2][G]
   int G = 0, rank = 0;
-  int64_t n = 0;
+  int64_t n = 0;   // slot stride (capacity); vectors of up to n entries fit
 };
 struct PeerBuf {
   bool ready = false;
@@ -213,9 +215,9 @@ struct PeerBuf {
   unsigned* counter = nullptr;  // CTA arrival counter of the publishing kernel
   unsigned long long seq = 0;   // last sequence number handed out
 };
-// Collective over the communicator; leaves out->ready false when peer mapping is unavailable
-// (the callers then fall back to ncclAllReduce).
-void PeerSetup(Ctx* ctx, int64_t n, PeerBuf* out);
+// Collective over the communicator: the context's peer buffers with room for n-vectors, or
+// nullptr when peer mapping is unavailable (the callers then fall back to ncclAllReduce).
+PeerBuf* PeerEnsure(Ctx* ctx, int64_t n);
 void PeerRelease(PeerBuf* pb);
 
 // Optional fusions of a sparse apply (used by the CG loop of kkt.cu).

@@ -230,7 +230,6 @@ void AddBlock(Ctx* ctx, int nb, const double* G, int64_t ldg, double* M, int64_t
 KktSolver::~KktSolver() {
   if (h_scal) cudaFreeHost(h_scal);
   if (ring) cudaFreeHost(ring);
-  PeerRelease(&peer);
 }
 
 void KktSolver::Init(const std::vector<double>& g_host, const std::vector<double>& c_host) {
@@ -351,11 +350,11 @@ void KktSolver::Init(const std::vector<double>& g_host, const std::vector<double
     fast_h = a_diag && alpha2 != 0.0 && H.blks.size() == 1 && H.blks[0].map->kind == MK_SPARSE &&
              H.blks[0].row_off == 0 && H.blks[0].col_off == 0 && H.blks[0].m() == rows_h &&
              H.blks[0].n() == n && H.blks[0].map->sell.built && H.blks[0].map->sell_t.built;
-    if (fast_h && h_sharded) PeerSetup(ctx, n, &peer);
+    if (fast_h && h_sharded) peer = PeerEnsure(ctx, n);
     CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
     description = Format("kkt=CG n=%lld rows_h=%lld tol=%.1e%s%s%s", (long long)n, (long long)rows_h, cg_tol,
                          h_sharded ? " sharded" : "", fast_h ? " fused-matvec" : "",
-                         peer.ready ? " peer-allreduce" : "");
+                         peer ? " peer-allreduce" : "");
   } else {
     throw Error(EPS_ERR_INVALID, Format("unknown kkt mode %d", mode));
   }
@@ -372,12 +371,12 @@ void KktSolver::MatVec(const double* p, double* w, const int* skip) {
     e1.skip = skip;
     e2.skip = skip;
     pending_seq = 0;
-    if (peer.ready) {
+    if (peer) {
       // push this rank's part to every rank; the kernel that consumes w (CgStart / CgTail)
       // completes the sum and adds d.*p.  Never skipped: see CgTailKernel.
-      e2.publish = &peer.x;
-      e2.publish_seq = pending_seq = ++peer.seq;
-      e2.publish_counter = peer.counter;
+      e2.publish = &peer->x;
+      e2.publish_seq = pending_seq = ++peer->seq;
+      e2.publish_counter = peer->counter;
     } else if (!h_sharded || ctx->rank == 0) {
       e2.ep_d = ddiag.p;
       e2.ep_p = p;
@@ -385,7 +384,7 @@ void KktSolver::MatVec(const double* p, double* w, const int* skip) {
     SellApply(ctx, b.trans ? M.sell_t : M.sell, b.scale, p, 0.0, th1.p, b.trans ? KC_SPMV_T : KC_SPMV_N, &e1);
     SellApply(ctx, b.trans ? M.sell : M.sell_t, alpha2 * b.scale, th1.p, 0.0, w,
               b.trans ? KC_SPMV_N : KC_SPMV_T, &e2);
-    if (h_sharded && !peer.ready) AllReduceSum(ctx, w, n);
+    if (h_sharded && !peer) AllReduceSum(ctx, w, n);
     return;
   }
   bool have = false;
@@ -450,7 +449,7 @@ void KktSolver::Solve(const double* rhs, double* x) {
       MatVec(x, cg_w.p, nullptr);
       CgStartKernel<<<grid, kBlock, 0, ctx->stream>>>(n, rhs, cg_w.p, cg_r.p, cg_p.p, cg_tol, scal.p,
                                                        rs.partials, rs.counter, cg_done.p, ring, base,
-                                                       peer.x, pending_seq, ddiag.p, x);
+                                                       peer ? peer->x : PeerXchg(), pending_seq, ddiag.p, x);
       ctx->count_launch();
       int it = 0;
       bool converged = false;
@@ -467,7 +466,7 @@ void KktSolver::Solve(const double* rhs, double* x) {
           int* dp = cg_done.p;
           CgResult* rg = ring;
           long long seq = base + it + 1;
-          PeerXchg pxv = peer.x;
+          PeerXchg pxv = peer ? peer->x : PeerXchg();
           unsigned long long xs = pending_seq;
           const double* dgp = ddiag.p;
           void* args[] = {&nn, &wp, &pp, &xp, &rp, &sp, &part, &dp, &rg, &seq, &pxv, &xs, &dgp};

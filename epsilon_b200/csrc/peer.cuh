@@ -9,10 +9,12 @@ namespace eps {
 // the last CTA to arrive raises flag [parity][rank] = seq on every rank.
 __device__ __forceinline__ void PeerPublishFinish(const PeerXchg& px, unsigned long long seq,
                                                   unsigned* counter) {
-  __threadfence_system();  // this thread's remote stores are visible system-wide
+  // one system-scope fence per CTA: the barrier orders every thread's remote stores before
+  // thread 0's fence (fences are cumulative), which orders them before the counter update
   __syncthreads();
   __shared__ bool last_;
   if (threadIdx.x == 0) {
+    __threadfence_system();
     const unsigned prev = atomicAdd(counter, 1u);
     last_ = prev == gridDim.x - 1;
   }

@@ -353,7 +353,7 @@ void SellApply(Ctx* ctx, const Sell& S, double alpha, const double* x, double be
     ctx->count_launch();
   }
   if (ex && ex->publish) {
-    EPS_CHECK(beta == 0.0 && ex->publish->n == S.R, "publishing apply: beta must be 0 and sizes must match");
+    EPS_CHECK(beta == 0.0 && ex->publish->n >= S.R, "publishing apply: beta must be 0 and the vector must fit the slots");
     ProfScope ps(ctx, KC_ALLREDUCE, 8.0 * S.T * S.R + 8.0 * S.R * ex->publish->G);
     SellReducePublishKernel<<<(S.R + 255) / 256, 256, 0, ctx->stream>>>(S.R, S.T, P, alpha, *ex->publish,
                                                                          ex->publish_seq, ex->publish_counter);
