@@ -20,7 +20,7 @@ ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 COMMON = ["-O3", "-std=c++17", "-lineinfo", "--extended-lambda", "-Xcompiler", "-fPIC",
           "-Xcompiler", "-fvisibility=default", "-I", INCLUDE, "-I", CSRC]
 # Files whose elementwise arithmetic must round like the reference's x86-64 build (no FMA).
-NO_FMA = {"prox_elem.cu", "prox_block.cu", "tv1d.cu"}
+NO_FMA = {"prox_elem.cu", "prox_block.cu", "tv1d.cu", "tv1d_par.cu"}
 
 
 def sources():

@@ -375,6 +375,8 @@ void eps_solver::Init(const eps_problem& p) {
   graph_ok = params.use_graph && !params.profile;
   for (auto& op : ops)
     if (op.kkt && op.kkt->mode == EPS_KKT_CG) graph_ok = false;  // host-checked inner loop
+  for (auto& stp : stages)
+    if (stp->kind == ST_TV) graph_ok = false;                      // host-checked active-set rounds
   memset(&status, 0, sizeof(status));
   status.state = EPS_NOT_STARTED;
   status.m = (int32_t)m_total;
@@ -389,6 +391,7 @@ void eps_solver::ResetVariables() {
   x.zero();
   ybuf[0].zero();
   ybuf[1].zero();
+  for (auto& stp : stages) stp->tv_work.zero();  // cold active set for the TV solver
   parity = 0;
   iter = 0;
   started = false;

@@ -33,6 +33,7 @@ Ctx::~Ctx() {
   sell_scratch.release();
   red_partials.release();
   red_counter.release();
+  if (h_flag) cudaFreeHost(h_flag);
   if (own_stream && stream) cudaStreamDestroy(stream);
 }
 
@@ -63,6 +64,11 @@ ReduceScratch GetReduceScratch(Ctx* ctx) {
     ctx->red_counter.zero();
   }
   return ReduceScratch{ctx->red_partials.p, ctx->red_counter.p};
+}
+
+int* PinnedFlag(Ctx* ctx) {
+  if (!ctx->h_flag) CUDA_CHECK(cudaMallocHost(&ctx->h_flag, 64));
+  return ctx->h_flag;
 }
 
 double* GrowScratch(Ctx* ctx, DevBuf<double>* buf, size_t count) {

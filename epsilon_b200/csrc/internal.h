@@ -112,6 +112,7 @@ struct Ctx {
   DevBuf<double> split_scratch, seg_scratch, red_partials, sell_scratch;
   DevBuf<unsigned int> red_counter;
   int64_t scratch_generation = 0;
+  int* h_flag = nullptr;
   ~Ctx();
   void count_launch(int n = 1) {
     if (capturing) capture_launches += n; else launches += n;
@@ -249,6 +250,7 @@ struct ReduceScratch {
 };
 ReduceScratch GetReduceScratch(Ctx* ctx);
 double* GrowScratch(Ctx* ctx, DevBuf<double>* buf, size_t count);
+int* PinnedFlag(Ctx* ctx);  // one pinned host int for device->host round trips
 
 // ---- composite block operator (BlockMatrix, vector/block_matrix.h) --------------------
 struct Blk {

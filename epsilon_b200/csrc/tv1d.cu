@@ -22,7 +22,6 @@ namespace eps {
 
 namespace {
 
-// work layout (doubles): knot[2n] | slope[2n] | icpt[2n] | lo[n] | hi[n] | v[n]
 __global__ void TvForwardKernel(int n, const double* __restrict__ v, double lam, double* knot,
                                 double* slope, double* icpt, double* lo, double* hi, double* beta) {
   if (threadIdx.x != 0 || blockIdx.x != 0) return;
@@ -204,33 +203,57 @@ TvPostKernel(ElemSeg sg, const double* __restrict__ consts, const double* __rest
 
 }  // namespace
 
-size_t Tv1dWorkDoubles(int64_t len) {
+// tv1d_par.cu
+size_t Tv1dParallelBytes(int64_t n);
+int Tv1dParallelSolve(Ctx* ctx, int n, const double* v, double lam, double* beta, char* scratch,
+                      int* h_changed);
+
+namespace {
+// Below this length the sequential dynamic program on one thread beats ~15 rounds of
+// launches + host round trips of the parallel solver.
+constexpr int kTvParallelMin = 16384;
+size_t DpDoubles(int64_t len) {
   const int64_t ntiles = (len + kTvTile - 1) / kTvTile + 1;
-  return (size_t)(10 * len + 4 * ntiles + 16);
+  return (size_t)(8 * len + 4 * ntiles + 16);
+}
+}  // namespace
+
+// work layout (doubles): v[n] | beta[n] | scratch of the dynamic program | scratch of the
+// parallel solver (whose first part, the active set, persists between calls: warm start)
+size_t Tv1dWorkDoubles(int64_t len) {
+  return (size_t)(2 * len) + DpDoubles(len) + (len >= kTvParallelMin ? Tv1dParallelBytes(len) / 8 + 32 : 0);
 }
 
 void Tv1dProxStep(Ctx* ctx, const ElemSeg& seg, const double* consts, double* u, const double* y_old,
                   double* y_new, double* x, double* work) {
   const int n = seg.len;
   if (n <= 0) return;
-  double* knot = work;
+  double* v = work;
+  double* beta = v + n;
+  double* knot = beta + n;
   double* slope = knot + 2 * (size_t)n;
   double* icpt = slope + 2 * (size_t)n;
   double* lo = icpt + 2 * (size_t)n;
   double* hi = lo + n;
-  double* v = hi + n;
-  double* beta = v + n;
   const int n1 = n - 1;
   const int ntiles = (n1 + kTvTile - 1) / kTvTile;
-  double* tile_in = beta + n;
+  double* tile_in = hi + n;
   Clamp* tiles = reinterpret_cast<Clamp*>(tile_in + ntiles + 1);
+  char* par = reinterpret_cast<char*>(work + 2 * (size_t)n + DpDoubles(n));
+  par += (256 - (reinterpret_cast<uintptr_t>(par) & 255)) & 255;
   const int grid = GridFor(n, 256, 2, ctx->sm_count);
   {
     ProfScope ps(ctx, KC_VEC, 32.0 * n);
     TvPreKernel<<<grid, 256, 0, ctx->stream>>>(seg, consts, u, y_old, v);
     ctx->count_launch();
   }
-  {
+  bool solved = false;
+  if (n >= kTvParallelMin && seg.lam > 0.0 && !getenv("EPS_TV_SEQUENTIAL")) {
+    EPS_CHECK(!ctx->capturing, "the parallel TV solver cannot be captured in a CUDA graph");
+    solved = Tv1dParallelSolve(ctx, n, v, seg.lam, beta, par, PinnedFlag(ctx)) >= 0;
+  }
+  if (!solved) {
+    // sequential dynamic program (exact; also the fallback should the rounds above not settle)
     ProfScope ps(ctx, KC_TV, 16.0 * n);
     TvForwardKernel<<<1, 32, 0, ctx->stream>>>(n, v, seg.lam, knot, slope, icpt, lo, hi, beta);
     ctx->count_launch();
