@@ -2,6 +2,8 @@
 #include <cstdarg>
 #include <mutex>
 
+#include <thread>
+
 #include "internal.h"
 
 namespace eps {
@@ -34,6 +36,7 @@ Ctx::~Ctx() {
   red_partials.release();
   red_counter.release();
   if (h_flag) cudaFreeHost(h_flag);
+  delete staging;
   if (own_stream && stream) cudaStreamDestroy(stream);
 }
 
@@ -64,6 +67,90 @@ ReduceScratch GetReduceScratch(Ctx* ctx) {
     ctx->red_counter.zero();
   }
   return ReduceScratch{ctx->red_partials.p, ctx->red_counter.p};
+}
+
+// ---- staged upload ---------------------------------------------------------------------
+// cudaMemcpyAsync from pageable memory runs at a few GB/s (one driver thread copies through
+// a small bounce buffer).  The wire format hands us pageable bytes (Python strings in the
+// reference, solvemodule.cc:58-72), so for large buffers kWorkers host threads copy
+// interleaved chunks into their own pinned buffers and DMA them on their own streams.
+namespace {
+constexpr int kWorkers = 4;
+constexpr int kSlots = 2;
+constexpr size_t kChunk = (size_t)8 << 20;
+constexpr size_t kStagedMin = (size_t)32 << 20;
+}  // namespace
+
+struct Ctx::Staging {
+  char* buf[kWorkers][kSlots] = {};
+  cudaStream_t stream[kWorkers] = {};
+  cudaEvent_t ev[kWorkers][kSlots] = {};
+  cudaEvent_t done[kWorkers] = {};
+  cudaEvent_t start = nullptr;
+  ~Staging() {
+    for (int w = 0; w < kWorkers; w++) {
+      for (int s = 0; s < kSlots; s++) {
+        if (buf[w][s]) cudaFreeHost(buf[w][s]);
+        if (ev[w][s]) cudaEventDestroy(ev[w][s]);
+      }
+      if (done[w]) cudaEventDestroy(done[w]);
+      if (stream[w]) cudaStreamDestroy(stream[w]);
+    }
+    if (start) cudaEventDestroy(start);
+  }
+};
+
+void UploadBytes(Ctx* ctx, void* dst, const void* src, size_t bytes) {
+  if (bytes == 0) return;
+  if (bytes < kStagedMin || ctx->capturing) {
+    CUDA_CHECK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    return;
+  }
+  if (!ctx->staging) {
+    auto* st = new Ctx::Staging();
+    ctx->staging = st;
+    for (int w = 0; w < kWorkers; w++) {
+      CUDA_CHECK(cudaStreamCreateWithFlags(&st->stream[w], cudaStreamNonBlocking));
+      CUDA_CHECK(cudaEventCreateWithFlags(&st->done[w], cudaEventDisableTiming));
+      for (int s = 0; s < kSlots; s++) {
+        CUDA_CHECK(cudaHostAlloc(&st->buf[w][s], kChunk, cudaHostAllocDefault));
+        CUDA_CHECK(cudaEventCreateWithFlags(&st->ev[w][s], cudaEventDisableTiming));
+      }
+    }
+    CUDA_CHECK(cudaEventCreateWithFlags(&st->start, cudaEventDisableTiming));
+  }
+  Ctx::Staging* st = ctx->staging;
+  // the destination may still be in use by earlier work on the context stream
+  CUDA_CHECK(cudaEventRecord(st->start, ctx->stream));
+  const size_t nchunks = (bytes + kChunk - 1) / kChunk;
+  const int device = ctx->device;
+  cudaError_t errs[kWorkers];
+  std::vector<std::thread> threads;
+  for (int w = 0; w < kWorkers; w++) {
+    errs[w] = cudaSuccess;
+    threads.emplace_back([=, &errs]() {
+      cudaError_t e = cudaSetDevice(device);
+      if (e == cudaSuccess) e = cudaStreamWaitEvent(st->stream[w], st->start, 0);
+      int slot = 0;
+      for (size_t c = w; c < nchunks && e == cudaSuccess; c += kWorkers, slot ^= 1) {
+        const size_t off = c * kChunk;
+        const size_t len = std::min(kChunk, bytes - off);
+        e = cudaEventSynchronize(st->ev[w][slot]);  // the DMA that last used this slot is done
+        if (e != cudaSuccess) break;
+        memcpy(st->buf[w][slot], static_cast<const char*>(src) + off, len);
+        e = cudaMemcpyAsync(static_cast<char*>(dst) + off, st->buf[w][slot], len, cudaMemcpyHostToDevice,
+                            st->stream[w]);
+        if (e == cudaSuccess) e = cudaEventRecord(st->ev[w][slot], st->stream[w]);
+      }
+      if (e == cudaSuccess) e = cudaEventRecord(st->done[w], st->stream[w]);
+      errs[w] = e;
+    });
+  }
+  for (auto& t : threads) t.join();
+  for (int w = 0; w < kWorkers; w++) {
+    CUDA_CHECK(errs[w]);
+    CUDA_CHECK(cudaStreamWaitEvent(ctx->stream, st->done[w], 0));
+  }
 }
 
 int* PinnedFlag(Ctx* ctx) {

@@ -42,6 +42,9 @@ void SetLastError(const std::string& msg);
   } while (0)
 
 struct Ctx;
+// Host (pageable) -> device copy ordered on the context stream; large buffers go through
+// pinned staging buffers filled by several host threads (ctx.cu).
+void UploadBytes(Ctx* ctx, void* dst, const void* src, size_t bytes);
 
 // ---- device memory ----------------------------------------------------------------
 template <typename T>
@@ -72,7 +75,7 @@ struct DevBuf {
   }
   void zero() { if (n) CUDA_CHECK(cudaMemsetAsync(p, 0, n * sizeof(T), ctx->stream)); }
   void upload(const T* host, size_t count) {
-    if (count) CUDA_CHECK(cudaMemcpyAsync(p, host, count * sizeof(T), cudaMemcpyHostToDevice, ctx->stream));
+    if (count) UploadBytes(ctx, p, host, count * sizeof(T));
   }
   void download(T* host, size_t count) const {
     if (count) CUDA_CHECK(cudaMemcpyAsync(host, p, count * sizeof(T), cudaMemcpyDeviceToHost, ctx->stream));
@@ -113,6 +116,8 @@ struct Ctx {
   DevBuf<unsigned int> red_counter;
   int64_t scratch_generation = 0;
   int* h_flag = nullptr;
+  struct Staging;              // pinned upload staging (ctx.cu)
+  Staging* staging = nullptr;
   ~Ctx();
   void count_launch(int n = 1) {
     if (capturing) capture_launches += n; else launches += n;

@@ -132,7 +132,8 @@ double* SplitScratch(Ctx* ctx, size_t count) { return GrowScratch(ctx, &ctx->spl
 void DenseGemv(Ctx* ctx, const double* A, int lda, int m, int n, bool trans, double alpha,
                const double* x, double beta, double* y, int tri) {
   if (m == 0 || n == 0) return;
-  const int target = ctx->sm_count * 4;
+  // enough CTAs for ~6+ waves (4 resident per SM): a grid of 2.1 waves runs as 3 and loses 30 %
+  const int target = ctx->sm_count * 24;
   const double bytes = (tri ? 4.0 : 8.0) * m * n + 8.0 * m + 8.0 * n;
   if (!trans) {
     const int rb = (m + kGemvBlock * kGemvNRows - 1) / (kGemvBlock * kGemvNRows);
