@@ -71,46 +71,82 @@ GemvNKernel(const double* __restrict__ A, int64_t lda, int m, int n, int cols_pe
   }
 }
 
-// y_part[s][j] = sum_{i in split s} A[i,j] x[i]  for a group of CG columns per CTA.
+// y_part[s][j] = sum_{i in split s} A[i,j] x[i]  for groups of kGemvTCols columns.
+// Work items (column group, row split) are walked with a grid-stride loop by a grid sized to
+// the resident CTA slots, so there is no partial last wave (a 3.4-wave grid measured 75 % of
+// the copy peak, profiles/r01_ncu_full_GemvTKernel_before.csv).  VEC2: 128-bit loads, two
+// consecutive rows per thread (needs even lda / row offsets and 16-byte aligned A, x).
 constexpr int kGemvTCols = 8;
-__global__ void __launch_bounds__(kGemvBlock)
-GemvTKernel(const double* __restrict__ A, int64_t lda, int m, int n, int rows_per_split,
-            const double* __restrict__ x, double* __restrict__ out, int64_t out_stride, int tri) {
+template <bool VEC2>
+__global__ void __launch_bounds__(kGemvBlock, 2)
+GemvTKernel(const double* __restrict__ A, int64_t lda, int m, int n, int rows_per_split, int n_groups,
+            int n_items, const double* __restrict__ x, double* __restrict__ out, int64_t out_stride,
+            int tri) {
   __shared__ double smem[kGemvTCols * 32];
-  const int jg = blockIdx.x * kGemvTCols;
-  const int split = blockIdx.y;
-  int i0 = split * rows_per_split;
-  const int i1 = min(m, i0 + rows_per_split);
-  if (tri) i0 = max(i0, jg);  // lower-triangular A: rows above the column group are zero
-  double acc[kGemvTCols];
+  for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+    const int jg = (item % n_groups) * kGemvTCols;
+    const int split = item / n_groups;
+    int i0 = split * rows_per_split;
+    const int i1 = min(m, i0 + rows_per_split);
+    if (tri) i0 = max(i0, jg & ~1);  // lower-triangular A: rows above the column group are zero
+    double acc[kGemvTCols];
 #pragma unroll
-  for (int c = 0; c < kGemvTCols; c++) acc[c] = 0.0;
-  const int ncol = min(kGemvTCols, n - jg);
-  if (ncol == kGemvTCols) {
-    for (int i = i0 + threadIdx.x; i < i1; i += kGemvBlock * 2) {
-      const int i2 = i + kGemvBlock;
-      const bool v2 = i2 < i1;
-      double a0[kGemvTCols], a1[kGemvTCols];
-      const double xv0 = x[i];
-      const double xv1 = v2 ? x[i2] : 0.0;
+    for (int c = 0; c < kGemvTCols; c++) acc[c] = 0.0;
+    const int ncol = min(kGemvTCols, n - jg);
+    if (ncol == kGemvTCols && VEC2) {
+      // rows i, i+1 (one double2) and i+512, i+513 per pass: 16 x 16 B in flight per thread
+      int i = i0 + 2 * threadIdx.x;
+      for (; i + 2 * kGemvBlock + 1 < i1; i += 4 * kGemvBlock) {
+        const int i2 = i + 2 * kGemvBlock;
+        double2 a0[kGemvTCols], a1[kGemvTCols];
 #pragma unroll
-      for (int c = 0; c < kGemvTCols; c++) {
-        const double* col = A + (int64_t)(jg + c) * lda;
-        a0[c] = LdStream(col + i);
-        a1[c] = v2 ? LdStream(col + i2) : 0.0;
+        for (int c = 0; c < kGemvTCols; c++) {
+          const double* col = A + (int64_t)(jg + c) * lda;
+          a0[c] = LdStream2(col + i);
+          a1[c] = LdStream2(col + i2);
+        }
+        const double2 x0 = *reinterpret_cast<const double2*>(x + i);
+        const double2 x1 = *reinterpret_cast<const double2*>(x + i2);
+#pragma unroll
+        for (int c = 0; c < kGemvTCols; c++)
+          acc[c] += (a0[c].x * x0.x + a0[c].y * x0.y) + (a1[c].x * x1.x + a1[c].y * x1.y);
       }
+      for (; i < i1; i += 2 * kGemvBlock) {  // remainder passes, element-wise guards
+        const bool two = i + 1 < i1;
+        const double xa = x[i], xb = two ? x[i + 1] : 0.0;
 #pragma unroll
-      for (int c = 0; c < kGemvTCols; c++) acc[c] += a0[c] * xv0 + a1[c] * xv1;
+        for (int c = 0; c < kGemvTCols; c++) {
+          const double* col = A + (int64_t)(jg + c) * lda;
+          acc[c] += col[i] * xa + (two ? col[i + 1] * xb : 0.0);
+        }
+      }
+    } else if (ncol == kGemvTCols) {
+      for (int i = i0 + threadIdx.x; i < i1; i += kGemvBlock * 2) {
+        const int i2 = i + kGemvBlock;
+        const bool v2 = i2 < i1;
+        double a0[kGemvTCols], a1[kGemvTCols];
+        const double xv0 = x[i];
+        const double xv1 = v2 ? x[i2] : 0.0;
+#pragma unroll
+        for (int c = 0; c < kGemvTCols; c++) {
+          const double* col = A + (int64_t)(jg + c) * lda;
+          a0[c] = LdStream(col + i);
+          a1[c] = v2 ? LdStream(col + i2) : 0.0;
+        }
+#pragma unroll
+        for (int c = 0; c < kGemvTCols; c++) acc[c] += a0[c] * xv0 + a1[c] * xv1;
+      }
+    } else {
+      for (int i = i0 + threadIdx.x; i < i1; i += kGemvBlock) {
+        const double xv = x[i];
+        for (int c = 0; c < ncol; c++) acc[c] += A[(int64_t)(jg + c) * lda + i] * xv;
+      }
     }
-  } else {
-    for (int i = i0 + threadIdx.x; i < i1; i += kGemvBlock) {
-      const double xv = x[i];
-      for (int c = 0; c < ncol; c++) acc[c] += A[(int64_t)(jg + c) * lda + i] * xv;
+    BlockSum<kGemvTCols>(acc, smem);
+    if (threadIdx.x == 0) {
+      for (int c = 0; c < ncol; c++) out[(int64_t)split * out_stride + jg + c] = acc[c];
     }
-  }
-  BlockSum<kGemvTCols>(acc, smem);
-  if (threadIdx.x == 0) {
-    for (int c = 0; c < ncol; c++) out[(int64_t)split * out_stride + jg + c] = acc[c];
+    __syncthreads();  // smem is reused by the next item
   }
 }
 
@@ -152,13 +188,30 @@ void DenseGemv(Ctx* ctx, const double* A, int lda, int m, int n, bool trans, dou
     ctx->count_launch();
   } else {
     const int cg = (n + kGemvTCols - 1) / kGemvTCols;
-    int splits = std::max(1, std::min((m + 2047) / 2048, target / cg));
+    // items of ~4096 rows x 8 columns (256 KB): small against a CTA's share of the matrix, so
+    // the grid-stride loop balances to a few per cent
+    int splits = std::max(1, (m + 4095) / 4096);
     int rps = (m + splits - 1) / splits;
+    rps = (rps + 1) & ~1;  // even row offsets keep the 128-bit loads aligned
     splits = (m + rps - 1) / rps;
+    const int n_items = cg * splits;
     double* part = SplitScratch(ctx, (size_t)splits * n);
+    const bool vec2 = (lda % 2 == 0) && ((reinterpret_cast<uintptr_t>(A) & 15) == 0) &&
+                      ((reinterpret_cast<uintptr_t>(x) & 15) == 0);
+    static int slots_per_sm[2] = {0, 0};
+    if (!slots_per_sm[vec2]) {
+      int v = 0;
+      if (vec2) CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&v, GemvTKernel<true>, kGemvBlock, 0));
+      else CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&v, GemvTKernel<false>, kGemvBlock, 0));
+      slots_per_sm[vec2] = std::max(1, v);
+    }
+    const int grid = std::min(n_items, ctx->sm_count * slots_per_sm[vec2]);
     {
       ProfScope ps(ctx, KC_GEMV_T, bytes);
-      GemvTKernel<<<dim3(cg, splits), kGemvBlock, 0, ctx->stream>>>(A, lda, m, n, rps, x, part, n, tri);
+      if (vec2)
+        GemvTKernel<true><<<grid, kGemvBlock, 0, ctx->stream>>>(A, lda, m, n, rps, cg, n_items, x, part, n, tri);
+      else
+        GemvTKernel<false><<<grid, kGemvBlock, 0, ctx->stream>>>(A, lda, m, n, rps, cg, n_items, x, part, n, tri);
       ctx->count_launch();
     }
     ProfScope ps(ctx, KC_VEC, 8.0 * splits * n);
