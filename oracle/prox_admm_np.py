@@ -546,3 +546,132 @@ def eval_prox(f, lam: float, v: Dict[str, np.ndarray]) -> Dict[str, np.ndarray]:
     u = np.concatenate([a * np.asarray(v[k], dtype=np.float64).ravel() for k in order])
     x = s.ops[0].apply(u)
     return {k: x[sl].copy() for k, sl in s.cols[0].items()}
+
+
+# ---------------------------------------------------------------------------
+# ProxADMMTwoBlockSolver (src/epsilon/algorithms/prox_admm_two_block.cc)
+# ---------------------------------------------------------------------------
+
+class ProxADMMTwoBlock:
+    """Consensus form: x_i = prox_{f_i}(z - u) for all i, z = projection of x + u onto
+    {H z + b = 0} (ZeroProx, prox/zero.cc:10-36), u += x - z  (prox_admm_two_block.cc:96-133).
+    Every prox sees A = sqrt(rho) * I on its own variables (:66-71)."""
+
+    def __init__(self, problem, params: Optional[dict] = None):
+        self.problem = problem
+        self.params = dict(DEFAULT_PARAMS)
+        self.params.update(params or {})
+        assert self.params["rho"] == 1.0
+        p = problem
+        sizes = p.variables()
+        self.N = len(p.prox)
+        # flat layout: variables grouped by owning prox function, ids sorted inside a group
+        self.cols: Dict[str, slice] = {}
+        off = 0
+        self.prox_cols = []
+        for i in range(self.N):
+            loc = {}
+            start = off
+            for v in p.prox_variables(i):
+                self.cols[v] = slice(off, off + sizes[v])
+                loc[v] = slice(off - start, off - start + sizes[v])
+                off += sizes[v]
+            self.prox_cols.append((start, off, loc))
+        self.n_all = off
+        # InitConstraints (:21-49): H over the constraint variables, z = 0 for them
+        rows, bs = [], []
+        in_constraint = set()
+        for c in p.constraints:
+            Hc, bc = _affine_blocks(c, self.cols, self.n_all)
+            rows.append(Hc)
+            bs.append(bc)
+            for t in c.terms:
+                if hasattr(t.operand, "var_id"):
+                    in_constraint.add(t.operand.var_id)
+        self.H = sp.vstack(rows, format="csr") if rows else sp.csr_matrix((0, self.n_all))
+        self.hb = np.concatenate(bs) if bs else np.zeros(0)
+        self.m = self.H.shape[0]
+        self.n = int(sum(sizes[v] for v in in_constraint))
+        self.mask = np.zeros(self.n_all)
+        for v in in_constraint:
+            self.mask[self.cols[v]] = 1.0
+        if self.m:
+            HHt = (self.H @ self.H.T).tocsc()
+            d = _diag_if_diagonal(HHt)
+            self.hh_diag = d
+            self.hh_chol = None if d is not None else sla.cho_factor(HHt.toarray(), lower=True)
+        # InitProxOperators (:51-84)
+        self.ops = []
+        for i, f in enumerate(p.prox):
+            start, end, loc = self.prox_cols[i]
+            Hs, gs = [], []
+            for a in f.args:
+                Ha, ga = _affine_blocks(a, loc, end - start)
+                Hs.append(Ha)
+                gs.append(ga)
+            H = sp.vstack(Hs, format="csr") if Hs else sp.csr_matrix((0, end - start))
+            g = np.concatenate(gs) if gs else np.zeros(0)
+            self.ops.append(_make_operator(f, H, g, sp.identity(end - start, format="csr")))
+        self.reset()
+
+    def reset(self):
+        self.z = np.zeros(self.n_all)
+        self.z_prev = np.zeros(self.n_all)
+        self.u = np.zeros(self.n_all)
+        self.x = np.zeros(self.n_all)
+        self.iter = 0
+        self.status = {"state": 0, "num_iterations": 0}
+
+    def _project(self, v):
+        """ZeroProx::Apply with A = I: v - H'(HH')^-1 (Hv + b), restricted to H's columns."""
+        if self.m == 0:
+            return v * self.mask
+        r = np.asarray(self.H @ v).ravel() + self.hb
+        y = r / self.hh_diag if self.hh_diag is not None else sla.cho_solve(self.hh_chol, r)
+        return (v - np.asarray(self.H.T @ y).ravel()) * self.mask
+
+    def iteration(self):
+        self.z_prev = self.z.copy()
+        zu = self.z - self.u
+        x = np.zeros(self.n_all)
+        for i in range(self.N):
+            start, end, _ = self.prox_cols[i]
+            x[start:end] = self.ops[i].apply(zu[start:end])
+        self.x = x
+        self.z = self._project(self.x + self.u)
+        self.u = self.u + (self.x - self.z)
+
+    def compute_residuals(self):
+        """prox_admm_two_block.cc:135-156 (both tolerances use sqrt(n_))."""
+        abs_tol, rel_tol, rho = self.params["abs_tol"], self.params["rel_tol"], self.params["rho"]
+        nrm = lambda a: float(np.sqrt(np.sum(a * a)))
+        st = {"r_norm": nrm(self.x - self.z), "s_norm": rho * nrm(self.z - self.z_prev),
+              "epsilon_primal": abs_tol * np.sqrt(self.n) + rel_tol * max(nrm(self.x), nrm(self.z)),
+              "epsilon_dual": abs_tol * np.sqrt(self.n) + rel_tol * rho * nrm(self.u)}
+        ok = st["r_norm"] <= st["epsilon_primal"] and st["s_norm"] <= st["epsilon_dual"]
+        st["state"] = STATE_OPTIMAL if ok else STATE_RUNNING
+        st["num_iterations"] = self.iter
+        self.status = st
+        return st
+
+    def solution(self):
+        return {v: self.x[sl].copy() for v, sl in self.cols.items()}
+
+    def solve(self):
+        self.reset()
+        trace = []
+        max_it, epoch = int(self.params["max_iterations"]), int(self.params["epoch_iterations"])
+        self.iter = 0
+        while self.iter < max_it:
+            self.iteration()
+            if self.iter % epoch == 0:
+                trace.append(dict(self.compute_residuals()))
+                if self.status["state"] == STATE_OPTIMAL:
+                    break
+            self.iter += 1
+        if self.iter == max_it:
+            self.compute_residuals()
+            self.status["state"] = STATE_MAX_ITERATIONS
+            trace.append(dict(self.status))
+        return {"status": dict(self.status), "trace": trace, "x": self.solution(),
+                "m": self.m, "n": self.n, "N": self.N}

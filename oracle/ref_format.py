@@ -120,7 +120,13 @@ def write_reference_problem(problem: ProxAffineProblem, out_dir: str,
         f.write("\n".join(parts) + "\n")
     with open(os.path.join(out_dir, "params.pbtxt"), "w") as f:
         for k, v in (params or {}).items():
-            f.write("%s: %s\n" % (k, str(v).lower() if isinstance(v, bool) else repr(v)))
+            if isinstance(v, bool):
+                txt = str(v).lower()
+            elif isinstance(v, str):
+                txt = v            # enum identifier (e.g. solver: PROX_ADMM_TWO_BLOCK)
+            else:
+                txt = repr(v)
+            f.write("%s: %s\n" % (k, txt))
 
 
 def write_reference_prox(f: ProxFunction, lam: float, v: Dict[str, np.ndarray], out_dir: str) -> None:

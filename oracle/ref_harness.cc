@@ -39,6 +39,7 @@
 
 #include "epsilon/affine/affine.h"
 #include "epsilon/algorithms/prox_admm.h"
+#include "epsilon/algorithms/prox_admm_two_block.h"
 #include "epsilon/expression.pb.h"
 #include "epsilon/expression/expression_util.h"
 #include "epsilon/prox/prox.h"
@@ -188,8 +189,17 @@ int RunSolve(const std::string& dir, bool trace, int dump_iter) {
 
   std::string out = dir + (trace ? "/out_trace" : "/out_solve");
   MakeDir(out);
-  ProxADMMSolver solver(problem, data, params);
-  if (trace) return ProxADMMSolverTest::Trace(&solver, params, out, dump_iter);
+  // CreateSolver of python/epopt/solvemodule.cc:74-87
+  std::unique_ptr<Solver> any;
+  if (params.solver() == SolverParams::PROX_ADMM_TWO_BLOCK) {
+    CHECK(!trace) << "stepping is only possible for ProxADMMSolver (friend class)";
+    any.reset(new ProxADMMTwoBlockSolver(problem, data, params));
+  } else {
+    ProxADMMSolver* s = new ProxADMMSolver(problem, data, params);
+    any.reset(s);
+    if (trace) return ProxADMMSolverTest::Trace(s, params, out, dump_iter);
+  }
+  Solver& solver = *any;
 
   double t0 = Now();
   BlockVector x = solver.Solve();

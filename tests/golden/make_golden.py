@@ -50,6 +50,18 @@ SOLVE_CASES = {
 }
 
 
+# ProxADMMTwoBlockSolver (SolverParams.solver = PROX_ADMM_TWO_BLOCK, solve_test.py:59)
+TWO_BLOCK_CASES = {
+    "tb_lasso_dense_100x500": ("lasso", (100, 500), {}, {"max_iterations": 500}),
+    "tb_lasso_sparse_4000x400": ("lasso", (4000, 400), {"density": 0.02, "seed": 3}, {"max_iterations": 500}),
+    "tb_logreg_l1_2000x200": ("logreg_l1", (2000, 200), {"density": 0.05, "seed": 4}, {"max_iterations": 300}),
+    "tb_hinge_l2_1500x100": ("hinge_l2", (1500, 100), {"seed": 5}, {"max_iterations": 300}),
+    "tb_group_lasso_400x10x12": ("group_lasso", (400, 10, 12), {"seed": 6}, {"max_iterations": 300}),
+    "tb_tv_1d_5000": ("tv_1d", (5000,), {"seed": 7}, {"max_iterations": 300}),
+    "tb_lasso_maxiter_13": ("lasso", (80, 120), {"seed": 12}, {"max_iterations": 13}),
+}
+
+
 def problem_digest(prob) -> str:
     """SHA-256 over every constant and matrix buffer of the problem, in traversal order."""
     h = hashlib.sha256()
@@ -81,7 +93,7 @@ def problem_digest(prob) -> str:
 
 
 def make_problem(name):
-    gen, args, kw, params = SOLVE_CASES[name]
+    gen, args, kw, params = (TWO_BLOCK_CASES if name.startswith("tb_") else SOLVE_CASES)[name]
     prob, info = getattr(problems, gen)(*args, **kw)
     return prob, info, params
 
@@ -153,6 +165,32 @@ def main():
                                 "num_iterations": int(r["status"]["num_iterations"]),
                                 "state": int(r["status"]["state"])}
         print(name, index["solve"][name])
+    # two-block solver: the reference offers no stepping hook for it, so the per-epoch
+    # residuals come from stock Solve() runs cut at max_iterations = k+1 (the final
+    # ComputeResiduals of such a run sees exactly the state of epoch k, prox_admm_two_block.cc:123-126)
+    index["two_block"] = {}
+    for name in TWO_BLOCK_CASES:
+        prob, info, params = make_problem(name)
+        p = dict(params, solver="PROX_ADMM_TWO_BLOCK")
+        final = ref_runner.run(prob, params=p, mode="solve")
+        fs = final["status"]
+        rows = []
+        last_epoch = fs["num_iterations"] if fs["state"] == 3 else (fs["num_iterations"] - 1) // 10 * 10
+        for k in range(0, last_epoch + 1, 10):
+            if fs["state"] == 3 and k == fs["num_iterations"]:
+                break
+            cut = ref_runner.run(prob, params=dict(p, max_iterations=k + 1), mode="solve")["status"]
+            assert cut["num_iterations"] == k + 1 and cut["state"] == 4
+            rows.append([2, k] + [cut[x] for x in TRACE_KEYS[2:]])
+        rows.append([fs[x] for x in TRACE_KEYS])
+        v = info["solution_var"]
+        np.savez_compressed(os.path.join(HERE, name + ".npz"), trace=np.array(rows, dtype=np.float64),
+                            status=np.array([fs[x] for x in TRACE_KEYS], dtype=np.float64),
+                            x=final["x"][v].astype(np.float64),
+                            objective=np.float64(info["objective"](final["x"])))
+        index["two_block"][name] = {"digest": problem_digest(prob), "solution_var": v, "epochs": len(rows),
+                                    "num_iterations": int(fs["num_iterations"]), "state": int(fs["state"])}
+        print(name, index["two_block"][name])
     for name, (f, lam, v) in prox_cases().items():
         x = ref_runner.run_prox(f, lam, v)
         np.savez_compressed(os.path.join(HERE, "prox_" + name + ".npz"), lam=np.float64(lam),

@@ -112,3 +112,19 @@ def test_scaled_zone_branches():
     assert np.array_equal(onp.scaled_zone(v, lam, 1.0, 1.0, 0.0), [-2, 0, 0, 0, 0, 0, 2])      # soft threshold
     assert np.array_equal(onp.scaled_zone(v, lam, 1.0, 0.0, 0.0), [-3, -1, -0.5, 0, 0, 0, 2])  # hinge
     assert np.array_equal(onp.scaled_zone(v, lam, 1.0, 1.0, 0.5), [-2, -0.5, -0.5, 0, 0.5, 0.5, 2])
+
+
+@pytest.mark.parametrize("name", sorted(INDEX.get("two_block", {})))
+def test_two_block_matches_reference(name):
+    """ProxADMMTwoBlockSolver restatement vs the stock reference solver (SolverParams.solver =
+    PROX_ADMM_TWO_BLOCK); per-epoch residuals come from runs cut at max_iterations = k+1."""
+    prob, info, params = make_golden.make_problem(name)
+    assert make_golden.problem_digest(prob) == INDEX["two_block"][name]["digest"]
+    gold = np.load(os.path.join(GOLDEN, name + ".npz"))
+    out = onp.ProxADMMTwoBlock(prob, params).solve()
+    check_trace(out["trace"], gold["trace"], rtol=1e-9)
+    st = dict(zip(TRACE_KEYS, gold["status"]))
+    assert out["status"]["num_iterations"] == int(st["num_iterations"])
+    assert out["status"]["state"] == int(st["state"])
+    x = out["x"][INDEX["two_block"][name]["solution_var"]]
+    assert np.abs(x - gold["x"]).max() <= 1e-9 * max(1.0, np.abs(gold["x"]).max())
