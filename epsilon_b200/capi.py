@@ -42,6 +42,7 @@ class Params(C.Structure):
         ("use_graph", C.c_int32),
         ("profile", C.c_int32),
         ("gram_max_n", C.c_int64),
+        ("solver", C.c_int32),
     ]
 
 

@@ -14,18 +14,9 @@ double WallMs() {
 }
 }  // namespace
 
-// One iteration: prox_admm.cc:135-147.  ybuf[parity] is y (= y_prev during this
-// iteration), ybuf[1-parity] receives the new y.
-void eps_solver::Iteration() {
-  const double* yo = ybuf[parity].p;
-  double* yn = ybuf[1 - parity].p;
-  // u -= b; u -= sum_i y_i                                   (:137-139)
-  if (has_b) VecAxpby(ctx, m_total, 1.0, u.p, -1.0, b.p, u.p);
-  for (auto& stp : stages) {
-    Stage& st = *stp;
-    SegAxpy(ctx, st.pairs.p, st.prefix.p, (int)st.members.size(), st.total, u.p, yo, -1.0, nullptr, 0.0);
-  }
-  // for i: u += y_i; x_i = prox_i(u); y_i = A x_i; u -= y_i   (:141-147)
+// for i: u += y_i; x_i = prox_i(u); y_i = A x_i; u -= y_i   (prox_admm.cc:141-147), stage by
+// stage; yo holds the previous y_i, yn receives the new ones.
+void eps_solver::RunStages(const double* yo, double* yn) {
   for (auto& stp : stages) {
     Stage& st = *stp;
     const int nseg = (int)st.members.size();
@@ -65,7 +56,45 @@ void eps_solver::Iteration() {
       }
     }
   }
+}
+
+// One iteration: prox_admm.cc:135-147.  ybuf[parity] is y (= y_prev during this
+// iteration), ybuf[1-parity] receives the new y.
+void eps_solver::Iteration() {
+  if (two_block) { TwoBlockIteration(); return; }
+  const double* yo = ybuf[parity].p;
+  double* yn = ybuf[1 - parity].p;
+  // u -= b; u -= sum_i y_i                                   (:137-139)
+  if (has_b) VecAxpby(ctx, m_total, 1.0, u.p, -1.0, b.p, u.p);
+  for (auto& stp : stages) {
+    Stage& st = *stp;
+    SegAxpy(ctx, st.pairs.p, st.prefix.p, (int)st.members.size(), st.total, u.p, yo, -1.0, nullptr, 0.0);
+  }
+  RunStages(yo, yn);
   parity = 1 - parity;
+}
+
+// ProxADMMTwoBlockSolver::Solve body (prox_admm_two_block.cc:99-113).  Every prox operator was
+// initialised with A = I on its own variables, laid out exactly like the x arena, so
+// "x_i = prox_i(z - u)" is RunStages on a scratch copy of z - u with zero previous y.
+void eps_solver::TwoBlockIteration() {
+  const double* z = zbuf[zpar].p;
+  double* zn = zbuf[1 - zpar].p;   // becomes z; the old z becomes z_prev
+  VecAxpby(ctx, n_all, 1.0, z, -1.0, ub.p, u.p);                 // zu = z - u          (:102)
+  RunStages(zeros.p, ybuf[0].p);                                  // x = sum_i prox_i(zu) (:103-107)
+  VecAxpby(ctx, n_all, 1.0, x.p, 1.0, ub.p, v_tmp.p);            // v = x + u
+  const double* t = nullptr;
+  if (m_c > 0) {
+    // ZeroProx (prox/zero.cc:10-36) with A = I:  z = v - H'(HH')^-1 (H v + b)
+    Hc.Apply(v_tmp.p, r_m.p);
+    VecAxpby(ctx, m_c, 1.0, r_m.p, 1.0, hb.p, r_m.p);
+    proj->Solve(r_m.p, y_m.p);
+    Hc.ApplyT(y_m.p, diff_m.p);
+    t = diff_m.p;
+  }
+  // z = v - t (restricted to the constraint variables), u += x - z (:111), residual sums
+  TwoBlockDualStep(ctx, n_all, x.p, v_tmp.p, t, has_mask ? cmask.p : nullptr, z, zn, ub.p, resid.p);
+  zpar = 1 - zpar;
 }
 
 void eps_solver::RunIteration() {
@@ -117,6 +146,20 @@ void eps_solver::RunIteration() {
 
 // prox_admm.cc:178-217.  On entry ybuf[parity] = y, ybuf[1-parity] = y_prev.
 void eps_solver::ComputeResiduals() {
+  if (two_block) {
+    // prox_admm_two_block.cc:135-156; the five sums were left in `resid` by the last iteration
+    CUDA_CHECK(cudaMemcpyAsync(h_resid, resid.p, 5 * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+    const double rho = params.rho;
+    status.r_norm = std::sqrt(h_resid[0]);
+    status.s_norm = rho * std::sqrt(h_resid[1]);
+    status.epsilon_primal = params.abs_tol * std::sqrt((double)tb_n) +
+                            params.rel_tol * std::fmax(std::sqrt(h_resid[2]), std::sqrt(h_resid[3]));
+    status.epsilon_dual = params.abs_tol * std::sqrt((double)tb_n) + params.rel_tol * rho * std::sqrt(h_resid[4]);
+    status.state = (status.r_norm <= status.epsilon_primal && status.s_norm <= status.epsilon_dual)
+                       ? EPS_OPTIMAL : EPS_RUNNING;
+    return;
+  }
   const double* yn = ybuf[parity].p;
   const double* yo = ybuf[1 - parity].p;
   double* R = resid.p;  // [0] r^2  [1] s^2  [2] max_i ||A x_i||^2  [3] ||A'u||^2
@@ -203,6 +246,7 @@ void eps_params_default(eps_params* p) {
   p->use_graph = 1;
   p->profile = 0;
   p->gram_max_n = 60000;
+  p->solver = EPS_SOLVER_PROX_ADMM;
 }
 
 int eps_solver_create(eps_problem* p, const eps_params* params, eps_solver** out) {

@@ -67,8 +67,20 @@ struct eps_solver {
   bool graph_ok = false;
   int eager_done[2] = {0, 0};
 
+  // ---- ProxADMMTwoBlockSolver (prox_admm_two_block.cc): consensus form ----
+  bool two_block = false;
+  eps::BlockOp Hc;                       // the constraint matrix H over the x/z layout (m_c x n_all)
+  std::unique_ptr<eps::KktSolver> proj;  // (H H') y = r of the ZeroProx projection (prox/zero.cc)
+  int64_t m_c = 0, n_all = 0, tb_n = 0;  // rows of H; all variables; H.A.n() (constraint variables)
+  bool has_mask = false;
+  eps::DevBuf<double> zbuf[2], ub, zeros, hb, v_tmp, r_m, y_m, cmask;
+  int zpar = 0;                          // zbuf[zpar] = z, zbuf[1 - zpar] = z_prev
+
   ~eps_solver();
   void Init(const eps_problem& p);
+  void InitTwoBlock(const eps_problem& original);
+  void RunStages(const double* yo, double* yn);  // x_i = prox_i(u) for every stage (+ fused dual updates)
+  void TwoBlockIteration();
   void Iteration();          // one ADMM iteration, eager launches
   void RunIteration();       // graph replay when available
   void ComputeResiduals();

@@ -81,7 +81,44 @@ const char* TypeName(int t) {
 
 using namespace eps;
 
-void eps_solver::Init(const eps_problem& p) {
+namespace {
+// Consensus form of ProxADMMTwoBlockSolver (prox_admm_two_block.cc:66-71): every variable of
+// f_i sees the constraint block A(var, var) = sqrt(rho) I.  The synthetic "constraints" are
+// laid out in the order of the x arena (prox by prox, variable ids ascending inside one), so
+// that each f_i touches one contiguous span with A = I.
+eps_problem ConsensusForm(const eps_problem& p) {
+  eps_problem q = p;
+  q.constraints.clear();
+  const int N = (int)p.prox.size();
+  std::vector<int> owner(p.vars.size(), -1);
+  for (int i = 0; i < N; i++)
+    for (const AffineExpr& a : p.prox[i].args)
+      for (const Term& t : a.terms)
+        if (t.var >= 0 && owner[t.var] < 0) owner[t.var] = i;
+  for (int i = 0; i < N; i++) {
+    std::vector<int> vs;
+    for (size_t v = 0; v < p.vars.size(); v++)
+      if (owner[v] == i) vs.push_back((int)v);
+    std::sort(vs.begin(), vs.end(), [&](int a, int b) { return p.vars[a].id < p.vars[b].id; });
+    for (int v : vs) {
+      AffineExpr e;
+      e.rows = p.vars[v].size;
+      Term t;
+      t.var = v;
+      e.terms.push_back(std::move(t));
+      q.constraints.push_back(std::move(e));
+    }
+  }
+  return q;
+}
+}  // namespace
+
+void eps_solver::Init(const eps_problem& original) {
+  two_block = params.solver == EPS_SOLVER_PROX_ADMM_TWO_BLOCK;
+  EPS_CHECK(params.solver == EPS_SOLVER_PROX_ADMM || two_block, "unknown solver %d", params.solver);
+  eps_problem consensus;
+  if (two_block) consensus = ConsensusForm(original);
+  const eps_problem& p = two_block ? consensus : original;
   ctx = p.ctx;
   vars = p.vars;
   N = (int)p.prox.size();
@@ -372,7 +409,8 @@ void eps_solver::Init(const eps_problem& p) {
   CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
   ResetVariables();
 
-  graph_ok = params.use_graph && !params.profile;
+  if (two_block) InitTwoBlock(original);
+  graph_ok = params.use_graph && !params.profile && !two_block;
   for (auto& op : ops)
     if (op.kkt && op.kkt->mode == EPS_KKT_CG) graph_ok = false;  // host-checked inner loop
   for (auto& stp : stages)
@@ -381,12 +419,90 @@ void eps_solver::Init(const eps_problem& p) {
   status.state = EPS_NOT_STARTED;
   status.m = (int32_t)m_total;
   status.n = (int32_t)n_total;
+  if (two_block) { status.m = (int32_t)m_c; status.n = (int32_t)tb_n; }  // H.A.m(), H.A.n()
   status.N = N;
-  description = Format("ProxADMM m=%lld n=%lld N=%d stages=%zu graph=%d\n", (long long)m_total,
-                       (long long)n_total, N, stages.size(), graph_ok ? 1 : 0) + description;
+  description = Format("%s m=%lld n=%lld N=%d stages=%zu graph=%d\n", two_block ? "ProxADMMTwoBlock" : "ProxADMM",
+                       (long long)status.m, (long long)status.n, N, stages.size(), graph_ok ? 1 : 0) + description;
+}
+
+// InitConstraints of the two-block solver (prox_admm_two_block.cc:21-49): H, b over the x/z
+// layout, and the solve object of the ZeroProx projection.
+void eps_solver::InitTwoBlock(const eps_problem& p) {
+  n_all = 0;
+  for (auto& op : ops) {
+    EPS_CHECK(op.span_lo == op.x_off && op.span_len == op.n && (op.n == 0 || op.simple_scalar),
+              "consensus layout: prox spans [%lld,+%lld) vs x offset %lld", (long long)op.span_lo,
+              (long long)op.span_len, (long long)op.x_off);
+    n_all += op.n;
+  }
+  EPS_CHECK(n_all == m_total, "consensus layout: %lld variables vs %lld rows", (long long)n_all, (long long)m_total);
+  std::vector<int64_t> coff(p.constraints.size() + 1, 0);
+  for (size_t c = 0; c < p.constraints.size(); c++) coff[c + 1] = coff[c] + p.constraints[c].rows;
+  m_c = coff.back();
+  Hc.ctx = ctx;
+  Hc.rows = m_c;
+  Hc.cols = n_all;
+  std::vector<double> hb_host(m_c, 0.0), mask_host(n_all, 0.0);
+  tb_n = 0;
+  std::vector<char> seen(vars.size(), 0);
+  for (size_t c = 0; c < p.constraints.size(); c++) {
+    std::vector<double> bc;
+    if (EvalConstants(ctx, p.constraints[c], &bc)) std::copy(bc.begin(), bc.end(), hb_host.begin() + coff[c]);
+    for (const Term& t : p.constraints[c].terms) {
+      if (t.var < 0) continue;
+      EPS_CHECK(var_x_off[t.var] >= 0, "variable %s appears in constraints but in no prox function",
+                vars[t.var].id.c_str());
+      Hc.blks.push_back(TermBlk(ctx, t, p.constraints[c].rows, (int)coff[c], (int)var_x_off[t.var]));
+      if (!seen[t.var]) {
+        seen[t.var] = 1;
+        tb_n += vars[t.var].size;
+        std::fill(mask_host.begin() + var_x_off[t.var], mask_host.begin() + var_x_off[t.var] + vars[t.var].size, 1.0);
+      }
+    }
+  }
+  Hc.Compile();
+  has_mask = tb_n != n_all;
+  const int64_t na = std::max<int64_t>(n_all, 1), mc = std::max<int64_t>(m_c, 1);
+  zbuf[0].alloc(ctx, na); zbuf[1].alloc(ctx, na); ub.alloc(ctx, na); zeros.alloc(ctx, na);
+  v_tmp.alloc(ctx, na); hb.alloc(ctx, mc); r_m.alloc(ctx, mc); y_m.alloc(ctx, mc); cmask.alloc(ctx, na);
+  zeros.zero();
+  hb.upload(hb_host.data(), m_c);
+  cmask.upload(mask_host.data(), n_all);
+  CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+  if (m_c > 0) {
+    // (H H') y = r  ==  KktSolver with "H" := H' (blocks transposed), 2a = 1, no A term
+    auto k = std::make_unique<KktSolver>();
+    k->ctx = ctx;
+    k->mode = params.kkt_mode;
+    k->n = m_c;
+    k->rows_h = n_all;
+    k->rows_a = 0;
+    k->alpha2 = 1.0;
+    k->cg_tol = params.cg_tol;
+    k->cg_max_iter = params.cg_max_iterations;
+    k->gram_max_n = params.gram_max_n;
+    k->H.ctx = ctx; k->H.rows = n_all; k->H.cols = m_c;
+    for (const Blk& b : Hc.blks) {
+      Blk t = b;
+      t.row_off = b.col_off;
+      t.col_off = b.row_off;
+      t.trans = !b.trans;
+      k->H.blks.push_back(t);
+    }
+    k->A.ctx = ctx; k->A.rows = 0; k->A.cols = m_c;
+    k->Init(std::vector<double>(), std::vector<double>());
+    description += Format("two-block projection onto {Hz + b = 0}: H %lld x %lld, %s\n", (long long)m_c,
+                          (long long)n_all, k->description.c_str());
+    proj = std::move(k);
+  }
+  ResetVariables();
 }
 
 void eps_solver::ResetVariables() {
+  if (two_block && ub.n) {
+    zbuf[0].zero(); zbuf[1].zero(); ub.zero(); y_m.zero();
+    zpar = 0;
+  }
   u.zero();
   x.zero();
   ybuf[0].zero();

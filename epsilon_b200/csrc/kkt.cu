@@ -274,6 +274,12 @@ void KktSolver::Init(const std::vector<double>& g_host, const std::vector<double
     else if (a_pos && rows_h > 0 && rows_h < n && rows_h <= gram_max_n && !h_sharded) mode = EPS_KKT_WOODBURY;
     else if (n <= gram_max_n) mode = EPS_KKT_GRAM;
     else mode = EPS_KKT_CG;
+    // the dense Gram of row-overlapping blocks goes through a densified copy: matrix-free
+    // when that copy would not fit
+    if (mode == EPS_KKT_GRAM &&
+        ((alpha2 != 0.0 && !RowDisjoint(H) && (double)H.rows * H.cols >= 2e9) ||
+         (!RowDisjoint(A) && (double)A.rows * A.cols >= 2e9)))
+      mode = EPS_KKT_CG;
   }
 
   if (mode == EPS_KKT_DIAGONAL) {

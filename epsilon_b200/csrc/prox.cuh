@@ -56,6 +56,12 @@ void SegSumSq(Ctx* ctx, const SegPair* pairs_dev, const SegPair* pairs_host, int
 void KktScalarPre(Ctx* ctx, int64_t n, double a, const double* c0, double* u, const double* y_old,
                   double* rhs);
 void KktScalarPost(Ctx* ctx, int64_t n, double a, const double* x, double* u, double* y_new);
+// Two-block consensus ADMM (prox_admm_two_block.cc:111-113,135-146), one pass:
+//   z = mask .* (v - t)   (t = H'y of the projection; mask may be null)
+//   u += x - z
+//   sums[0..4] = ||x - z||^2, ||z - z_prev||^2, ||x||^2, ||z||^2, ||u||^2
+void TwoBlockDualStep(Ctx* ctx, int64_t n, const double* x, const double* v, const double* t,
+                      const double* mask, const double* z_prev, double* z, double* u, double* sums);
 // x = dinv .* rhs
 void KktDiagSolve(Ctx* ctx, int64_t n, const double* dinv, const double* rhs, double* x);
 

@@ -1,6 +1,8 @@
 // Block prox (NORM_2), segment utilities for the ADMM bookkeeping, the elementwise
 // pre/post kernels of the KKT prox, and the 1-D total-variation prox.
 // Compiled with -fmad=false (see prox_elem.cu).
+#include <algorithm>
+
 #include "device.cuh"
 #include "prox.cuh"
 
@@ -200,6 +202,44 @@ void KktScalarPost(Ctx* ctx, int64_t n, double a, const double* x, double* u, do
     y_new[i] = yn;
     u[i] = u[i] - yn;
   });
+}
+
+namespace {
+__global__ void __launch_bounds__(256)
+TwoBlockDualKernel(int64_t n, const double* __restrict__ x, const double* __restrict__ v,
+                   const double* __restrict__ t, const double* __restrict__ mask,
+                   const double* __restrict__ z_prev, double* __restrict__ z, double* __restrict__ u,
+                   double* partials, unsigned* counter, double* sums) {
+  __shared__ double smem[5 * 32];
+  double acc[5] = {0, 0, 0, 0, 0};
+  const int64_t stride = (int64_t)gridDim.x * 256;
+  for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n; i += stride) {
+    double zi = v[i] - (t ? t[i] : 0.0);
+    if (mask) zi *= mask[i];
+    const double xi = x[i];
+    const double d = xi - zi;
+    const double ui = u[i] + d;
+    const double dz = zi - z_prev[i];
+    z[i] = zi;
+    u[i] = ui;
+    acc[0] += d * d;
+    acc[1] += dz * dz;
+    acc[2] += xi * xi;
+    acc[3] += zi * zi;
+    acc[4] += ui * ui;
+  }
+  GridSumFinish<5>(acc, smem, partials, counter, sums, 0);
+}
+}  // namespace
+
+void TwoBlockDualStep(Ctx* ctx, int64_t n, const double* x, const double* v, const double* t,
+                      const double* mask, const double* z_prev, double* z, double* u, double* sums) {
+  if (n <= 0) return;
+  ReduceScratch rs = GetReduceScratch(ctx);
+  const int grid = std::min(512, GridFor(n, 256, 4, ctx->sm_count, 4));
+  ProfScope ps(ctx, KC_VEC, 56.0 * n);
+  TwoBlockDualKernel<<<grid, 256, 0, ctx->stream>>>(n, x, v, t, mask, z_prev, z, u, rs.partials, rs.counter, sums);
+  ctx->count_launch();
 }
 
 void KktDiagSolve(Ctx* ctx, int64_t n, const double* dinv, const double* rhs, double* x) {

@@ -22,10 +22,12 @@ from .problem import (MAP_DENSE, MAP_DIAGONAL, MAP_KRONECKER, MAP_SCALAR, MAP_SP
 STATE_NAMES = {0: "NOT_STARTED", 1: "INITIALIZING", 2: "RUNNING", 3: "OPTIMAL",
                4: "MAX_ITERATIONS_REACHED", 5: "ERROR"}
 KKT_MODES = {"auto": 0, "diagonal": 1, "woodbury": 2, "gram": 3, "cg": 4}
+# SolverParams.Solver (proto/epsilon/solver_params.proto:63-67)
+SOLVERS = {"PROX_ADMM": 0, "PROX_ADMM_TWO_BLOCK": 1, "prox_admm": 0, "prox_admm_two_block": 1}
 
 # SolverParams defaults (proto/epsilon/solver_params.proto:4-71)
 PARAM_FIELDS = {"max_iterations", "rho", "abs_tol", "rel_tol", "epoch_iterations", "warm_start",
-                "kkt_mode", "cg_tol", "cg_max_iterations", "use_graph", "profile", "gram_max_n"}
+                "kkt_mode", "cg_tol", "cg_max_iterations", "use_graph", "profile", "gram_max_n", "solver"}
 
 
 class Context:
@@ -229,6 +231,8 @@ def make_params(lib, **kw) -> capi.Params:
             raise TypeError("unknown solver parameter %r" % k)
         if k == "kkt_mode" and isinstance(v, str):
             v = KKT_MODES[v]
+        if k == "solver" and isinstance(v, str):
+            v = SOLVERS[v]
         setattr(p, k, int(v) if isinstance(v, bool) else v)
     return p
 

@@ -62,6 +62,11 @@ enum eps_state {
   EPS_ERROR = 5
 };
 
+/* SolverParams.Solver, proto/epsilon/solver_params.proto:63-67 (same numeric values).
+ * PROX_ADMM           = ProxADMMSolver          (src/epsilon/algorithms/prox_admm.cc)
+ * PROX_ADMM_TWO_BLOCK = ProxADMMTwoBlockSolver  (src/epsilon/algorithms/prox_admm_two_block.cc) */
+enum eps_solver_kind { EPS_SOLVER_PROX_ADMM = 0, EPS_SOLVER_PROX_ADMM_TWO_BLOCK = 1 };
+
 /* How the linear-equality (KKT) prox of SumSquare/Affine/Constant is solved.  The
  * reference always eliminates blocks with BlockCholesky in the order NextKey picks
  * (src/epsilon/vector/block_cholesky.cc:51-64,119-133); AUTO reproduces that choice
@@ -170,6 +175,7 @@ typedef struct eps_params {
   int32_t use_graph;        /* capture the per-iteration kernel sequence in a CUDA graph */
   int32_t profile;          /* bracket kernel classes with CUDA events (disables graphs) */
   int64_t gram_max_n;       /* largest n factored densely in AUTO mode (60000) */
+  int32_t solver;           /* eps_solver_kind: SolverParams.solver (solver_params.proto:63-67) */
 } eps_params;
 void eps_params_default(eps_params* p);
 

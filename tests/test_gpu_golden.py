@@ -194,3 +194,34 @@ def test_unsupported_structure_is_an_error(ctx):
     f = ProxFunction("NORM_1", args=[Affine(4, [Term(x, LinearMapSpec.Dense(rng.standard_normal((4, 5))))])])
     with pytest.raises(EpsError):
         eval_prox(f, 1.0, {"x": rng.standard_normal(5)}, ctx=ctx)
+
+
+@pytest.mark.parametrize("name", sorted(INDEX.get("two_block", {})))
+def test_two_block_matches_reference_golden(ctx, name):
+    """ProxADMMTwoBlockSolver (SolverParams.solver = PROX_ADMM_TWO_BLOCK) on the device vs the
+    stock reference solver: identical iteration counts, per-epoch residuals, solution."""
+    prob, info, params = make_golden.make_problem(name)
+    if make_golden.problem_digest(prob) == INDEX["two_block"][name]["digest"]:
+        gold = dict(np.load(os.path.join(GOLDEN, name + ".npz")))
+    else:
+        o = onp.ProxADMMTwoBlock(prob, params).solve()
+        gold = {"trace": np.array([[t[k] for k in TRACE_KEYS] for t in o["trace"]], dtype=np.float64),
+                "status": np.array([o["status"][k] for k in TRACE_KEYS], dtype=np.float64),
+                "x": o["x"][INDEX["two_block"][name]["solution_var"]],
+                "objective": np.float64(info["objective"](o["x"]))}
+    with ProxADMMSolver(prob, dict(params, solver="PROX_ADMM_TWO_BLOCK"), ctx=ctx) as s:
+        x = s.solve()
+        st = s.status.as_dict()
+        trace = list(s.trace)
+        desc = s.describe()
+    assert len(trace) == gold["trace"].shape[0], (len(trace), gold["trace"].shape, desc)
+    for t, g in zip(trace, gold["trace"]):
+        gd = dict(zip(TRACE_KEYS, g))
+        assert t["num_iterations"] == int(gd["num_iterations"]) and t["state"] == int(gd["state"]), (t, gd, desc)
+        for k in TRACE_KEYS[2:]:
+            assert t[k] == pytest.approx(gd[k], rel=1e-8, abs=1e-12), (k, t, gd, desc)
+    gst = dict(zip(TRACE_KEYS, gold["status"]))
+    assert st["num_iterations"] == int(gst["num_iterations"]) and st["state"] == int(gst["state"])
+    v = INDEX["two_block"][name]["solution_var"]
+    assert np.abs(x[v] - gold["x"]).max() <= 1e-7 * max(1.0, np.abs(gold["x"]).max())
+    assert info["objective"](x) == pytest.approx(float(gold["objective"]), rel=1e-6)
