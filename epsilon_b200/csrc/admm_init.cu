@@ -55,7 +55,9 @@ bool EvalConstants(Ctx* ctx, const AffineExpr& e, std::vector<double>* out) {
 bool IsKktType(int t) { return t == EPS_PROX_SUM_SQUARE || t == EPS_PROX_AFFINE || t == EPS_PROX_CONSTANT; }
 bool IsElemType(int t) {
   return t == EPS_PROX_NORM_1 || t == EPS_PROX_SUM_HINGE || t == EPS_PROX_SUM_DEADZONE ||
-         t == EPS_PROX_SUM_QUANTILE || t == EPS_PROX_NON_NEGATIVE || t == EPS_PROX_SUM_LOGISTIC;
+         t == EPS_PROX_SUM_QUANTILE || t == EPS_PROX_NON_NEGATIVE || t == EPS_PROX_SUM_LOGISTIC ||
+         t == EPS_PROX_SUM_EXP || t == EPS_PROX_SUM_INV_POS || t == EPS_PROX_SUM_NEG_ENTR ||
+         t == EPS_PROX_SUM_NEG_LOG;
 }
 
 const char* TypeName(int t) {
@@ -69,6 +71,10 @@ const char* TypeName(int t) {
     case EPS_PROX_SUM_DEADZONE: return "SUM_DEADZONE";
     case EPS_PROX_SUM_HINGE: return "SUM_HINGE";
     case EPS_PROX_SUM_LOGISTIC: return "SUM_LOGISTIC";
+    case EPS_PROX_SUM_EXP: return "SUM_EXP";
+    case EPS_PROX_SUM_INV_POS: return "SUM_INV_POS";
+    case EPS_PROX_SUM_NEG_ENTR: return "SUM_NEG_ENTR";
+    case EPS_PROX_SUM_NEG_LOG: return "SUM_NEG_LOG";
     case EPS_PROX_SUM_QUANTILE: return "SUM_QUANTILE";
     case EPS_PROX_NORM_2: return "NORM_2";
     case EPS_PROX_TOTAL_VARIATION_1D: return "TOTAL_VARIATION_1D";

@@ -73,6 +73,64 @@ __device__ __forceinline__ double LogisticProx(double v, double lam, bool active
   return x;
 }
 
+// The other ElemwiseSmoothFunction operators of the reference (NewtonProx, newton.cc:47-107):
+//   SUM_EXP      f = exp(x)         sum_exp.cc:10-36
+//   SUM_NEG_ENTR f = x log x        sum_neg_entr.cc:10-42   (proj_feasible: x >= 1e-6)
+//   SUM_INV_POS  f = 1/x            sum_inv_pos.cc:10-41    (proj_feasible: x >= 1e-6)
+// Same per-element damped Newton as LogisticProx: solve x - v + lam f'(x) = 0.
+template <int TYPE>
+struct Smooth {
+  static __device__ __forceinline__ double grad(double x) {
+    if (TYPE == EPS_PROX_SUM_EXP) return exp(x);
+    if (TYPE == EPS_PROX_SUM_NEG_ENTR) return 1.0 + log(x);
+    return -1.0 / (x * x);
+  }
+  static __device__ __forceinline__ double hess(double x) {
+    if (TYPE == EPS_PROX_SUM_EXP) return exp(x);
+    if (TYPE == EPS_PROX_SUM_NEG_ENTR) return 1.0 / x;
+    return 2.0 / (x * x * x);
+  }
+  static __device__ __forceinline__ double proj(double x) {
+    return TYPE == EPS_PROX_SUM_EXP ? x : fmax(x, 1e-6);
+  }
+};
+
+template <int TYPE>
+__device__ __forceinline__ double NewtonProxElem(double v, double lam, bool active) {
+  double x = Smooth<TYPE>::proj(v);
+  // exp overflows at the reference's starting point x = v for large v (it then returns NaN);
+  // start right of the root but where exp is finite: x + lam e^x = v  =>  x <= log(v/lam)
+  if (TYPE == EPS_PROX_SUM_EXP && lam > 0.0 && v > 1.0) x = fmin(v, log(v / lam) + 1.0);
+  double g = x - v + lam * Smooth<TYPE>::grad(x);
+  bool done = !active || lam == 0.0;
+  for (int it = 0; it < 100; it++) {
+    if (__all_sync(kFull, done)) break;
+    if (!done) {
+      const double dx = g / (1.0 + lam * Smooth<TYPE>::hess(x));
+      double theta = 1.0;
+      bool moved = false;
+      while (theta > 1e-12) {
+        const double nx = Smooth<TYPE>::proj(x - theta * dx);
+        const double ng = nx - v + lam * Smooth<TYPE>::grad(nx);
+        if (fabs(ng) <= (1.0 - 0.001 * theta) * fabs(g)) {
+          moved = nx != x;
+          x = nx; g = ng;
+          break;
+        }
+        theta *= 0.5;
+      }
+      if (!moved || fabs(g) <= 2.3e-16 * fmax(1.0, fmax(fabs(v), fabs(x)))) done = true;
+    }
+  }
+  return x;
+}
+
+// SumNegLogProx, closed form (sum_neg_log.cc:10-26): root of x - v - lam/x = 0, x > 0
+__device__ __forceinline__ double NegLogProx(double v, double lam) {
+  if (v >= 0) return (v + sqrt(v * v + 4 * lam)) / 2;
+  return 2 * lam / (-v + sqrt(v * v + 4 * lam));
+}
+
 template <int TYPE>
 __global__ void __launch_bounds__(kBlock)
 ElemProxKernel(const ElemSeg* __restrict__ segs, const int64_t* __restrict__ prefix, int nseg,
@@ -99,6 +157,10 @@ ElemProxKernel(const ElemSeg* __restrict__ segs, const int64_t* __restrict__ pre
       }
       if (TYPE == EPS_PROX_SUM_LOGISTIC) {
         xo = LogisticProx(v, lam, active);  // warp-cooperative: every lane takes part
+      } else if (TYPE == EPS_PROX_SUM_EXP || TYPE == EPS_PROX_SUM_NEG_ENTR || TYPE == EPS_PROX_SUM_INV_POS) {
+        xo = NewtonProxElem<TYPE>(v, lam, active);
+      } else if (TYPE == EPS_PROX_SUM_NEG_LOG) {
+        if (active) xo = NegLogProx(v, lam);
       } else if (active) {
         if (TYPE == EPS_PROX_NON_NEGATIVE) {
           xo = fmax(v, 0.0);
@@ -136,6 +198,10 @@ void ElemProxStep(Ctx* ctx, const ElemSeg* segs, const int64_t* prefix, int nseg
     case EPS_PROX_NON_NEGATIVE: LAUNCH(EPS_PROX_NON_NEGATIVE); break;
     case EPS_PROX_SUM_QUANTILE: LAUNCH(EPS_PROX_SUM_QUANTILE); break;
     case EPS_PROX_SUM_LOGISTIC: LAUNCH(EPS_PROX_SUM_LOGISTIC); break;
+    case EPS_PROX_SUM_EXP: LAUNCH(EPS_PROX_SUM_EXP); break;
+    case EPS_PROX_SUM_NEG_ENTR: LAUNCH(EPS_PROX_SUM_NEG_ENTR); break;
+    case EPS_PROX_SUM_INV_POS: LAUNCH(EPS_PROX_SUM_INV_POS); break;
+    case EPS_PROX_SUM_NEG_LOG: LAUNCH(EPS_PROX_SUM_NEG_LOG); break;
     case EPS_PROX_NORM_1:
     case EPS_PROX_SUM_HINGE:
     case EPS_PROX_SUM_DEADZONE: LAUNCH(EPS_PROX_NORM_1); break;

@@ -30,8 +30,12 @@ PROX_TYPES = {
     "NON_NEGATIVE": 20,
     "NORM_1": 21,
     "SUM_DEADZONE": 22,
+    "SUM_EXP": 23,
     "SUM_HINGE": 24,
+    "SUM_INV_POS": 25,
     "SUM_LOGISTIC": 27,
+    "SUM_NEG_ENTR": 28,
+    "SUM_NEG_LOG": 29,
     "SUM_QUANTILE": 31,
     "NORM_2": 102,
     "TOTAL_VARIATION_1D": 106,

@@ -134,6 +134,45 @@ def newton_logistic(v: np.ndarray, lam: np.ndarray) -> np.ndarray:
     return x
 
 
+def newton_prox(v: np.ndarray, lam: np.ndarray, gradf, hessf, proj=lambda x: x) -> np.ndarray:
+    """ApplyNewtonProx (newton.cc:47-91) for any ElemwiseSmoothFunction (newton.h:23-32)."""
+    n = v.size
+    eps = max(1e-12, 1e-10 / n)
+    x = proj(v.copy())
+    with np.errstate(all="ignore"):
+        for _ in range(100):
+            gx = x - v + lam * gradf(x)
+            dx = gx / (1.0 + lam * hessf(x))
+            theta, x_res = 1.0, float(np.sqrt(gx @ gx))
+            while theta > eps:
+                nx = proj(x - theta * dx)
+                r = nx - v + lam * gradf(nx)
+                nx_res = float(np.sqrt(r @ r))
+                if nx_res <= (1 - 0.001 * theta) * x_res:
+                    x, x_res = nx, nx_res
+                    break
+                theta *= 0.5
+            if x_res < eps:
+                break
+    return x
+
+
+_FEASIBLE = lambda x: np.maximum(x, 1e-6)   # proj_feasible, sum_neg_entr.cc:40-42, sum_inv_pos.cc:37-39
+SMOOTH = {
+    # type: (gradf, hessf, proj_feasible)
+    "SUM_EXP": (np.exp, np.exp, lambda x: x),                                        # sum_exp.cc:10-36
+    "SUM_NEG_ENTR": (lambda x: 1 + np.log(x), lambda x: 1 / x, _FEASIBLE),           # sum_neg_entr.cc:10-42
+    "SUM_INV_POS": (lambda x: -1 / (x * x), lambda x: 2 / (x * x * x), _FEASIBLE),   # sum_inv_pos.cc:10-41
+}
+
+
+def neg_log_prox(v: np.ndarray, lam: np.ndarray) -> np.ndarray:
+    """ApplyNegLogProx, sum_neg_log.cc:10-26 (closed form)."""
+    s = np.sqrt(v * v + 4 * lam)
+    with np.errstate(all="ignore"):
+        return np.where(v >= 0, (v + s) / 2, 2 * lam / (-v + s))
+
+
 # ---------------------------------------------------------------------------
 # 1-D total variation (C restatement in oracle/tv1d_dp.c; pure Python for small n)
 # ---------------------------------------------------------------------------
@@ -371,6 +410,10 @@ class _VectorProx:
             return norm2_block(v, float(self.lam[0]))
         if t == "SUM_LOGISTIC":
             return newton_logistic(v, self.lam)
+        if t in SMOOTH:
+            return newton_prox(v, self.lam, *SMOOTH[t])
+        if t == "SUM_NEG_LOG":
+            return neg_log_prox(v, self.lam)
         if t == "TOTAL_VARIATION_1D":
             assert self.scalar
             return tv1d(v, float(self.lam[0]))

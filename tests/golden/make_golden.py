@@ -127,6 +127,10 @@ def prox_cases():
     out["sum_logistic"] = (simple("SUM_LOGISTIC", n), 1.7, {"x": rng.standard_normal(n) * 4})
     out["sum_logistic_large_lambda"] = (simple("SUM_LOGISTIC", 500, alpha=3.0), 25.0,
                                         {"x": rng.standard_normal(500) * 10})
+    out["sum_exp"] = (simple("SUM_EXP", n, alpha=0.8), 1.2, {"x": rng.standard_normal(n) * 3})
+    out["sum_neg_entr"] = (simple("SUM_NEG_ENTR", n, alpha=1.3), 0.9, {"x": rng.standard_normal(n) * 3 + 2})
+    out["sum_inv_pos"] = (simple("SUM_INV_POS", n, alpha=0.6), 1.4, {"x": rng.standard_normal(n) * 3 + 1})
+    out["sum_neg_log"] = (simple("SUM_NEG_LOG", n, alpha=1.1), 0.7, {"x": rng.standard_normal(n) * 3})
     out["tv_1d"] = (simple("TOTAL_VARIATION_1D", n, alpha=2.0), 1.5,
                     {"x": np.repeat(rng.standard_normal(20) * 3, 100) + rng.standard_normal(n)})
     out["tv_1d_len2"] = (simple("TOTAL_VARIATION_1D", 2, alpha=0.1), 1.0, {"x": np.array([1.0, -2.0])})

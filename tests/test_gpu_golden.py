@@ -96,7 +96,8 @@ def test_admm_matches_reference_golden(ctx, name, mode):
 
 PROX_TOL = {"NORM_1": 0.0, "SUM_HINGE": 0.0, "SUM_DEADZONE": 0.0, "SUM_QUANTILE": 0.0,
             "NON_NEGATIVE": 0.0, "TOTAL_VARIATION_1D": 1e-13, "NORM_2": 1e-14,
-            "SUM_LOGISTIC": 1e-12, "SUM_SQUARE": 1e-10}
+            "SUM_LOGISTIC": 1e-12, "SUM_EXP": 1e-10, "SUM_NEG_ENTR": 1e-10, "SUM_INV_POS": 1e-10,
+            "SUM_NEG_LOG": 1e-15, "SUM_SQUARE": 1e-10}
 
 
 @pytest.mark.parametrize("name", sorted(INDEX["prox"]))
