@@ -145,6 +145,16 @@ struct Csr {
 };
 
 // Column-tiled SELL-32 storage (sell.cu).
+// One warp's contiguous stream of slices inside a visit (stream layout, sell.cu).
+struct SellStream {
+  int64_t voff;      // first value of the stream (doubles)
+  int64_t ioff;      // first 16-bit index of the stream
+  int32_t ss_begin;  // first slice (stream order) and how many
+  int32_t ss_cnt;
+  int32_t q_total;   // 32-wide value rows in the stream
+  int32_t pad;
+};
+
 struct Sell {
   bool built = false;
   int R = 0, Cn = 0, T = 0, TW = 0, RR = 0, rows_per = 0, n_slices = 0, n_cta = 0;
@@ -153,6 +163,11 @@ struct Sell {
   DevBuf<int64_t> voff, ioff;
   DevBuf<double> val;
   DevBuf<uint16_t> idx;
+  // stream layout (version 2): a CTA walks visits = (column tile, row range); inside a visit
+  // every warp owns one contiguous stream
+  int version = 1, n_visits = 0;
+  DevBuf<int32_t> visit_tile, cta_visit;
+  DevBuf<SellStream> streams;
 };
 
 struct MapData {

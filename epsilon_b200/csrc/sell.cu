@@ -236,9 +236,421 @@ SellReducePublishKernel(int R, int T, const double* __restrict__ P, double alpha
   PeerPublishFinish(px, seq, counter);
 }
 
+
+// ===== stream layout (version 2) ==========================================================
+// Work is cut at (tile, row) granularity: the tile-major list of (tile, row) pairs is split
+// into n_cta contiguous ranges of equal cost; the part of a range inside one tile is a
+// "visit".  Inside a visit the rows are sorted by length, packed into 32-row slices, and the
+// slices are dealt to the 32 warps in serpentine order; the slices of one warp are stored
+// back to back, so a warp reads ONE contiguous stream of values and of indices per visit and
+// can keep two batches of loads in flight across slice boundaries (the version-1 kernel
+// drained its loads at the end of every 25-entry slice: long-scoreboard stalls, 77 % of the
+// HBM peak).
+
+constexpr int kBatch = 8;  // 32-wide value rows per batch of loads
+
+struct VisitTab {
+  const int32_t* lin0;        // [n_visits+1] first (tile,row) pair of the visit, tile-major
+  const int32_t* slice_base;  // [n_visits+1] first slice of the visit (visit-major numbering)
+  int n_visits;
+};
+
+__host__ __device__ __forceinline__ int WarpPrefix(int n_sl, int w) {
+  // slices that warps < w receive when n_sl slices are dealt in serpentine order
+  const int full = n_sl >> 5, rem = n_sl & 31;
+  const int extra = (full & 1) == 0 ? (w < rem ? w : rem) : (w - (32 - rem) > 0 ? w - (32 - rem) : 0);
+  return w * full + extra;
+}
+
+// slice j of a visit with n_sl slices -> position in stream order, relative to the visit
+__host__ __device__ __forceinline__ int StreamPos(int n_sl, int j) {
+  const int round = j >> 5, pos = j & 31;
+  const int w = (round & 1) == 0 ? pos : 31 - pos;
+  return WarpPrefix(n_sl, w) + round;
+}
+
+__device__ __forceinline__ int UpperBound(const int32_t* a, int n, int key) {
+  // first index with a[i] > key
+  int lo = 0, hi = n;
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (a[mid] <= key) lo = mid + 1; else hi = mid;
+  }
+  return lo;
+}
+
+struct CostOp {
+  const int32_t* seglen;
+  __host__ __device__ int64_t operator()(int64_t i) const { return 10 * (int64_t)seglen[i] + 12; }
+};
+
+__global__ void CutKernel(int64_t TR, int G, const int64_t* __restrict__ csum, int32_t* __restrict__ cut) {
+  const int g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g > G) return;
+  if (g == 0) { cut[0] = 0; return; }
+  if (g == G) { cut[G] = (int32_t)TR; return; }
+  const int64_t total = csum[TR - 1];
+  const int64_t target = (int64_t)((double)total * g / G);
+  int64_t lo = 0, hi = TR;
+  while (lo < hi) {
+    const int64_t mid = (lo + hi) >> 1;
+    if (csum[mid] < target) lo = mid + 1; else hi = mid;
+  }
+  cut[g] = (int32_t)lo;
+}
+
+__global__ void VisitKeysKernel(int64_t TR, VisitTab vt, const int32_t* __restrict__ seglen,
+                                uint32_t* __restrict__ keys, int32_t* __restrict__ vals) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= TR) return;
+  const int v = UpperBound(vt.lin0, vt.n_visits, (int)i) - 1;
+  keys[i] = ((uint32_t)v << 16) | (uint32_t)(0xFFFF - seglen[i]);
+  vals[i] = (int32_t)i;
+}
+
+__global__ void StreamSliceLenKernel(int n_slices, VisitTab vt, const uint32_t* __restrict__ skeys,
+                                     int32_t* __restrict__ sl_len, int64_t* __restrict__ vsize) {
+  const int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= n_slices) return;
+  const int v = UpperBound(vt.slice_base, vt.n_visits, s) - 1;
+  const int j = s - vt.slice_base[v];
+  const int n_sl = vt.slice_base[v + 1] - vt.slice_base[v];
+  const int len = 0xFFFF - (int)(skeys[vt.lin0[v] + 32 * j] & 0xFFFF);
+  const int ss = vt.slice_base[v] + StreamPos(n_sl, j);
+  sl_len[ss] = len;
+  vsize[ss] = 32 * (int64_t)len;
+}
+
+// one warp per slice
+__global__ void StreamFillKernel(int R, int TW, int n_slices, VisitTab vt, const int32_t* __restrict__ visit_tile,
+                                 const SellStream* __restrict__ streams, const int32_t* __restrict__ svals,
+                                 const int32_t* __restrict__ segstart, const int32_t* __restrict__ seglen,
+                                 const int32_t* __restrict__ ccol, const double* __restrict__ cval,
+                                 const int32_t* __restrict__ sl_len, const int64_t* __restrict__ voff,
+                                 double* __restrict__ val, uint16_t* __restrict__ idx,
+                                 int32_t* __restrict__ rowid) {
+  const int s = blockIdx.x * (blockDim.x / 32) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (s >= n_slices) return;
+  const int v = UpperBound(vt.slice_base, vt.n_visits, s) - 1;
+  const int j = s - vt.slice_base[v];
+  const int n_sl = vt.slice_base[v + 1] - vt.slice_base[v];
+  const int round = j >> 5, pos5 = j & 31;
+  const int w = (round & 1) == 0 ? pos5 : 31 - pos5;
+  const int ss = vt.slice_base[v] + WarpPrefix(n_sl, w) + round;
+  const int t = visit_tile[v];
+  const int pos = vt.lin0[v] + 32 * j + lane;
+  int row = -1, start = 0, mylen = 0;
+  if (pos < vt.lin0[v + 1]) {
+    const int i = svals[pos];
+    row = i - t * R;
+    start = segstart[i];
+    mylen = seglen[i];
+  }
+  rowid[(size_t)ss * 32 + lane] = row;
+  const int len = sl_len[ss];
+  const SellStream sd = streams[v * 32 + w];
+  const int64_t vo = voff[ss];
+  const int q0 = (int)((vo - sd.voff) >> 5);
+  const int base = t * TW;
+  for (int k = 0; k < len; k++) {
+    const bool in = k < mylen;
+    const int q = q0 + k;
+    val[vo + (int64_t)k * 32 + lane] = in ? cval[start + k] : 0.0;
+    idx[sd.ioff + (int64_t)(q >> 2) * 128 + lane * 4 + (q & 3)] = in ? (uint16_t)(ccol[start + k] - base) : (uint16_t)0;
+  }
+}
+
+__device__ __forceinline__ uint2 LdStreamU2(const uint16_t* p) {
+  uint2 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0, %1}, [%2];" : "=r"(r.x), "=r"(r.y) : "l"(p));
+  return r;
+}
+
+struct SellBatch {
+  double v[kBatch];
+  uint2 ix[kBatch / 4];
+};
+
+template <bool GUARD>
+__device__ __forceinline__ void LoadBatch(SellBatch& b, const double* v, const uint16_t* ix, int q0, int Q) {
+#pragma unroll
+  for (int j = 0; j < kBatch / 4; j++) {
+    if (!GUARD || q0 + 4 * j < Q) b.ix[j] = LdStreamU2(ix + (size_t)((q0 >> 2) + j) * 128);
+    else b.ix[j] = make_uint2(0u, 0u);
+  }
+#pragma unroll
+  for (int j = 0; j < kBatch; j++) {
+    if (!GUARD || q0 + j < Q) b.v[j] = LdStream(v + (size_t)(q0 + j) * 32);
+    else b.v[j] = 0.0;
+  }
+}
+
+// Per-warp cursor over the slices of a stream: which row the running sum belongs to.
+struct SliceCursor {
+  const int32_t* sl_len;
+  const int32_t* rowid;
+  double* Pt;
+  int ss, ss_end, lane;
+  int len_cur, row_cur, len_next, row_next, kk;
+  double acc;
+  __device__ __forceinline__ void Prefetch() {
+    if (ss + 1 < ss_end) {
+      len_next = sl_len[ss + 1];
+      row_next = rowid[(size_t)(ss + 1) * 32 + lane];
+    } else {
+      len_next = 0x7FFFFFFF;
+      row_next = -1;
+    }
+  }
+  __device__ __forceinline__ void Start(int begin, int cnt) {
+    ss = begin; ss_end = begin + cnt; kk = 0; acc = 0.0;
+    len_cur = sl_len[ss];
+    row_cur = rowid[(size_t)ss * 32 + lane];
+    Prefetch();
+    SkipEmpty();
+  }
+  __device__ __forceinline__ void Next() {
+    if (row_cur >= 0) Pt[row_cur] = acc;
+    acc = 0.0; kk = 0;
+    ss++;
+    len_cur = len_next; row_cur = row_next;
+    Prefetch();
+  }
+  __device__ __forceinline__ void SkipEmpty() {
+    while (ss < ss_end && len_cur == 0) Next();
+  }
+  __device__ __forceinline__ void Add(double v, double x) {
+    acc += v * x;
+    if (++kk == len_cur) { Next(); SkipEmpty(); }
+  }
+};
+
+template <bool GUARD>
+__device__ __forceinline__ void ConsumeBatch(const SellBatch& b, const double* xs, SliceCursor& c, int q0, int Q) {
+#pragma unroll
+  for (int j = 0; j < kBatch; j++) {
+    const uint32_t word = (j & 2) ? b.ix[j >> 2].y : b.ix[j >> 2].x;
+    const uint32_t col = (j & 1) ? (word >> 16) : (word & 0xFFFF);
+    if (!GUARD || q0 + j < Q) c.Add(b.v[j], xs[col]);
+  }
+}
+
+__global__ void __launch_bounds__(kSellThreads, 1)
+SellStreamKernel(int R, int Cn, int TW, const int32_t* __restrict__ cta_visit,
+                 const int32_t* __restrict__ visit_tile, const SellStream* __restrict__ streams,
+                 const int32_t* __restrict__ sl_len, const double* __restrict__ val,
+                 const uint16_t* __restrict__ idx, const int32_t* __restrict__ rowid,
+                 const double* __restrict__ x, double* __restrict__ P, int use_tma,
+                 const int* __restrict__ skip) {
+  extern __shared__ __align__(128) double xs[];
+  __shared__ __align__(8) unsigned long long bar;
+  if (skip && *skip) return;  // speculative launch after the CG loop converged (kkt.cu)
+  const int v_lo = cta_visit[blockIdx.x], v_hi = cta_visit[blockIdx.x + 1];
+  if (v_lo >= v_hi) return;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint32_t bar_a = SmemAddr(&bar);
+  if (use_tma && threadIdx.x == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_a));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  int cur_t = -1;
+  uint32_t phase = 0;
+  for (int vi = v_lo; vi < v_hi; vi++) {
+    const int t = visit_tile[vi];
+    // this warp's stream: issue the first loads before waiting for the x tile
+    const SellStream sd = streams[vi * 32 + warp];
+    const int Q = sd.q_total;
+    const double* v = val + sd.voff + lane;
+    const uint16_t* ix = idx + sd.ioff + lane * 4;
+    SellBatch ba, bb;
+    if (Q >= kBatch) LoadBatch<false>(ba, v, ix, 0, Q); else LoadBatch<true>(ba, v, ix, 0, Q);
+    if (t != cur_t) {
+      const int c0 = t * TW;
+      const int cw = min(TW, Cn - c0);
+      __syncthreads();  // every warp is done reading the previous tile (and sees the barrier init)
+      if (use_tma) {
+        // one TMA bulk copy of the x tile (cp.async.bulk, completion on an mbarrier)
+        const uint32_t bytes = (uint32_t)cw * 8u;
+        if (threadIdx.x == 0) {
+          asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_a), "r"(bytes) : "memory");
+          asm volatile(
+              "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+              ::"r"(SmemAddr(xs)), "l"(x + c0), "r"(bytes), "r"(bar_a) : "memory");
+        }
+        uint32_t done = 0;
+        while (!done) {
+          asm volatile(
+              "{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}\n"
+              : "=r"(done) : "r"(bar_a), "r"(phase) : "memory");
+        }
+        phase ^= 1u;
+      } else {
+        for (int i = threadIdx.x; i < cw; i += kSellThreads) xs[i] = x[c0 + i];
+        __syncthreads();
+      }
+      cur_t = t;
+    }
+    if (sd.ss_cnt == 0) continue;
+    SliceCursor c;
+    c.sl_len = sl_len; c.rowid = rowid; c.Pt = P + (size_t)t * R; c.lane = lane;
+    c.Start(sd.ss_begin, sd.ss_cnt);
+    int q = 0;
+    // two batches in flight; full batches need no guards
+    while (q + 3 * kBatch <= Q) {
+      LoadBatch<false>(bb, v, ix, q + kBatch, Q);
+      ConsumeBatch<false>(ba, xs, c, q, Q);
+      LoadBatch<false>(ba, v, ix, q + 2 * kBatch, Q);
+      ConsumeBatch<false>(bb, xs, c, q + kBatch, Q);
+      q += 2 * kBatch;
+    }
+    // here ba holds batch q (fully inside the stream iff q + kBatch <= Q)
+    while (q < Q) {
+      LoadBatch<true>(bb, v, ix, q + kBatch, Q);
+      ConsumeBatch<true>(ba, xs, c, q, Q);
+      ba = bb;
+      q += kBatch;
+    }
+    // rows after the last stored entry (empty in this tile)
+    while (c.ss < c.ss_end) c.Next();
+  }
+}
+
 }  // namespace
 
+
+static void BuildSellStream(Ctx* ctx, const Csr& A, Sell* S) {
+  const int R = A.m, Cn = A.n;
+  S->version = 2;
+  S->R = R; S->Cn = Cn; S->nnz = A.nnz;
+  const int T = (Cn + kMaxTile - 1) / kMaxTile;
+  int TW = (Cn + T - 1) / T;
+  TW = (TW + 1) / 2 * 2;  // keep tile starts 16-byte aligned for the bulk copy
+  S->T = T; S->TW = TW;
+  const int64_t TR = (int64_t)T * R;
+  EPS_CHECK(TR < ((int64_t)1 << 31) - 64, "too many (tile,row) pairs for the SELL build (%lld)", (long long)TR);
+  DevBuf<int32_t> segstart(ctx, TR), seglen(ctx, TR);
+  SegBoundsKernel<<<(R + 255) / 256, 256, 0, ctx->stream>>>(R, T, TW, A.rowptr.p, A.col.p, segstart.p, seglen.p);
+
+  // equal-cost cut of the tile-major (tile,row) list over the CTAs
+  const int G = (int)std::max<int64_t>(1, std::min<int64_t>(ctx->sm_count, (TR + 31) / 32));
+  std::vector<int32_t> cut(G + 1);
+  {
+    DevBuf<int64_t> csum(ctx, TR);
+    cub::CountingInputIterator<int64_t> cnt(0);
+    cub::TransformInputIterator<int64_t, CostOp, cub::CountingInputIterator<int64_t>> cost(cnt, CostOp{seglen.p});
+    size_t bytes = 0;
+    CUDA_CHECK(cub::DeviceScan::InclusiveSum(nullptr, bytes, cost, csum.p, (int)TR, ctx->stream));
+    DevBuf<char> tmp(ctx, bytes);
+    CUDA_CHECK(cub::DeviceScan::InclusiveSum(tmp.p, bytes, cost, csum.p, (int)TR, ctx->stream));
+    DevBuf<int32_t> dcut(ctx, G + 1);
+    CutKernel<<<(G + 1 + 255) / 256, 256, 0, ctx->stream>>>(TR, G, csum.p, dcut.p);
+    dcut.download(cut.data(), G + 1);
+  }
+  // visits: the part of each CTA's range inside one tile
+  std::vector<int32_t> lin0, slice_base, vtile, cta_visit(G + 1);
+  int n_slices = 0;
+  for (int g = 0; g < G; g++) {
+    cta_visit[g] = (int)vtile.size();
+    int64_t c0 = cut[g];
+    const int64_t c1 = std::max<int64_t>(cut[g + 1], c0);
+    while (c0 < c1) {
+      const int t = (int)(c0 / R);
+      const int64_t e = std::min<int64_t>(c1, (int64_t)(t + 1) * R);
+      lin0.push_back((int32_t)c0);
+      slice_base.push_back(n_slices);
+      vtile.push_back(t);
+      n_slices += (int)((e - c0 + 31) / 32);
+      c0 = e;
+    }
+  }
+  const int NV = (int)vtile.size();
+  cta_visit[G] = NV;
+  lin0.push_back((int32_t)TR);
+  slice_base.push_back(n_slices);
+  EPS_CHECK(NV < 65536, "too many SELL visits (%d)", NV);
+  S->n_cta = G; S->n_visits = NV; S->n_slices = n_slices;
+  DevBuf<int32_t> d_lin0(ctx, NV + 1), d_sbase(ctx, NV + 1);
+  d_lin0.upload(lin0.data(), NV + 1);
+  d_sbase.upload(slice_base.data(), NV + 1);
+  S->visit_tile.alloc(ctx, std::max(NV, 1));
+  S->visit_tile.upload(vtile.data(), NV);
+  S->cta_visit.alloc(ctx, G + 1);
+  S->cta_visit.upload(cta_visit.data(), G + 1);
+  const VisitTab vt{d_lin0.p, d_sbase.p, NV};
+
+  // sort the rows of every visit by length (descending, stable)
+  DevBuf<int32_t> vals_in(ctx, TR), vals_out(ctx, TR);
+  DevBuf<uint32_t> keys_in(ctx, TR), keys_out(ctx, TR);
+  VisitKeysKernel<<<(unsigned)((TR + 255) / 256), 256, 0, ctx->stream>>>(TR, vt, seglen.p, keys_in.p, vals_in.p);
+  {
+    size_t bytes = 0;
+    CUDA_CHECK(cub::DeviceRadixSort::SortPairs(nullptr, bytes, keys_in.p, keys_out.p, vals_in.p, vals_out.p,
+                                               (int)TR, 0, 32, ctx->stream));
+    DevBuf<char> tmp(ctx, bytes);
+    CUDA_CHECK(cub::DeviceRadixSort::SortPairs(tmp.p, bytes, keys_in.p, keys_out.p, vals_in.p, vals_out.p,
+                                               (int)TR, 0, 32, ctx->stream));
+    CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+  }
+  // slice lengths in stream order and their value offsets
+  S->sl_len.alloc(ctx, n_slices + 1);
+  S->voff.alloc(ctx, n_slices + 1);
+  std::vector<int64_t> hv(n_slices + 1);
+  {
+    DevBuf<int64_t> vsize(ctx, n_slices + 1);
+    vsize.zero();
+    StreamSliceLenKernel<<<(n_slices + 255) / 256, 256, 0, ctx->stream>>>(n_slices, vt, keys_out.p, S->sl_len.p, vsize.p);
+    size_t bytes = 0;
+    CUDA_CHECK(cub::DeviceScan::ExclusiveSum(nullptr, bytes, vsize.p, S->voff.p, n_slices + 1, ctx->stream));
+    DevBuf<char> tmp(ctx, bytes);
+    CUDA_CHECK(cub::DeviceScan::ExclusiveSum(tmp.p, bytes, vsize.p, S->voff.p, n_slices + 1, ctx->stream));
+    S->voff.download(hv.data(), n_slices + 1);
+  }
+  // one stream per (visit, warp)
+  std::vector<SellStream> st((size_t)std::max(NV, 1) * 32);
+  int64_t ioff = 0;
+  for (int v = 0; v < NV; v++) {
+    const int n_sl = slice_base[v + 1] - slice_base[v];
+    for (int w = 0; w < 32; w++) {
+      SellStream& d = st[(size_t)v * 32 + w];
+      d.ss_begin = slice_base[v] + WarpPrefix(n_sl, w);
+      d.ss_cnt = WarpPrefix(n_sl, w + 1) - WarpPrefix(n_sl, w);
+      d.voff = hv[d.ss_begin];
+      d.q_total = (int32_t)((hv[d.ss_begin + d.ss_cnt] - hv[d.ss_begin]) / 32);
+      d.ioff = ioff;
+      d.pad = 0;
+      ioff += (int64_t)((d.q_total + 3) / 4) * 128;
+    }
+  }
+  S->streams.alloc(ctx, st.size());
+  S->streams.upload(st.data(), st.size());
+  S->n_val = hv[n_slices];
+  S->n_idx = ioff;
+  S->val.alloc(ctx, std::max<int64_t>(S->n_val, 1));
+  S->idx.alloc(ctx, std::max<int64_t>(S->n_idx, 4));
+  S->idx.zero();
+  S->rowid.alloc(ctx, (size_t)std::max(n_slices, 1) * 32);
+  StreamFillKernel<<<(n_slices + 7) / 8, 256, 0, ctx->stream>>>(
+      R, TW, n_slices, vt, S->visit_tile.p, S->streams.p, vals_out.p, segstart.p, seglen.p, A.col.p, A.val.p,
+      S->sl_len.p, S->voff.p, S->val.p, S->idx.p, S->rowid.p);
+  CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+  CUDA_CHECK(cudaGetLastError());
+  S->voff.release();  // only needed while building
+  static bool attr_set = false;
+  if (!attr_set) {
+    CUDA_CHECK(cudaFuncSetAttribute(SellStreamKernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    kMaxTile * 8 + 64));
+    attr_set = true;
+  }
+  S->built = true;
+}
+
 void BuildSell(Ctx* ctx, const Csr& A, Sell* S) {
+  const char* ver = getenv("EPS_SELL_VERSION");
+  if (!ver || atoi(ver) != 1) {
+    BuildSellStream(ctx, A, S);
+    return;
+  }
   const int R = A.m, Cn = A.n;
   S->R = R; S->Cn = Cn; S->nnz = A.nnz;
   const int T = (Cn + kMaxTile - 1) / kMaxTile;
@@ -347,9 +759,14 @@ void SellApply(Ctx* ctx, const Sell& S, double alpha, const double* x, double be
     // pointer and the width of the last tile can break that
     const int last = S.Cn - (S.T - 1) * S.TW;
     const int use_tma = ((reinterpret_cast<uintptr_t>(x) & 15) == 0 && last % 2 == 0) ? 1 : 0;
-    SellSpmvKernel<<<S.n_cta, kSellThreads, (size_t)S.TW * 8 + 64, ctx->stream>>>(
-        S.R, S.Cn, S.TW, S.RR, S.rows_per / 32, S.cta_begin.p, S.sl_len.p, S.voff.p, S.ioff.p, S.val.p, S.idx.p,
-        S.rowid.p, x, P, use_tma, skip);
+    if (S.version == 2)
+      SellStreamKernel<<<S.n_cta, kSellThreads, (size_t)S.TW * 8 + 64, ctx->stream>>>(
+          S.R, S.Cn, S.TW, S.cta_visit.p, S.visit_tile.p, S.streams.p, S.sl_len.p, S.val.p, S.idx.p, S.rowid.p, x,
+          P, use_tma, skip);
+    else
+      SellSpmvKernel<<<S.n_cta, kSellThreads, (size_t)S.TW * 8 + 64, ctx->stream>>>(
+          S.R, S.Cn, S.TW, S.RR, S.rows_per / 32, S.cta_begin.p, S.sl_len.p, S.voff.p, S.ioff.p, S.val.p, S.idx.p,
+          S.rowid.p, x, P, use_tma, skip);
     ctx->count_launch();
   }
   if (ex && ex->publish) {

@@ -83,3 +83,28 @@ def test_sparse_sell_ragged(ctx, monkeypatch):
     a[7, 69999] = 3.0
     a[100:400, 25600] = rng.standard_normal((300, 1))  # first column of the second tile
     _check(ctx, LinearMapSpec.Sparse(a.tocsc()), rng)
+
+
+@pytest.mark.parametrize("m,n,d", [(5, 7, 0.5), (31, 33, 0.2), (1, 40000, 0.01), (40000, 1, 0.3), (64, 64, 0.0),
+                                   (1025, 51201, 0.003)])
+def test_sparse_sell_small_shapes(ctx, m, n, d, monkeypatch):
+    """Stream layout edge cases: fewer rows than a slice, fewer slices than warps, a single row or
+    column, no stored entries at all, a tile boundary that is not a multiple of the tile width."""
+    monkeypatch.setenv("EPS_SPARSE_FORMAT", "sell")
+    rng = np.random.default_rng(m * 7 + n)
+    a = sp.random(m, n, density=d, random_state=np.random.RandomState(9), format="csc")
+    a.data = rng.standard_normal(a.nnz)
+    _check(ctx, LinearMapSpec.Sparse(a), rng)
+
+
+def test_sparse_sell_skewed_rows(ctx, monkeypatch):
+    """Row lengths from 0 to several thousand inside one visit (sorting, empty trailing slices)."""
+    monkeypatch.setenv("EPS_SPARSE_FORMAT", "sell")
+    rng = np.random.default_rng(21)
+    m, n = 5000, 30000
+    lens = np.minimum((rng.pareto(1.2, m) * 3).astype(int), 4000)
+    lens[::7] = 0
+    rows = np.repeat(np.arange(m), lens)
+    cols = np.concatenate([rng.choice(n, k, replace=False) for k in lens if k]) if lens.sum() else np.zeros(0, int)
+    a = sp.csc_matrix((rng.standard_normal(rows.size), (rows, cols)), shape=(m, n))
+    _check(ctx, LinearMapSpec.Sparse(a), rng)
