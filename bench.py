@@ -307,7 +307,7 @@ def main_ours(args):
         if world == 1 and args.m == 1_000_000 and args.n == 100_000:
             import csv
             rd = wr = 0.0
-            for row in csv.reader(open(os.path.join(ROOT, "profiles", "r01_ncu_full_SellSpmvKernel.csv"))):
+            for row in csv.reader(open(os.path.join(ROOT, "profiles", "r01_ncu_full_SellStreamKernel.csv"))):
                 if row and row[0] in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
                     scale = {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0}[row[1]]
                     v = 0.5 * (float(row[2]) + float(row[3])) * scale   # mean of the A' and A launches
@@ -318,11 +318,11 @@ def main_ours(args):
     sell = os.environ.get("EPS_SPARSE_FORMAT", "sell") != "csr"
     roofline = {
         "bound": "hbm",
-        "kernel": ("SellSpmvKernel" if sell else "CsrSpmvKernel") + " (A and A' passes of the CG matvec)",
+        "kernel": ("SellStreamKernel" if sell else "CsrSpmvKernel") + " (A and A' passes of the CG matvec)",
         "achieved": achieved, "peak": peak,
         "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "6650 GB/s (of fallback)",
         "unit": "GB/s", "frac": achieved / peak if achieved else None, "traffic": traffic,
-        "traffic_source": "profiles/r01_ncu_full_SellSpmvKernel.csv (ncu --set full, mean of one A and one A' launch)" if traffic else None,
+        "traffic_source": "profiles/r01_ncu_full_SellStreamKernel.csv (ncu --set full, mean of one A and one A' launch)" if traffic else None,
         "launches": spmv_launches, "ms_per_launch": spmv_ms / max(spmv_launches, 1),
         "algorithmic_bytes_per_launch": spmv_bytes / max(spmv_launches, 1),
         "share_of_step": spmv_ms / total_prof_ms if total_prof_ms else None,

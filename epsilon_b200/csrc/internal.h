@@ -165,7 +165,7 @@ struct Sell {
   DevBuf<uint16_t> idx;
   // stream layout (version 2): a CTA walks visits = (column tile, row range); inside a visit
   // every warp owns one contiguous stream
-  int version = 1, n_visits = 0;
+  int version = 1, n_visits = 0, nw = 32;
   DevBuf<int32_t> visit_tile, cta_visit;
   DevBuf<SellStream> streams;
 };

@@ -247,7 +247,6 @@ SellReducePublishKernel(int R, int T, const double* __restrict__ P, double alpha
 // drained its loads at the end of every 25-entry slice: long-scoreboard stalls, 77 % of the
 // HBM peak).
 
-constexpr int kBatch = 8;  // 32-wide value rows per batch of loads
 
 struct VisitTab {
   const int32_t* lin0;        // [n_visits+1] first (tile,row) pair of the visit, tile-major
@@ -255,18 +254,18 @@ struct VisitTab {
   int n_visits;
 };
 
-__host__ __device__ __forceinline__ int WarpPrefix(int n_sl, int w) {
-  // slices that warps < w receive when n_sl slices are dealt in serpentine order
-  const int full = n_sl >> 5, rem = n_sl & 31;
-  const int extra = (full & 1) == 0 ? (w < rem ? w : rem) : (w - (32 - rem) > 0 ? w - (32 - rem) : 0);
+__host__ __device__ __forceinline__ int WarpPrefix(int n_sl, int w, int NW) {
+  // slices that warps < w receive when n_sl slices are dealt to NW warps in serpentine order
+  const int full = n_sl / NW, rem = n_sl % NW;
+  const int extra = (full & 1) == 0 ? (w < rem ? w : rem) : (w - (NW - rem) > 0 ? w - (NW - rem) : 0);
   return w * full + extra;
 }
 
 // slice j of a visit with n_sl slices -> position in stream order, relative to the visit
-__host__ __device__ __forceinline__ int StreamPos(int n_sl, int j) {
-  const int round = j >> 5, pos = j & 31;
-  const int w = (round & 1) == 0 ? pos : 31 - pos;
-  return WarpPrefix(n_sl, w) + round;
+__host__ __device__ __forceinline__ int StreamPos(int n_sl, int j, int NW) {
+  const int round = j / NW, pos = j % NW;
+  const int w = (round & 1) == 0 ? pos : NW - 1 - pos;
+  return WarpPrefix(n_sl, w, NW) + round;
 }
 
 __device__ __forceinline__ int UpperBound(const int32_t* a, int n, int key) {
@@ -279,9 +278,15 @@ __device__ __forceinline__ int UpperBound(const int32_t* a, int n, int key) {
   return lo;
 }
 
+// Streamed bytes of one (tile,row) pair; the x-tile staging a CTA pays when it enters a tile
+// is charged to the first row of the tile (a CTA that starts inside a tile pays it as well, so
+// every CTA carries one staging more than its share shows: equal for all, it cancels).
 struct CostOp {
   const int32_t* seglen;
-  __host__ __device__ int64_t operator()(int64_t i) const { return 10 * (int64_t)seglen[i] + 12; }
+  int64_t R, stage;
+  __host__ __device__ int64_t operator()(int64_t i) const {
+    return 10 * (int64_t)seglen[i] + 12 + (i % R == 0 ? stage : 0);
+  }
 };
 
 __global__ void CutKernel(int64_t TR, int G, const int64_t* __restrict__ csum, int32_t* __restrict__ cut) {
@@ -308,7 +313,7 @@ __global__ void VisitKeysKernel(int64_t TR, VisitTab vt, const int32_t* __restri
   vals[i] = (int32_t)i;
 }
 
-__global__ void StreamSliceLenKernel(int n_slices, VisitTab vt, const uint32_t* __restrict__ skeys,
+__global__ void StreamSliceLenKernel(int n_slices, int NW, VisitTab vt, const uint32_t* __restrict__ skeys,
                                      int32_t* __restrict__ sl_len, int64_t* __restrict__ vsize) {
   const int s = blockIdx.x * blockDim.x + threadIdx.x;
   if (s >= n_slices) return;
@@ -316,13 +321,13 @@ __global__ void StreamSliceLenKernel(int n_slices, VisitTab vt, const uint32_t* 
   const int j = s - vt.slice_base[v];
   const int n_sl = vt.slice_base[v + 1] - vt.slice_base[v];
   const int len = 0xFFFF - (int)(skeys[vt.lin0[v] + 32 * j] & 0xFFFF);
-  const int ss = vt.slice_base[v] + StreamPos(n_sl, j);
+  const int ss = vt.slice_base[v] + StreamPos(n_sl, j, NW);
   sl_len[ss] = len;
   vsize[ss] = 32 * (int64_t)len;
 }
 
 // one warp per slice
-__global__ void StreamFillKernel(int R, int TW, int n_slices, VisitTab vt, const int32_t* __restrict__ visit_tile,
+__global__ void StreamFillKernel(int R, int TW, int n_slices, int NW, VisitTab vt, const int32_t* __restrict__ visit_tile,
                                  const SellStream* __restrict__ streams, const int32_t* __restrict__ svals,
                                  const int32_t* __restrict__ segstart, const int32_t* __restrict__ seglen,
                                  const int32_t* __restrict__ ccol, const double* __restrict__ cval,
@@ -335,9 +340,9 @@ __global__ void StreamFillKernel(int R, int TW, int n_slices, VisitTab vt, const
   const int v = UpperBound(vt.slice_base, vt.n_visits, s) - 1;
   const int j = s - vt.slice_base[v];
   const int n_sl = vt.slice_base[v + 1] - vt.slice_base[v];
-  const int round = j >> 5, pos5 = j & 31;
-  const int w = (round & 1) == 0 ? pos5 : 31 - pos5;
-  const int ss = vt.slice_base[v] + WarpPrefix(n_sl, w) + round;
+  const int round = j / NW, pos5 = j % NW;
+  const int w = (round & 1) == 0 ? pos5 : NW - 1 - pos5;
+  const int ss = vt.slice_base[v] + WarpPrefix(n_sl, w, NW) + round;
   const int t = visit_tile[v];
   const int pos = vt.lin0[v] + 32 * j + lane;
   int row = -1, start = 0, mylen = 0;
@@ -347,9 +352,9 @@ __global__ void StreamFillKernel(int R, int TW, int n_slices, VisitTab vt, const
     start = segstart[i];
     mylen = seglen[i];
   }
-  rowid[(size_t)ss * 32 + lane] = row;
+  rowid[(size_t)ss * 32 + lane] = row < 0 ? -1 : t * R + row;
   const int len = sl_len[ss];
-  const SellStream sd = streams[v * 32 + w];
+  const SellStream sd = streams[v * NW + w];
   const int64_t vo = voff[ss];
   const int q0 = (int)((vo - sd.voff) >> 5);
   const int base = t * TW;
@@ -361,19 +366,28 @@ __global__ void StreamFillKernel(int R, int TW, int n_slices, VisitTab vt, const
   }
 }
 
+__device__ __forceinline__ unsigned long long GlobalTimer() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
 __device__ __forceinline__ uint2 LdStreamU2(const uint16_t* p) {
   uint2 r;
   asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0, %1}, [%2];" : "=r"(r.x), "=r"(r.y) : "l"(p));
   return r;
 }
 
+// KB 32-wide value rows per batch of loads
+template <int KB>
 struct SellBatch {
-  double v[kBatch];
-  uint2 ix[kBatch / 4];
+  double v[KB];
+  uint2 ix[KB / 4];
 };
 
-template <bool GUARD>
-__device__ __forceinline__ void LoadBatch(SellBatch& b, const double* v, const uint16_t* ix, int q0, int Q) {
+template <bool GUARD, int KB>
+__device__ __forceinline__ void LoadBatch(SellBatch<KB>& b, const double* v, const uint16_t* ix, int q0, int Q) {
+  constexpr int kBatch = KB;
 #pragma unroll
   for (int j = 0; j < kBatch / 4; j++) {
     if (!GUARD || q0 + 4 * j < Q) b.ix[j] = LdStreamU2(ix + (size_t)((q0 >> 2) + j) * 128);
@@ -387,47 +401,49 @@ __device__ __forceinline__ void LoadBatch(SellBatch& b, const double* v, const u
 }
 
 // Per-warp cursor over the slices of a stream: which row the running sum belongs to.
+// rowid holds the index into P (tile * R + row), -1 for the padding lanes of a visit's last slice.
 struct SliceCursor {
   const int32_t* sl_len;
   const int32_t* rowid;
-  double* Pt;
-  int ss, ss_end, lane;
-  int len_cur, row_cur, len_next, row_next, kk;
+  double* P;
+  int cur, end;          // current slice and one past the last one of the stream
+  int rem;               // value rows left in the current slice
+  int row_cur, len_next, row_next;
   double acc;
   __device__ __forceinline__ void Prefetch() {
-    if (ss + 1 < ss_end) {
-      len_next = sl_len[ss + 1];
-      row_next = rowid[(size_t)(ss + 1) * 32 + lane];
+    if (cur + 1 < end) {
+      len_next = sl_len[cur + 1];
+      row_next = rowid[(size_t)(cur + 1) * 32 + (threadIdx.x & 31)];
     } else {
       len_next = 0x7FFFFFFF;
       row_next = -1;
     }
   }
   __device__ __forceinline__ void Start(int begin, int cnt) {
-    ss = begin; ss_end = begin + cnt; kk = 0; acc = 0.0;
-    len_cur = sl_len[ss];
-    row_cur = rowid[(size_t)ss * 32 + lane];
+    cur = begin; end = begin + cnt; acc = 0.0;
+    rem = sl_len[begin];
+    row_cur = rowid[(size_t)begin * 32 + (threadIdx.x & 31)];
     Prefetch();
-    SkipEmpty();
   }
   __device__ __forceinline__ void Next() {
-    if (row_cur >= 0) Pt[row_cur] = acc;
-    acc = 0.0; kk = 0;
-    ss++;
-    len_cur = len_next; row_cur = row_next;
+    if (row_cur >= 0) P[row_cur] = acc;
+    acc = 0.0;
+    cur++;
+    rem = len_next; row_cur = row_next;
     Prefetch();
   }
   __device__ __forceinline__ void SkipEmpty() {
-    while (ss < ss_end && len_cur == 0) Next();
+    while (cur < end && rem == 0) Next();
   }
   __device__ __forceinline__ void Add(double v, double x) {
     acc += v * x;
-    if (++kk == len_cur) { Next(); SkipEmpty(); }
+    if (--rem == 0) { Next(); SkipEmpty(); }
   }
 };
 
-template <bool GUARD>
-__device__ __forceinline__ void ConsumeBatch(const SellBatch& b, const double* xs, SliceCursor& c, int q0, int Q) {
+template <bool GUARD, int KB>
+__device__ __forceinline__ void ConsumeBatch(const SellBatch<KB>& b, const double* xs, SliceCursor& c, int q0, int Q) {
+  constexpr int kBatch = KB;
 #pragma unroll
   for (int j = 0; j < kBatch; j++) {
     const uint32_t word = (j & 2) ? b.ix[j >> 2].y : b.ix[j >> 2].x;
@@ -436,16 +452,19 @@ __device__ __forceinline__ void ConsumeBatch(const SellBatch& b, const double* x
   }
 }
 
-__global__ void __launch_bounds__(kSellThreads, 1)
+template <int NW, int KB, bool TRACE>
+__global__ void __launch_bounds__(NW * 32, 1)
 SellStreamKernel(int R, int Cn, int TW, const int32_t* __restrict__ cta_visit,
                  const int32_t* __restrict__ visit_tile, const SellStream* __restrict__ streams,
                  const int32_t* __restrict__ sl_len, const double* __restrict__ val,
                  const uint16_t* __restrict__ idx, const int32_t* __restrict__ rowid,
                  const double* __restrict__ x, double* __restrict__ P, int use_tma,
-                 const int* __restrict__ skip) {
+                 const int* __restrict__ skip, unsigned long long* __restrict__ trace) {
+  constexpr int kBatch = KB;
   extern __shared__ __align__(128) double xs[];
   __shared__ __align__(8) unsigned long long bar;
   if (skip && *skip) return;  // speculative launch after the CG loop converged (kkt.cu)
+  if (TRACE && threadIdx.x == 0) trace[blockIdx.x * 4 + 0] = GlobalTimer();
   const int v_lo = cta_visit[blockIdx.x], v_hi = cta_visit[blockIdx.x + 1];
   if (v_lo >= v_hi) return;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -458,26 +477,42 @@ SellStreamKernel(int R, int Cn, int TW, const int32_t* __restrict__ cta_visit,
   uint32_t phase = 0;
   for (int vi = v_lo; vi < v_hi; vi++) {
     const int t = visit_tile[vi];
-    // this warp's stream: issue the first loads before waiting for the x tile
-    const SellStream sd = streams[vi * 32 + warp];
+    const bool restage = t != cur_t;
+    const int c0 = t * TW;
+    const int cw = min(TW, Cn - c0);
+    if (restage) {
+      // every warp is done reading the previous tile; nothing to wait for on the first visit
+      if (vi != v_lo) __syncthreads();
+      if (use_tma && threadIdx.x == 0) {
+        // one TMA bulk copy of the x tile (cp.async.bulk, completion on an mbarrier), issued
+        // before anything else so that it overlaps the first loads of the streams
+        const uint32_t bytes = (uint32_t)cw * 8u;
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_a), "r"(bytes) : "memory");
+        asm volatile(
+            "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+            ::"r"(SmemAddr(xs)), "l"(x + c0), "r"(bytes), "r"(bar_a) : "memory");
+      }
+    }
+    // this warp's stream: two batches of loads in flight before the x tile is needed
+    const SellStream sd = streams[vi * NW + warp];
     const int Q = sd.q_total;
     const double* v = val + sd.voff + lane;
     const uint16_t* ix = idx + sd.ioff + lane * 4;
-    SellBatch ba, bb;
-    if (Q >= kBatch) LoadBatch<false>(ba, v, ix, 0, Q); else LoadBatch<true>(ba, v, ix, 0, Q);
-    if (t != cur_t) {
-      const int c0 = t * TW;
-      const int cw = min(TW, Cn - c0);
-      __syncthreads();  // every warp is done reading the previous tile (and sees the barrier init)
+    SellBatch<KB> ba, bb;
+    if (Q >= 2 * kBatch) {
+      LoadBatch<false>(ba, v, ix, 0, Q);
+      LoadBatch<false>(bb, v, ix, kBatch, Q);
+    } else {
+      LoadBatch<true>(ba, v, ix, 0, Q);
+      LoadBatch<true>(bb, v, ix, kBatch, Q);
+    }
+    SliceCursor c;
+    c.sl_len = sl_len; c.rowid = rowid; c.P = P;
+    c.cur = c.end = 0;
+    if (sd.ss_cnt > 0) c.Start(sd.ss_begin, sd.ss_cnt);
+    if (restage) {
       if (use_tma) {
-        // one TMA bulk copy of the x tile (cp.async.bulk, completion on an mbarrier)
-        const uint32_t bytes = (uint32_t)cw * 8u;
-        if (threadIdx.x == 0) {
-          asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_a), "r"(bytes) : "memory");
-          asm volatile(
-              "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-              ::"r"(SmemAddr(xs)), "l"(x + c0), "r"(bytes), "r"(bar_a) : "memory");
-        }
+        if (vi == v_lo) __syncthreads();  // the barrier init is visible to every thread
         uint32_t done = 0;
         while (!done) {
           asm volatile(
@@ -486,33 +521,37 @@ SellStreamKernel(int R, int Cn, int TW, const int32_t* __restrict__ cta_visit,
         }
         phase ^= 1u;
       } else {
-        for (int i = threadIdx.x; i < cw; i += kSellThreads) xs[i] = x[c0 + i];
+        for (int i = threadIdx.x; i < cw; i += NW * 32) xs[i] = x[c0 + i];
         __syncthreads();
       }
       cur_t = t;
+      if (TRACE && threadIdx.x == 0) trace[blockIdx.x * 4 + 1] = GlobalTimer();
     }
     if (sd.ss_cnt == 0) continue;
-    SliceCursor c;
-    c.sl_len = sl_len; c.rowid = rowid; c.Pt = P + (size_t)t * R; c.lane = lane;
-    c.Start(sd.ss_begin, sd.ss_cnt);
+    c.SkipEmpty();
     int q = 0;
-    // two batches in flight; full batches need no guards
-    while (q + 3 * kBatch <= Q) {
-      LoadBatch<false>(bb, v, ix, q + kBatch, Q);
+    // full batches need no guards
+    while (q + 4 * kBatch <= Q) {
       ConsumeBatch<false>(ba, xs, c, q, Q);
       LoadBatch<false>(ba, v, ix, q + 2 * kBatch, Q);
       ConsumeBatch<false>(bb, xs, c, q + kBatch, Q);
+      LoadBatch<false>(bb, v, ix, q + 3 * kBatch, Q);
       q += 2 * kBatch;
     }
-    // here ba holds batch q (fully inside the stream iff q + kBatch <= Q)
     while (q < Q) {
-      LoadBatch<true>(bb, v, ix, q + kBatch, Q);
       ConsumeBatch<true>(ba, xs, c, q, Q);
-      ba = bb;
-      q += kBatch;
+      LoadBatch<true>(ba, v, ix, q + 2 * kBatch, Q);
+      ConsumeBatch<true>(bb, xs, c, q + kBatch, Q);
+      LoadBatch<true>(bb, v, ix, q + 3 * kBatch, Q);
+      q += 2 * kBatch;
     }
     // rows after the last stored entry (empty in this tile)
-    while (c.ss < c.ss_end) c.Next();
+    while (c.cur < c.end) c.Next();
+    if (TRACE && lane == 0) {
+      const unsigned long long now = GlobalTimer();
+      atomicMin(&trace[blockIdx.x * 4 + 2], now);  // first warp done
+      atomicMax(&trace[blockIdx.x * 4 + 3], now);  // last warp done
+    }
   }
 }
 
@@ -522,6 +561,12 @@ SellStreamKernel(int R, int Cn, int TW, const int32_t* __restrict__ cta_visit,
 static void BuildSellStream(Ctx* ctx, const Csr& A, Sell* S) {
   const int R = A.m, Cn = A.n;
   S->version = 2;
+  // 24 warps: 80 registers per thread hold two batches of loads without spills; measured on
+  // B200 (1M x 100k, density 1e-3): 96.4 % of the HBM copy peak vs 96.1 % (32 warps, spills),
+  // 93.8 % (20), 86.2 % (16)
+  const int NW = getenv("EPS_SELL_WARPS") ? atoi(getenv("EPS_SELL_WARPS")) : 24;
+  EPS_CHECK(NW == 16 || NW == 20 || NW == 24 || NW == 32, "EPS_SELL_WARPS must be 16, 20, 24 or 32");
+  S->nw = NW;
   S->R = R; S->Cn = Cn; S->nnz = A.nnz;
   const int T = (Cn + kMaxTile - 1) / kMaxTile;
   int TW = (Cn + T - 1) / T;
@@ -538,7 +583,8 @@ static void BuildSellStream(Ctx* ctx, const Csr& A, Sell* S) {
   {
     DevBuf<int64_t> csum(ctx, TR);
     cub::CountingInputIterator<int64_t> cnt(0);
-    cub::TransformInputIterator<int64_t, CostOp, cub::CountingInputIterator<int64_t>> cost(cnt, CostOp{seglen.p});
+    cub::TransformInputIterator<int64_t, CostOp, cub::CountingInputIterator<int64_t>> cost(
+        cnt, CostOp{seglen.p, (int64_t)R, getenv("EPS_SELL_NOSTAGE") ? (int64_t)0 : (int64_t)8 * TW});
     size_t bytes = 0;
     CUDA_CHECK(cub::DeviceScan::InclusiveSum(nullptr, bytes, cost, csum.p, (int)TR, ctx->stream));
     DevBuf<char> tmp(ctx, bytes);
@@ -599,7 +645,7 @@ static void BuildSellStream(Ctx* ctx, const Csr& A, Sell* S) {
   {
     DevBuf<int64_t> vsize(ctx, n_slices + 1);
     vsize.zero();
-    StreamSliceLenKernel<<<(n_slices + 255) / 256, 256, 0, ctx->stream>>>(n_slices, vt, keys_out.p, S->sl_len.p, vsize.p);
+    StreamSliceLenKernel<<<(n_slices + 255) / 256, 256, 0, ctx->stream>>>(n_slices, NW, vt, keys_out.p, S->sl_len.p, vsize.p);
     size_t bytes = 0;
     CUDA_CHECK(cub::DeviceScan::ExclusiveSum(nullptr, bytes, vsize.p, S->voff.p, n_slices + 1, ctx->stream));
     DevBuf<char> tmp(ctx, bytes);
@@ -607,14 +653,14 @@ static void BuildSellStream(Ctx* ctx, const Csr& A, Sell* S) {
     S->voff.download(hv.data(), n_slices + 1);
   }
   // one stream per (visit, warp)
-  std::vector<SellStream> st((size_t)std::max(NV, 1) * 32);
+  std::vector<SellStream> st((size_t)std::max(NV, 1) * NW);
   int64_t ioff = 0;
   for (int v = 0; v < NV; v++) {
     const int n_sl = slice_base[v + 1] - slice_base[v];
-    for (int w = 0; w < 32; w++) {
-      SellStream& d = st[(size_t)v * 32 + w];
-      d.ss_begin = slice_base[v] + WarpPrefix(n_sl, w);
-      d.ss_cnt = WarpPrefix(n_sl, w + 1) - WarpPrefix(n_sl, w);
+    for (int w = 0; w < NW; w++) {
+      SellStream& d = st[(size_t)v * NW + w];
+      d.ss_begin = slice_base[v] + WarpPrefix(n_sl, w, NW);
+      d.ss_cnt = WarpPrefix(n_sl, w + 1, NW) - WarpPrefix(n_sl, w, NW);
       d.voff = hv[d.ss_begin];
       d.q_total = (int32_t)((hv[d.ss_begin + d.ss_cnt] - hv[d.ss_begin]) / 32);
       d.ioff = ioff;
@@ -631,15 +677,19 @@ static void BuildSellStream(Ctx* ctx, const Csr& A, Sell* S) {
   S->idx.zero();
   S->rowid.alloc(ctx, (size_t)std::max(n_slices, 1) * 32);
   StreamFillKernel<<<(n_slices + 7) / 8, 256, 0, ctx->stream>>>(
-      R, TW, n_slices, vt, S->visit_tile.p, S->streams.p, vals_out.p, segstart.p, seglen.p, A.col.p, A.val.p,
+      R, TW, n_slices, NW, vt, S->visit_tile.p, S->streams.p, vals_out.p, segstart.p, seglen.p, A.col.p, A.val.p,
       S->sl_len.p, S->voff.p, S->val.p, S->idx.p, S->rowid.p);
   CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
   CUDA_CHECK(cudaGetLastError());
   S->voff.release();  // only needed while building
   static bool attr_set = false;
   if (!attr_set) {
-    CUDA_CHECK(cudaFuncSetAttribute(SellStreamKernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    kMaxTile * 8 + 64));
+    const int smem = kMaxTile * 8 + 64;
+#define EPS_SELL_ATTR(NW) \
+    CUDA_CHECK(cudaFuncSetAttribute(SellStreamKernel<NW, 8, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); \
+    CUDA_CHECK(cudaFuncSetAttribute(SellStreamKernel<NW, 8, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    EPS_SELL_ATTR(16) EPS_SELL_ATTR(20) EPS_SELL_ATTR(24) EPS_SELL_ATTR(32)
+#undef EPS_SELL_ATTR
     attr_set = true;
   }
   S->built = true;
@@ -759,11 +809,53 @@ void SellApply(Ctx* ctx, const Sell& S, double alpha, const double* x, double be
     // pointer and the width of the last tile can break that
     const int last = S.Cn - (S.T - 1) * S.TW;
     const int use_tma = ((reinterpret_cast<uintptr_t>(x) & 15) == 0 && last % 2 == 0) ? 1 : 0;
-    if (S.version == 2)
-      SellStreamKernel<<<S.n_cta, kSellThreads, (size_t)S.TW * 8 + 64, ctx->stream>>>(
+    if (S.version == 2) {
+      // EPS_SELL_TRACE=<launch number>: per-CTA timeline of that launch on stderr (diagnostics)
+      static const int trace_at = getenv("EPS_SELL_TRACE") ? atoi(getenv("EPS_SELL_TRACE")) : -1;
+      static int launch_no = 0;
+      static DevBuf<unsigned long long> tbuf;
+      unsigned long long* trace = nullptr;
+      if (trace_at >= 0 && launch_no++ == trace_at) {
+        tbuf.alloc(ctx, (size_t)S.n_cta * 4);
+        std::vector<unsigned long long> init((size_t)S.n_cta * 4, 0ull);
+        for (int g = 0; g < S.n_cta; g++) init[g * 4 + 2] = ~0ull;
+        tbuf.upload(init.data(), init.size());
+        CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+        trace = tbuf.p;
+      }
+      using KernT = void (*)(int, int, int, const int32_t*, const int32_t*, const SellStream*, const int32_t*,
+                             const double*, const uint16_t*, const int32_t*, const double*, double*, int, const int*,
+                             unsigned long long*);
+      KernT kern = nullptr;
+      switch (S.nw) {
+        case 16: kern = trace ? SellStreamKernel<16, 8, true> : SellStreamKernel<16, 8, false>; break;
+        case 20: kern = trace ? SellStreamKernel<20, 8, true> : SellStreamKernel<20, 8, false>; break;
+        case 24: kern = trace ? SellStreamKernel<24, 8, true> : SellStreamKernel<24, 8, false>; break;
+        default: kern = trace ? SellStreamKernel<32, 8, true> : SellStreamKernel<32, 8, false>; break;
+      }
+      kern<<<S.n_cta, S.nw * 32, (size_t)S.TW * 8 + 64, ctx->stream>>>(
           S.R, S.Cn, S.TW, S.cta_visit.p, S.visit_tile.p, S.streams.p, S.sl_len.p, S.val.p, S.idx.p, S.rowid.p, x,
-          P, use_tma, skip);
-    else
+          P, use_tma, skip, trace);
+      if (trace) {
+        std::vector<unsigned long long> h((size_t)S.n_cta * 4);
+        tbuf.download(h.data(), h.size());
+        unsigned long long t0 = ~0ull;
+        for (int g = 0; g < S.n_cta; g++) if (h[g * 4]) t0 = std::min(t0, h[g * 4]);
+        std::vector<double> a, b, c, d;
+        for (int g = 0; g < S.n_cta; g++) {
+          if (!h[g * 4]) continue;
+          a.push_back((h[g * 4] - t0) * 1e-3);
+          b.push_back((h[g * 4 + 1] - t0) * 1e-3);
+          c.push_back((h[g * 4 + 2] - t0) * 1e-3);
+          d.push_back((h[g * 4 + 3] - t0) * 1e-3);
+        }
+        auto q = [](std::vector<double>& v, double f) { std::sort(v.begin(), v.end()); return v.empty() ? 0.0 : v[(size_t)(f * (v.size() - 1))]; };
+        fprintf(stderr, "[sell trace] R=%d Cn=%d T=%d ctas=%zu us since first CTA start: start min/med/max %.1f %.1f %.1f | "
+                "x staged %.1f %.1f %.1f | first warp done %.1f %.1f %.1f | last warp done %.1f %.1f %.1f\n",
+                S.R, S.Cn, S.T, a.size(), q(a, 0), q(a, .5), q(a, 1), q(b, 0), q(b, .5), q(b, 1), q(c, 0), q(c, .5), q(c, 1),
+                q(d, 0), q(d, .5), q(d, 1));
+      }
+    } else
       SellSpmvKernel<<<S.n_cta, kSellThreads, (size_t)S.TW * 8 + 64, ctx->stream>>>(
           S.R, S.Cn, S.TW, S.RR, S.rows_per / 32, S.cta_begin.p, S.sl_len.p, S.voff.p, S.ioff.p, S.val.p, S.idx.p,
           S.rowid.p, x, P, use_tma, skip);
