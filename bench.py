@@ -45,6 +45,9 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--ref-m", type=int, default=30_000)
     ap.add_argument("--ref-n", type=int, default=3_000)
+    # --impl reference: a larger sample (Init = dense n x n inverse, ~35 s per repetition at n = 6000)
+    ap.add_argument("--ref-arm-m", type=int, default=60_000)
+    ap.add_argument("--ref-arm-n", type=int, default=6_000)
     return ap.parse_args()
 
 
@@ -151,9 +154,9 @@ def main_reference(args):
         return
     workload = "sparse lasso %dx%d CSR density %g fp64" % (args.m, args.n, args.density)
     steps_total, loop_total, init_total, last = 0, 0.0, 0.0, None
-    reps = max(1, min(args.steps, 3))
+    reps = 1  # one whole solve of the sample (Init ~1-2 min on one core + ~20 iterations)
     for _ in range(reps):
-        last = run_reference_sample(args.ref_m, args.ref_n, args.density)
+        last = run_reference_sample(args.ref_arm_m, args.ref_arm_n, args.density)
         steps_total += last["iterations"]
         loop_total += last["loop_s"]
         init_total += last["init_s"]

@@ -4,6 +4,7 @@
 //   SparseMatrixImpl::Apply  src/epsilon/linear/sparse_matrix_impl.h:24    (Eigen CSC * x)
 //   DiagonalMatrixImpl::Apply diagonal_matrix_impl.h:23, ScalarMatrixImpl::Apply scalar_matrix_impl.h:24
 // All arithmetic is fp64 (LinearMapImpl::Scalar = double, linear_map.h:35); indices int32.
+#include <chrono>
 #include <cub/cub.cuh>
 
 #include "device.cuh"
@@ -464,6 +465,13 @@ int eps_map_csc(eps_ctx* ctx, int m, int n, int64_t nnz, const int32_t* colptr,
   CUDA_CHECK(cudaSetDevice(ctx->c.device));
   auto d = std::make_shared<MapData>();
   d->ctx = &ctx->c; d->kind = MK_SPARSE; d->m = m; d->n = n;
+  // EPS_TIMING=1: wall time of the ingest phases on stderr
+  static const bool timing = getenv("EPS_TIMING") != nullptr;
+  auto now = [&]() { cudaStreamSynchronize(ctx->c.stream); return std::chrono::steady_clock::now(); };
+  auto ms = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) {
+    return std::chrono::duration<double, std::milli>(b - a).count();
+  };
+  const auto t0 = timing ? now() : std::chrono::steady_clock::time_point();
   // CSR of A' is the wire layout itself.
   Csr& t = d->csr_t;
   t.m = n; t.n = m; t.nnz = nnz;
@@ -474,13 +482,18 @@ int eps_map_csc(eps_ctx* ctx, int m, int n, int64_t nnz, const int32_t* colptr,
   t.col.upload(rowidx, nnz);
   t.val.upload(vals, nnz);
   CUDA_CHECK(cudaStreamSynchronize(ctx->c.stream));
+  const auto t1 = timing ? now() : t0;
   TransposeCsrOnDevice(&ctx->c, t, &d->csr);
+  const auto t2 = timing ? now() : t0;
   const char* fmt = getenv("EPS_SPARSE_FORMAT");  // "csr" forces the plain CSR kernel
   const bool want_sell = fmt ? strcmp(fmt, "csr") != 0 : true;
   if (want_sell && (nnz >= ((int64_t)1 << 18) || (fmt && strcmp(fmt, "sell") == 0)) && m > 0 && n > 0) {
     BuildSell(&ctx->c, d->csr, &d->sell);
     BuildSell(&ctx->c, d->csr_t, &d->sell_t);
   }
+  if (timing)
+    fprintf(stderr, "[eps timing] map_csc %dx%d nnz=%lld: upload %.1f ms, transpose %.1f ms, sell x2 %.1f ms\n", m, n,
+            (long long)nnz, ms(t0, t1), ms(t1, t2), ms(t2, now()));
   if (nnz <= (int64_t)4 << 20) {
     d->h_colptr.assign(colptr, colptr + n + 1);
     d->h_rowidx.assign(rowidx, rowidx + nnz);
