@@ -234,9 +234,19 @@ def main_ours(args):
     params = {"cg_tol": args.cg_tol}
 
     # ---- e2e: whole solve from host buffers through the C ABI -----------------------------
+    # The host copy of the matrix (the wire CSC arrays) lives in page-locked memory, as the
+    # contract asks: the library then DMAs it without a staging copy (ctx.cu, UploadBytes).
+    a.sort_indices()
+    pinned = [torch.from_numpy(v).pin_memory() for v in (a.data, a.indices, a.indptr)]
+    a.data, a.indices, a.indptr = (t.numpy() for t in pinned)
     e2e = None
     h2d_bytes = 12 * nnz_local + 4 * (args.n + 1) + 8 * m_local
     if not args.no_e2e:
+        # one untimed whole solve first: CUDA module loading, first-touch allocations and the
+        # cuda/cub kernels of the ingest path are a per-process cost, not a per-solve one
+        with ProxADMMSolver(prob, params, ctx=ctx, sharded_args=sharded) as s0:
+            s0.solve()
+        ctx.synchronize()
         barrier()
         t0 = time.time()
         s = ProxADMMSolver(prob, params, ctx=ctx, sharded_args=sharded)
@@ -248,6 +258,7 @@ def main_ours(args):
         obj = info["objective"](x)
         e2e = {"value": iters / t_e2e, "unit": "iterations/s",
                "h2d_bytes_per_step": h2d_bytes / iters, "d2h_bytes_per_step": 8 * 2 * args.n / iters,
+               "warmup_solves": 1, "host_buffers": "pinned (cudaHostAlloc)",
                "time_to_tol_s": t_e2e, "init_s": st["init_ms"] / 1e3, "loop_s": st["loop_ms"] / 1e3,
                "iterations": iters, "num_iterations": st["num_iterations"], "state": st["state"],
                "cg_iterations": st["cg_iterations"], "objective": obj,

@@ -106,6 +106,15 @@ void UploadBytes(Ctx* ctx, void* dst, const void* src, size_t bytes) {
     CUDA_CHECK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
     return;
   }
+  {
+    // page-locked source (cudaHostAlloc / cudaHostRegister by the caller): one DMA, no staging
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, src) == cudaSuccess && at.type == cudaMemoryTypeHost) {
+      CUDA_CHECK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+      return;
+    }
+    cudaGetLastError();  // an unregistered pointer is not an error here
+  }
   if (!ctx->staging) {
     auto* st = new Ctx::Staging();
     ctx->staging = st;
