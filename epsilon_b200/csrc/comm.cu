@@ -104,11 +104,13 @@ void AllReduceSum(Ctx* ctx, double* buf, int64_t n) {
 }
 
 // ---- one-shot peer all-reduce: buffers mapped into every rank through CUDA IPC -------------
-// Layout of each rank's block: [flags: 2*G u64, padded to 4 KB][counter][receive: 2*G*n f64].
+// Layout of each rank's block: [flags: 2*G u64 | counter at 2 KB | per-CTA flags 2*G*kPeerMaxCtas u64 at 4 KB,
+// head padded to 64 KB][receive: 2*G*n f64].
 static void PeerSetup(Ctx* ctx, int64_t n, PeerBuf* out) {
   out->ready = false;
   const int G = ctx->n_ranks;
-  const size_t head = 4096;
+  const size_t head = 65536;
+  static_assert(4096 + 2 * kMaxRanks * kPeerMaxCtas * 8 <= 65536, "peer header");
   const size_t bytes = head + sizeof(double) * 2 * (size_t)G * n;
   CUDA_CHECK(cudaMalloc(&out->block, bytes));
   ctx->bytes_allocated += bytes;
@@ -150,6 +152,7 @@ static void PeerSetup(Ctx* ctx, int64_t n, PeerBuf* out) {
   for (int r = 0; r < G; r++) {
     char* base = static_cast<char*>(r == ctx->rank ? out->block : out->mapped[r]);
     out->x.flag[r] = reinterpret_cast<unsigned long long*>(base);
+    out->x.cflag[r] = reinterpret_cast<unsigned long long*>(base + 4096);
     out->x.recv[r] = reinterpret_cast<double*>(base + head);
   }
   out->counter = reinterpret_cast<unsigned*>(static_cast<char*>(out->block) + 2048);

@@ -222,9 +222,11 @@ void BuildSell(Ctx* ctx, const Csr& A, Sell* S);
 // that peer; the consumer waits for its G local flags and adds the G slots in rank order, so
 // all ranks obtain bit-identical sums.  Passed to kernels by value.
 constexpr int kMaxRanks = 8;
+constexpr int kPeerMaxCtas = 256;  // CTAs of the fused exchange kernel (one per SM)
 struct PeerXchg {
   double* recv[kMaxRanks] = {};              // recv[r]: rank r's buffer [2][G][n], mapped here
   unsigned long long* flag[kMaxRanks] = {};  // flag[r]: rank r's flags [2][G]
+  unsigned long long* cflag[kMaxRanks] = {}; // cflag[r]: rank r's per-CTA flags [2][G][kPeerMaxCtas]
   int G = 0, rank = 0;
   int64_t n = 0;   // slot stride (capacity); vectors of up to n entries fit
 };
@@ -252,6 +254,9 @@ struct SpmvExtra {
 };
 void SellApply(Ctx* ctx, const Sell& S, double alpha, const double* x, double beta, double* y, int kclass,
                const SpmvExtra* ex = nullptr);
+// The stream kernel alone: returns the T x R partial planes (context scratch, valid until the
+// next sparse apply); y = alpha * sum_t planes[t] is left to the caller's consumer kernel.
+const double* SellApplyPlanes(Ctx* ctx, const Sell& S, const double* x, int kclass, const int* skip);
 void DenseGemv(Ctx* ctx, const double* A, int lda, int m, int n, bool trans, double alpha,
                const double* x, double beta, double* y, int tri = 0);
 

@@ -132,6 +132,110 @@ CgTailKernel(int64_t n, double* __restrict__ w, double* __restrict__ p, double* 
   }
 }
 
+// The reduction of the second SpMV pass, the cross-GPU exchange and the CG update as ONE
+// cooperative kernel (one CTA per SM, every CTA owns the same contiguous slice of the n-vector
+// on every rank):
+//   part_i  = alpha * sum_t planes[t][i]                     (this rank's rows of H'(H p))
+//   G > 1 : part is pushed into slot [parity][rank] of every rank over NVLink (P2P stores);
+//           the CTA then raises ITS flag [parity][rank][cta] on every rank and waits for the G
+//           flags of the same slice -- no grid-wide or device-wide wait for the exchange, no
+//           arrival counter: a slice is summed (in rank order, identical bits everywhere) as soon
+//           as its G parts have landed
+//   w = sum + d.*p ; then the CG update of CgTailKernel.
+// Once `done` is raised only the flag handshake is executed, so that no rank can run two
+// exchanges ahead of a reader of the double-buffered slots.
+__global__ void __launch_bounds__(kTailBlock)
+CgFusedTailKernel(int64_t n, int T, const double* __restrict__ planes, double alpha,
+                  double* __restrict__ w, double* __restrict__ p, double* __restrict__ x,
+                  double* __restrict__ r, double* scal, double* partials, int* done,
+                  KktSolver::CgResult* ring, long long seq, PeerXchg px, unsigned long long xseq,
+                  const double* __restrict__ dg) {
+  namespace cg = cooperative_groups;
+  __shared__ double smem[64];
+  const int G = gridDim.x;
+  const int c = blockIdx.x;
+  const int parity = (int)(xseq & 1ull);
+  const bool finished = *done != 0;  // uniform: only ever written by the last phase of an earlier launch
+  // slice of this CTA (even length so that the rows stay 16-byte aligned)
+  int64_t per = (n + G - 1) / G;
+  per = (per + 1) & ~(int64_t)1;
+  const int64_t lo = min(n, (int64_t)c * per), hi = min(n, lo + per);
+  if (px.G > 1) {
+    if (!finished) {
+      for (int64_t i = lo + threadIdx.x; i < hi; i += kTailBlock) {
+        double s = 0.0;
+        for (int t = 0; t < T; t++) s += planes[(size_t)t * n + i];
+        const double out = alpha * s;
+        const size_t slot = ((size_t)parity * px.G + px.rank) * px.n + i;
+        for (int k = 0; k < px.G; k++) {
+          const int q = (px.rank + k) % px.G;  // start with the local copy, spread the peers
+          px.recv[q][slot] = out;
+        }
+      }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) __threadfence_system();  // cumulative: orders the CTA's remote stores
+    __syncthreads();
+    if (threadIdx.x < px.G)
+      StReleaseSys(px.cflag[threadIdx.x] + ((size_t)parity * px.G + px.rank) * kPeerMaxCtas + c, xseq);
+    if (threadIdx.x < px.G) {
+      const unsigned long long* f = px.cflag[px.rank] + ((size_t)parity * px.G + threadIdx.x) * kPeerMaxCtas + c;
+      while (LdAcquireSys(f) < xseq) {}
+    }
+    __syncthreads();
+  }
+  if (finished) return;
+  cg::grid_group grid = cg::this_grid();
+  const double rr = scal[0];
+  const double thresh = scal[1];
+  double v[1] = {0.0};
+  if (px.G > 1) {
+    for (int64_t i = lo + threadIdx.x; i < hi; i += kTailBlock) {
+      const double pi = p[i];
+      const double wi = PeerSum(px, xseq, i) + dg[i] * pi;
+      w[i] = wi;
+      v[0] += pi * wi;
+    }
+  } else {
+    for (int64_t i = lo + threadIdx.x; i < hi; i += kTailBlock) {
+      double s = 0.0;
+      for (int t = 0; t < T; t++) s += planes[(size_t)t * n + i];
+      const double pi = p[i];
+      const double wi = alpha * s + dg[i] * pi;
+      w[i] = wi;
+      v[0] += pi * wi;
+    }
+  }
+  BlockSum<1>(v, smem);
+  if (threadIdx.x == 0) partials[blockIdx.x] = v[0];
+  grid.sync();
+  const double pw = SumPartials(partials, G, smem);
+  const double a = pw != 0.0 ? rr / pw : 0.0;
+  v[0] = 0.0;
+  for (int64_t i = lo + threadIdx.x; i < hi; i += kTailBlock) {
+    x[i] += a * p[i];
+    const double t = r[i] - a * w[i];
+    r[i] = t;
+    v[0] += t * t;
+  }
+  BlockSum<1>(v, smem);
+  if (threadIdx.x == 0) partials[G + blockIdx.x] = v[0];
+  grid.sync();
+  const double rr_new = SumPartials(partials + G, G, smem);
+  const double b = rr != 0.0 ? rr_new / rr : 0.0;
+  for (int64_t i = lo + threadIdx.x; i < hi; i += kTailBlock) p[i] = r[i] + b * p[i];
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    const int conv = sqrt(rr_new) <= thresh ? 1 : 0;
+    scal[0] = rr_new;
+    if (conv) *done = 1;
+    KktSolver::CgResult* e = &ring[seq % kCgRing];
+    e->rr = rr_new;
+    e->converged = conv;
+    __threadfence_system();
+    *reinterpret_cast<volatile long long*>(&e->seq) = seq;
+  }
+}
+
 __global__ void InvertKernel(int64_t n, const double* __restrict__ d, double* __restrict__ out, int* bad) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
@@ -357,10 +461,17 @@ void KktSolver::Init(const std::vector<double>& g_host, const std::vector<double
              H.blks[0].row_off == 0 && H.blks[0].col_off == 0 && H.blks[0].m() == rows_h &&
              H.blks[0].n() == n && H.blks[0].map->sell.built && H.blks[0].map->sell_t.built;
     if (fast_h && h_sharded) peer = PeerEnsure(ctx, n);
+    fused_tail = fast_h && (!h_sharded || peer) && tail_grid <= kPeerMaxCtas && !getenv("EPS_NO_FUSED_TAIL");
+    if (fused_tail) {
+      int per_sm = 0;
+      CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, CgFusedTailKernel, kTailBlock, 0));
+      EPS_CHECK(per_sm >= 1, "CgFusedTailKernel does not fit an SM");
+    }
     CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
     description = Format("kkt=CG n=%lld rows_h=%lld tol=%.1e%s%s%s", (long long)n, (long long)rows_h, cg_tol,
                          h_sharded ? " sharded" : "", fast_h ? " fused-matvec" : "",
                          peer ? " peer-allreduce" : "");
+    if (fused_tail) description += " fused-tail";
   } else {
     throw Error(EPS_ERR_INVALID, Format("unknown kkt mode %d", mode));
   }
@@ -463,6 +574,38 @@ void KktSolver::Solve(const double* rhs, double* x) {
         // profile mode times every launch with its own event pair: no speculation there, so
         // that no-op launches do not enter the per-class statistics
         if (ctx->profile && wait_result(base + it).converged != 0.0) { converged = true; break; }
+        if (fused_tail) {
+          // first pass with its reduction, second pass as partial planes, then ONE kernel for
+          // the plane reduction, the cross-GPU exchange and the CG update
+          const Blk& b = H.blks[0];
+          const MapData& M = *b.map;
+          const Sell& S1 = b.trans ? M.sell_t : M.sell;
+          const Sell& S2 = b.trans ? M.sell : M.sell_t;
+          SpmvExtra e1;
+          e1.skip = cg_done.p;
+          SellApply(ctx, S1, b.scale, cg_p.p, 0.0, th1.p, b.trans ? KC_SPMV_T : KC_SPMV_N, &e1);
+          const double* planes = SellApplyPlanes(ctx, S2, th1.p, b.trans ? KC_SPMV_N : KC_SPMV_T, cg_done.p);
+          {
+          ProfScope ps(ctx, peer ? KC_ALLREDUCE : KC_VEC, 8.0 * S2.T * n + 72.0 * n);
+          int64_t nn = n;
+          int T = S2.T;
+          double alpha = alpha2 * b.scale;
+          double* wp = cg_w.p;
+          double *pp = cg_p.p, *xp = x, *rp = cg_r.p, *sp = scal.p, *part = cg_partials.p;
+          int* dp = cg_done.p;
+          CgResult* rg = ring;
+          long long seq = base + it + 1;
+          PeerXchg pxv = peer ? peer->x : PeerXchg();
+          unsigned long long xs = peer ? ++peer->seq : 0ull;
+          const double* dgp = ddiag.p;
+          void* args[] = {&nn, &T, &planes, &alpha, &wp, &pp, &xp, &rp, &sp, &part, &dp, &rg, &seq, &pxv, &xs, &dgp};
+          CUDA_CHECK(cudaLaunchCooperativeKernel((const void*)CgFusedTailKernel, dim3(tail_grid),
+                                                 dim3(kTailBlock), args, 0, ctx->stream));
+          ctx->count_launch();
+          }
+          if (wait_result(base + it).converged != 0.0) { converged = true; break; }
+          continue;
+        }
         MatVec(cg_p.p, cg_w.p, cg_done.p);
         {
           ProfScope ps(ctx, KC_VEC, 72.0 * n);

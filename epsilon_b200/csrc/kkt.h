@@ -39,6 +39,7 @@ struct KktSolver {
   DevBuf<double> cg_partials;
   int tail_grid = 0;
   bool fast_h = false;           // H = one SELL block, A'A diagonal: fused matvec
+  bool fused_tail = false;       // plane reduction + exchange + CG update in one kernel (CgFusedTailKernel)
   PeerBuf* peer = nullptr;       // row-sharded: the context's one-shot NVLink all-reduce buffers (not owned)
   unsigned long long pending_seq = 0;  // exchange the next consumer kernel has to complete (0: none)
   double cg_tol = 1e-12;

@@ -798,10 +798,7 @@ void BuildSell(Ctx* ctx, const Csr& A, Sell* S) {
   S->built = true;
 }
 
-void SellApply(Ctx* ctx, const Sell& S, double alpha, const double* x, double beta, double* y, int kclass,
-               const SpmvExtra* ex) {
-  const int* skip = ex ? ex->skip : nullptr;
-  if (S.R == 0) return;
+static double* SellLaunch(Ctx* ctx, const Sell& S, const double* x, int kclass, const int* skip) {
   double* P = GrowScratch(ctx, &ctx->sell_scratch, (size_t)S.T * S.R);
   {
     ProfScope ps(ctx, kclass, 12.0 * S.nnz + 4.0 * (S.R + 1) + 8.0 * S.Cn + 8.0 * S.R);
@@ -861,6 +858,19 @@ void SellApply(Ctx* ctx, const Sell& S, double alpha, const double* x, double be
           S.rowid.p, x, P, use_tma, skip);
     ctx->count_launch();
   }
+  return P;
+}
+
+const double* SellApplyPlanes(Ctx* ctx, const Sell& S, const double* x, int kclass, const int* skip) {
+  EPS_CHECK(S.R > 0, "empty sparse map");
+  return SellLaunch(ctx, S, x, kclass, skip);
+}
+
+void SellApply(Ctx* ctx, const Sell& S, double alpha, const double* x, double beta, double* y, int kclass,
+               const SpmvExtra* ex) {
+  const int* skip = ex ? ex->skip : nullptr;
+  if (S.R == 0) return;
+  double* P = SellLaunch(ctx, S, x, kclass, skip);
   if (ex && ex->publish) {
     EPS_CHECK(beta == 0.0 && ex->publish->n >= S.R, "publishing apply: beta must be 0 and the vector must fit the slots");
     ProfScope ps(ctx, KC_ALLREDUCE, 8.0 * S.T * S.R + 8.0 * S.R * ex->publish->G);
