@@ -304,23 +304,32 @@ __global__ void CutKernel(int64_t TR, int G, const int64_t* __restrict__ csum, i
   cut[g] = (int32_t)lo;
 }
 
+// Rows are sorted by length inside windows of kSortWindow consecutive rows of a visit, not
+// over the whole visit: a warp's slices then walk the visit's rows window by window, so the
+// 8-byte partial sums a CTA scatters into P fall into a few 32 KB windows at a time and complete
+// their 32-byte sectors in L2 before eviction.  (Sorted over a 108k-row visit -- logreg 2M x 200k,
+// 128 MB of partial planes -- the half-written sectors were evicted by the matrix stream:
+// 73 % of the HBM peak instead of 87 %.)
+constexpr int kSortWindow = 4096;
+
 __global__ void VisitKeysKernel(int64_t TR, VisitTab vt, const int32_t* __restrict__ seglen,
-                                uint32_t* __restrict__ keys, int32_t* __restrict__ vals) {
+                                uint64_t* __restrict__ keys, int32_t* __restrict__ vals) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= TR) return;
   const int v = UpperBound(vt.lin0, vt.n_visits, (int)i) - 1;
-  keys[i] = ((uint32_t)v << 16) | (uint32_t)(0xFFFF - seglen[i]);
+  const uint64_t window = (uint64_t)(((int)i - vt.lin0[v]) / kSortWindow);
+  keys[i] = ((uint64_t)v << 40) | (window << 16) | (uint64_t)(0xFFFF - seglen[i]);
   vals[i] = (int32_t)i;
 }
 
-__global__ void StreamSliceLenKernel(int n_slices, int NW, VisitTab vt, const uint32_t* __restrict__ skeys,
+__global__ void StreamSliceLenKernel(int n_slices, int NW, VisitTab vt, const uint64_t* __restrict__ skeys,
                                      int32_t* __restrict__ sl_len, int64_t* __restrict__ vsize) {
   const int s = blockIdx.x * blockDim.x + threadIdx.x;
   if (s >= n_slices) return;
   const int v = UpperBound(vt.slice_base, vt.n_visits, s) - 1;
   const int j = s - vt.slice_base[v];
   const int n_sl = vt.slice_base[v + 1] - vt.slice_base[v];
-  const int len = 0xFFFF - (int)(skeys[vt.lin0[v] + 32 * j] & 0xFFFF);
+  const int len = 0xFFFF - (int)(skeys[vt.lin0[v] + 32 * j] & 0xFFFFull);
   const int ss = vt.slice_base[v] + StreamPos(n_sl, j, NW);
   sl_len[ss] = len;
   vsize[ss] = 32 * (int64_t)len;
@@ -614,7 +623,7 @@ static void BuildSellStream(Ctx* ctx, const Csr& A, Sell* S) {
   cta_visit[G] = NV;
   lin0.push_back((int32_t)TR);
   slice_base.push_back(n_slices);
-  EPS_CHECK(NV < 65536, "too many SELL visits (%d)", NV);
+  EPS_CHECK(NV < (1 << 23), "too many SELL visits (%d)", NV);
   S->n_cta = G; S->n_visits = NV; S->n_slices = n_slices;
   DevBuf<int32_t> d_lin0(ctx, NV + 1), d_sbase(ctx, NV + 1);
   d_lin0.upload(lin0.data(), NV + 1);
@@ -627,15 +636,17 @@ static void BuildSellStream(Ctx* ctx, const Csr& A, Sell* S) {
 
   // sort the rows of every visit by length (descending, stable)
   DevBuf<int32_t> vals_in(ctx, TR), vals_out(ctx, TR);
-  DevBuf<uint32_t> keys_in(ctx, TR), keys_out(ctx, TR);
+  DevBuf<uint64_t> keys_in(ctx, TR), keys_out(ctx, TR);
   VisitKeysKernel<<<(unsigned)((TR + 255) / 256), 256, 0, ctx->stream>>>(TR, vt, seglen.p, keys_in.p, vals_in.p);
   {
+    int end_bit = 41;
+    while (end_bit < 64 && ((int64_t)1 << (end_bit - 40)) <= NV) end_bit++;
     size_t bytes = 0;
     CUDA_CHECK(cub::DeviceRadixSort::SortPairs(nullptr, bytes, keys_in.p, keys_out.p, vals_in.p, vals_out.p,
-                                               (int)TR, 0, 32, ctx->stream));
+                                               (int)TR, 0, end_bit, ctx->stream));
     DevBuf<char> tmp(ctx, bytes);
     CUDA_CHECK(cub::DeviceRadixSort::SortPairs(tmp.p, bytes, keys_in.p, keys_out.p, vals_in.p, vals_out.p,
-                                               (int)TR, 0, 32, ctx->stream));
+                                               (int)TR, 0, end_bit, ctx->stream));
     CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
   }
   // slice lengths in stream order and their value offsets
