@@ -30,6 +30,25 @@ void eps_solver::RunStages(const double* yo, double* yn) {
       case ST_TV:
         Tv1dProxStep(ctx, ops[st.members[0]].seg, consts.p, u.p, yo, yn, x.p, st.tv_work.p);
         break;
+      case ST_VEC: {
+        // general VectorProx reduction around a multi-argument operator (vector_prox.cc:131-137)
+        ProxOp& op = ops[st.members[0]];
+        double* us = u.p + op.span_lo;
+        double* xi = x.p + op.x_off;
+        VecAxpby(ctx, op.span_len, 1.0, us, 1.0, yo + op.y_off, us);      // w = u + y_i
+        op.A.ApplyT(us, op.vtmp.p);                                       // A'w
+        op.Hop.Apply(op.vtmp.p, op.vbuf.p);                               // H A'w
+        const double* g = op.g_off >= 0 ? consts.p + op.g_off : nullptr;
+        if (g) VecAxpby(ctx, op.rows_h, op.vec_bg, op.vbuf.p, 1.0, g, op.vbuf.p);
+        else VecScale(ctx, op.rows_h, op.vec_bg, op.vbuf.p, op.vbuf.p);
+        VecOpApply(ctx, op.vdesc, op.vbuf.p, &op.vwork);
+        if (g) VecAxpby(ctx, op.rows_h, 1.0, op.vbuf.p, -1.0, g, op.vbuf.p);
+        op.Hop.ApplyT(op.vbuf.p, xi);                                     // x = (1/beta) H'(x' - g)
+        VecScale(ctx, op.n, op.vec_cinv, xi, xi);
+        op.A.Apply(xi, yn + op.y_off);                                    // y_i = A x_i
+        VecAxpby(ctx, op.span_len, 1.0, us, -1.0, yn + op.y_off, us);     // u = w - y_i
+        break;
+      }
       case ST_KKT: {
         ProxOp& op = ops[st.members[0]];
         double* us = u.p + op.span_lo;

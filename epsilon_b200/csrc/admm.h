@@ -6,7 +6,7 @@
 
 namespace eps {
 
-enum StageKind { ST_ELEM = 0, ST_NORM2 = 1, ST_TV = 2, ST_KKT = 3 };
+enum StageKind { ST_ELEM = 0, ST_NORM2 = 1, ST_TV = 2, ST_KKT = 3, ST_VEC = 4 };
 
 // One f_i after Init.
 struct ProxOp {
@@ -22,6 +22,15 @@ struct ProxOp {
   double a = 0;
   std::unique_ptr<KktSolver> kkt;
   ElemSeg seg;                  // elementwise / block / tv operators
+  // multi-argument / sort-based vector operators (ST_VEC): the general form of the VectorProx
+  // scalar reduction, v = (beta/gamma) H A'w + g, x = (1/beta) H'(x' - g)  (vector_prox.cc:59-67,131-137)
+  BlockOp Hop;
+  int64_t rows_h = 0;
+  double vec_bg = 0, vec_cinv = 0;
+  int64_t g_off = -1;           // g in the constant arena
+  VecOpDesc vdesc;
+  VecOpWork vwork;
+  DevBuf<double> vbuf, vtmp;    // stacked argument (rows_h), A'w (n)
 };
 
 struct Stage {

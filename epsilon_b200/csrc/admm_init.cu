@@ -77,6 +77,8 @@ const char* TypeName(int t) {
     case EPS_PROX_SUM_NEG_LOG: return "SUM_NEG_LOG";
     case EPS_PROX_SUM_QUANTILE: return "SUM_QUANTILE";
     case EPS_PROX_NORM_2: return "NORM_2";
+    case EPS_PROX_MAX: return "MAX";
+    case EPS_PROX_SUM_KL_DIV: return "SUM_KL_DIV";
     case EPS_PROX_TOTAL_VARIATION_1D: return "TOTAL_VARIATION_1D";
     default: return "?";
   }
@@ -181,7 +183,8 @@ void eps_solver::Init(const eps_problem& original) {
     ProxOp& op = ops[i];
     const ProxFn& f = p.prox[i];
     op.type = f.type;
-    EPS_CHECK(!f.epigraph, "epigraph operators are outside the configured hot path (prox %d)", i);
+    EPS_CHECK(!f.epigraph || IsVecOpType(f.type, true),
+              "prox %d: the epigraph form of type %d has no device operator", i, f.type);
     for (size_t v = 0; v < vars.size(); v++)
       if (var_owner[v] == i) op.vars.push_back((int)v);
     std::sort(op.vars.begin(), op.vars.end(),
@@ -247,7 +250,64 @@ void eps_solver::Init(const eps_problem& original) {
   for (int i = 0; i < N; i++) {
     ProxOp& op = ops[i];
     const ProxFn& f = p.prox[i];
-    if (IsKktType(f.type)) {
+    if (IsVecOpType(f.type, f.epigraph)) {
+      // VectorProx::InitScalar (vector_prox.cc:51-70) with several arguments: every argument is
+      // a scalar multiple of one whole variable; H'H = beta I and H A'A H' = gamma I.
+      BlockOp& H = Hs[i];
+      EPS_CHECK(rows_h[i] == op.n, "prox %d (%s): arguments have %lld rows, variables %lld entries", i,
+                TypeName(f.type), (long long)rows_h[i], (long long)op.n);
+      std::vector<double> dh, da;
+      H.Compile();
+      EPS_CHECK(H.GramDiagonal(&dh) && op.A.GramDiagonal(&da),
+                "prox %d (%s): H'H and A'A must be diagonal", i, TypeName(f.type));
+      for (auto& b : H.blks)
+        EPS_CHECK(b.map->kind == MK_SCALAR && b.m() == b.n(),
+                  "prox %d (%s): every argument must be a scalar multiple of one variable", i, TypeName(f.type));
+      // with scalar blocks H is a signed scaled permutation: H A'A H' = diag(dh .* da) permuted
+      const double beta = dh[0], gamma = dh[0] * da[0];
+      for (int64_t j = 0; j < op.n; j++)
+        EPS_CHECK(dh[j] == beta && dh[j] * da[j] == gamma,
+                  "prox %d (%s): affine transformation is not scalar (diagonal case is not supported)", i,
+                  TypeName(f.type));
+      EPS_CHECK(beta > 0 && gamma > 0, "prox %d: H'H = %g, H A'A H' = %g", i, beta, gamma);
+      op.Hop.ctx = ctx; op.Hop.rows = H.rows; op.Hop.cols = H.cols; op.Hop.blks = H.blks;
+      op.Hop.Compile();
+      op.rows_h = rows_h[i];
+      op.vec_bg = beta / gamma;
+      op.vec_cinv = 1 / beta;
+      VecOpDesc& d = op.vdesc;
+      d.type = f.type;
+      d.epigraph = f.epigraph;
+      d.n0 = f.args[0].rows;
+      d.rows = rows_h[i];
+      d.lam = f.alpha * beta * beta / gamma;
+      d.zone_m = f.type == EPS_PROX_SUM_DEADZONE ? f.zone_m : 0.0;
+      d.zone_alpha = 1; d.zone_beta = f.type == EPS_PROX_SUM_HINGE ? 0 : 1;
+      if (f.type == EPS_PROX_SUM_QUANTILE) {
+        EPS_CHECK(f.q_alpha.size() == 1 && f.q_beta.size() == 1,
+                  "SUM_QUANTILE epigraph: only constant alpha/beta (the reference indexes them by the "
+                  "position in its permuted work array, scaled_zone.cc:238-252)");
+        d.zone_alpha = f.q_alpha[0];
+        d.zone_beta = f.q_beta[0];
+      }
+      if (f.epigraph)
+        EPS_CHECK(f.args.size() == 2 && f.args[1].rows == 1, "prox %d (%s): epigraph form takes (x, t)", i,
+                  TypeName(f.type));
+      if (f.type == EPS_PROX_SUM_KL_DIV)
+        EPS_CHECK(f.args.size() == 2 && f.args[0].rows == f.args[1].rows, "SUM_KL_DIV takes two equal-sized arguments");
+      if (f.type == EPS_PROX_MAX && !f.epigraph) EPS_CHECK(f.args.size() == 1, "MAX takes one argument");
+      op.g_off = -1;
+      if (!g_hosts[i].empty()) {
+        op.g_off = (int64_t)consts_host.size();
+        consts_host.insert(consts_host.end(), g_hosts[i].begin(), g_hosts[i].end());
+      }
+      op.vbuf.alloc(ctx, op.rows_h);
+      op.vtmp.alloc(ctx, op.n);
+      VecOpInit(ctx, d, &op.vwork);
+      description += Format("prox %d %s%s rows=%lld span=[%lld,+%lld) lambda=%.6g beta=%g gamma=%g\n", i,
+                            TypeName(f.type), f.epigraph ? " (epigraph)" : "", (long long)op.rows_h,
+                            (long long)op.span_lo, (long long)op.span_len, d.lam, beta, gamma);
+    } else if (IsKktType(f.type)) {
       auto k = std::make_unique<KktSolver>();
       k->ctx = ctx;
       k->mode = params.kkt_mode;
@@ -345,7 +405,8 @@ void eps_solver::Init(const eps_problem& original) {
   for (int i = 0; i < N; i++) {
     const ProxOp& op = ops[i];
     int kind = ST_KKT;
-    if (IsElemType(op.type)) kind = ST_ELEM;
+    if (op.rows_h > 0) kind = ST_VEC;
+    else if (IsElemType(op.type)) kind = ST_ELEM;
     else if (op.type == EPS_PROX_NORM_2) kind = ST_NORM2;
     else if (op.type == EPS_PROX_TOTAL_VARIATION_1D) kind = ST_TV;
     bool merged = false;
@@ -420,7 +481,7 @@ void eps_solver::Init(const eps_problem& original) {
   for (auto& op : ops)
     if (op.kkt && op.kkt->mode == EPS_KKT_CG) graph_ok = false;  // host-checked inner loop
   for (auto& stp : stages)
-    if (stp->kind == ST_TV) graph_ok = false;                      // host-checked active-set rounds
+    if (stp->kind == ST_TV || stp->kind == ST_VEC) graph_ok = false;  // host-checked rounds / library sorts
   memset(&status, 0, sizeof(status));
   status.state = EPS_NOT_STARTED;
   status.m = (int32_t)m_total;

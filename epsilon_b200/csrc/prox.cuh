@@ -62,6 +62,26 @@ void KktScalarPost(Ctx* ctx, int64_t n, double a, const double* x, double* u, do
 //   sums[0..4] = ||x - z||^2, ||z - z_prev||^2, ||x||^2, ||z||^2, ||u||^2
 void TwoBlockDualStep(Ctx* ctx, int64_t n, const double* x, const double* v, const double* t,
                       const double* mask, const double* z_prev, double* z, double* u, double* sums);
+// ---- multi-argument / sort-based vector operators (prox_vec.cu) ---------------------------
+// The operator acts on the stacked, already reduced argument vector V = [arg0 | arg1 | ...]
+// (VectorProx::PreProcessInput, vector_prox.cc:131) and overwrites it with the result.
+struct VecOpDesc {
+  int type = 0;
+  bool epigraph = false;
+  int64_t n0 = 0;        // rows of the first argument
+  int64_t rows = 0;      // all rows (n0 + 1 for the epigraph forms, 2*n0 for SUM_KL_DIV)
+  double lam = 0;        // VectorProx lambda (alpha * beta^2 / gamma)
+  double zone_m = 0, zone_alpha = 1, zone_beta = 1;
+};
+struct VecOpWork {
+  DevBuf<double> keys, keys2, vals, vals2, scan1, scan2, scal;
+  DevBuf<int> idx;
+  DevBuf<char> tmp;
+};
+bool IsVecOpType(int type, bool epigraph);
+void VecOpInit(Ctx* ctx, const VecOpDesc& d, VecOpWork* w);
+void VecOpApply(Ctx* ctx, const VecOpDesc& d, double* V, VecOpWork* w);
+
 // x = dinv .* rhs
 void KktDiagSolve(Ctx* ctx, int64_t n, const double* dinv, const double* rhs, double* x);
 

@@ -33,10 +33,12 @@ PROX_TYPES = {
     "SUM_EXP": 23,
     "SUM_HINGE": 24,
     "SUM_INV_POS": 25,
+    "SUM_KL_DIV": 26,
     "SUM_LOGISTIC": 27,
     "SUM_NEG_ENTR": 28,
     "SUM_NEG_LOG": 29,
     "SUM_QUANTILE": 31,
+    "MAX": 101,
     "NORM_2": 102,
     "TOTAL_VARIATION_1D": 106,
 }
@@ -144,6 +146,8 @@ class ProxFunction:
     # SUM_QUANTILE alpha/beta vectors (scaled_zone.cc:62-71)
     quantile_alpha: Optional[np.ndarray] = None
     quantile_beta: Optional[np.ndarray] = None
+    # sum_largest_params.k for SUM_LARGEST (sum_largest.cc:12)
+    sum_largest_k: int = 0
 
 
 @dataclass

@@ -48,10 +48,12 @@ enum eps_prox_type {
   EPS_PROX_SUM_EXP = 23,
   EPS_PROX_SUM_HINGE = 24,
   EPS_PROX_SUM_INV_POS = 25,
+  EPS_PROX_SUM_KL_DIV = 26,
   EPS_PROX_SUM_LOGISTIC = 27,
   EPS_PROX_SUM_NEG_ENTR = 28,
   EPS_PROX_SUM_NEG_LOG = 29,
   EPS_PROX_SUM_QUANTILE = 31,
+  EPS_PROX_MAX = 101,
   EPS_PROX_NORM_2 = 102,
   EPS_PROX_TOTAL_VARIATION_1D = 106
 };

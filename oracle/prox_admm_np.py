@@ -173,6 +173,132 @@ def neg_log_prox(v: np.ndarray, lam: np.ndarray) -> np.ndarray:
         return np.where(v >= 0, (v + s) / 2, 2 * lam / (-v + s))
 
 
+
+# ---------------------------------------------------------------------------
+# sort-based and epigraph operators (stacked arguments: v = [arg0 | arg1 | ...])
+# ---------------------------------------------------------------------------
+
+def max_prox(v: np.ndarray, lam: float) -> np.ndarray:
+    """MaxProx::ApplyVector, max.cc:8-41: x_i = min(v_i, t), sum_i (v_i - t)_+ = lam."""
+    y = np.sort(v)[::-1]
+    acc = np.cumsum(np.concatenate([[-lam], y]))           # acc before step i, in the reference's order
+    i = np.arange(y.size)
+    stop = np.nonzero(y * i < acc[:-1])[0]
+    k = int(stop[0]) if stop.size else y.size
+    t = acc[k] / k if k > 0 else 0.0
+    return np.minimum(v, t)
+
+
+def max_epigraph(v: np.ndarray, s: float):
+    """MaxEpigraph::ApplyVector, max.cc:46-85: projection onto {max_i x_i <= t}."""
+    y = np.sort(v)[::-1]
+    if s >= y[0]:
+        return v.copy(), s
+    acc = np.cumsum(np.concatenate([[0.0], y - s]))
+    div = 1.0 + np.arange(y.size)
+    stop = np.nonzero(div * (y - s) < acc[:-1])[0]
+    k = int(stop[0]) if stop.size else y.size
+    delta = acc[k] / (1.0 + k) if k > 0 else 0.0
+    t = s + delta
+    return v - np.maximum(0.0, v - t), t
+
+
+def sum_largest_prox(v: np.ndarray, lam: float, k: int) -> np.ndarray:
+    """SumLargestProx::ApplyVector, sum_largest.cc:17-58 (two-pointer sweep, as written)."""
+    y = np.sort(v)[::-1]
+    n = y.size
+    q, acc, inside, i, j = 0.0, -k * lam, 0, 0, 0
+    while i < n and j < n:
+        if y[i] * inside <= acc and (y[j] - lam) * inside <= acc:
+            break
+        if y[i] >= y[j] - lam:
+            acc += y[i]; inside += 1; i += 1
+        else:
+            acc += -y[j] + lam; inside -= 1; j += 1
+        q = acc / inside if inside else np.copysign(np.inf, acc) if acc else np.nan
+    return v - np.maximum(0.0, np.minimum(lam, v - q))
+
+
+def largest_real_cubic_root(b: float, c: float, d: float) -> float:
+    """LargestRealCubicRoot, newton.cc:293-323 (Durand-Kerner from the reference's start)."""
+    eps = 1e-12
+    p = complex(0.4, 0.9); q = p * p; r = p * p * p
+    for _ in range(100):
+        fp = p * p * p + b * p * p + c * p + d
+        np_ = p - fp / ((p - q) * (p - r))
+        fq = q * q * q + b * q * q + c * q + d
+        nq = q - fq / ((q - p) * (q - r))
+        fr = r * r * r + b * r * r + c * r + d
+        nr = r - fr / ((r - p) * (r - q))
+        if abs(fp) < eps and abs(fq) < eps and abs(fr) < eps:
+            break
+        p, q, r = np_, nq, nr
+    m = -1e41
+    for z in (p, q, r):
+        if abs(z.imag) < eps and z.real > m:
+            m = z.real
+    return m
+
+
+def sum_square_epigraph(u: np.ndarray, s: float):
+    """SumSquareEpigraph::ApplyVector, sum_square.cc:42-57."""
+    lam = largest_real_cubic_root(1 + s, 0.25 + s, (s - float(u @ u)) / 4)
+    lam = max(lam, 0.0)
+    return u / (1 + 2 * lam), s + lam
+
+
+def scaled_zone_epigraph(v: np.ndarray, s: float, alpha: float, beta: float, M: float, C: float = 0.0):
+    """ScaledZoneEpigraph::ApplyVector, scaled_zone.cc:152-279, for constant alpha/beta (the
+    reference indexes alpha/beta by the position in its permuted work array, :238-252, which is
+    only meaningful when they are constant).  The reference finds lam by a randomised
+    three-way-partition select; the root it brackets is the unique solution of
+        sum_{|key_k| > lam} w_k^2 (|key_k| - lam) = s + lam,   lam = acc / (div + 1)  (:268)
+    which is computed here from the sorted keys; the two differ by summation order only."""
+    y = v - C
+    keep = ~((np.abs(y) <= M) | ((y > 0) & (alpha == 0)) | ((y < 0) & (beta == 0)))
+    yk = y[keep]
+    fval = float(np.sum(np.where(yk > M, alpha * (yk - M), beta * (-yk - M))))
+    if fval <= s:
+        return v.copy(), s
+    w2 = np.where(yk > 0, alpha * alpha, beta * beta)
+    key = np.where(yk > 0, (yk - M) / alpha if alpha else 0.0, -(yk + M) / beta if beta else 0.0)  # |key|
+    order = np.argsort(-key, kind="stable")
+    key, w2 = key[order], w2[order]
+    acc = -s + np.cumsum(w2 * key)
+    div = np.cumsum(w2)
+    lam_k = acc / (div + 1)
+    nxt = np.concatenate([key[1:], [0.0]])
+    ok = np.nonzero(lam_k >= nxt)[0]
+    lam = float(lam_k[ok[0]])
+    return scaled_zone(v, np.full(v.size, lam), alpha, beta, M, C), s + lam
+
+
+def kl_div_prox(lam: np.ndarray, u: np.ndarray, v: np.ndarray):
+    """ApplyKLDivProx, sum_kl_div.cc:6-52 (per-element Newton on yhat, as written)."""
+    eps = 1e-13
+    n = u.size
+    x, y = np.empty(n), np.empty(n)
+    for i in range(n):
+        li, ui, vi = float(lam[i]), float(u[i]), float(v[i])
+        yhat = max((0.5 + li - vi) / li, eps)
+        if abs(ui) < eps * eps and abs(vi) < eps * eps:
+            x[i], y[i] = ui, vi
+            continue
+        for _ in range(1000):
+            f = li * yhat * yhat + (vi - li) * yhat - ui + li * np.log(yhat)
+            F = 2 * li * yhat + (vi - li) + li / yhat
+            res = f / F
+            if abs(res) < eps or (yhat <= eps * 2 and res > 0) or (li * yhat + vi - li <= eps * 2 and res > 0):
+                break
+            yhat = yhat - res
+            if yhat < eps:
+                yhat = eps
+            if li * yhat + vi - li < eps:
+                yhat = (eps + li - vi) / li
+        y[i] = li * yhat + vi - li
+        x[i] = y[i] * yhat
+    return x, y
+
 # ---------------------------------------------------------------------------
 # 1-D total variation (C restatement in oracle/tv1d_dp.c; pure Python for small n)
 # ---------------------------------------------------------------------------
@@ -398,8 +524,29 @@ class _VectorProx:
             self.lam = lam
         self.scalar = scalar
 
+    def _apply_epigraph(self, v: np.ndarray) -> np.ndarray:
+        """Epigraph operators: arguments [x (n) | t (1)], projection onto {f(x) <= t}."""
+        t = self.f.type
+        n = self.f.args[0].rows
+        assert len(self.f.args) == 2 and self.f.args[1].rows == 1
+        x, s = v[:n], float(v[n])
+        if t == "SUM_SQUARE":
+            xo, to = sum_square_epigraph(x, s)
+        elif t == "MAX":
+            xo, to = max_epigraph(x, s)
+        elif t in ZONE_TYPES:
+            al, be, M = zone_params(self.f, n)
+            assert np.ndim(al) == 0 or np.all(al == al[0]), "epigraph with vector alpha/beta"
+            a0 = float(np.ravel(al)[0]); b0 = float(np.ravel(be)[0])
+            xo, to = scaled_zone_epigraph(x, s, a0, b0, M)
+        else:
+            raise ValueError("no restatement for epigraph type %s" % t)
+        return np.concatenate([xo, [to]])
+
     def _apply_vector(self, v: np.ndarray) -> np.ndarray:
         t = self.f.type
+        if self.f.epigraph:
+            return self._apply_epigraph(v)
         if t in ZONE_TYPES:
             al, be, M = zone_params(self.f, v.size)
             return scaled_zone(v, self.lam, al, be, M)
@@ -417,6 +564,16 @@ class _VectorProx:
         if t == "TOTAL_VARIATION_1D":
             assert self.scalar
             return tv1d(v, float(self.lam[0]))
+        sizes = [a.rows for a in self.f.args]
+        offs = np.concatenate([[0], np.cumsum(sizes)])
+        arg = lambda k: v[offs[k]:offs[k + 1]]
+        if t == "MAX":
+            return max_prox(v, float(self.lam[0]))
+        if t == "SUM_LARGEST":
+            return sum_largest_prox(v, float(self.lam[0]), int(self.f.sum_largest_k))
+        if t == "SUM_KL_DIV":
+            x, y = kl_div_prox(self.lam[:sizes[0]], arg(0), arg(1))
+            return np.concatenate([x, y])
         raise ValueError("no restatement for prox type %s" % t)
 
     def apply(self, v: np.ndarray) -> np.ndarray:
@@ -429,7 +586,7 @@ class _VectorProx:
 
 
 def _make_operator(f, H, g, A):
-    if f.type in KKT_TYPES:
+    if f.type in KKT_TYPES and not f.epigraph:
         return _KktProx(f, H, g, A)
     return _VectorProx(f, H, g, A)
 

@@ -94,6 +94,8 @@ class _RefWriter:
             pf += " arg_size { dim: %d dim: 1 }" % a.rows
         if f.type == "SUM_DEADZONE":
             pf += " scaled_zone_params { m: %s }" % repr(float(f.zone_m))
+        if f.type == "SUM_LARGEST":
+            pf += " sum_largest_params { k: %d }" % int(f.sum_largest_k)
         if f.type == "SUM_QUANTILE":
             qa = "expression_type: CONSTANT %s %s" % (
                 self.size(f.quantile_alpha.size), self.dense_constant(f.quantile_alpha, "qalpha"))

@@ -47,6 +47,8 @@ SOLVE_CASES = {
     "tv_1d_200000": ("tv_1d", (200000,), {"seed": 11}, {"max_iterations": 100}),
     # stop by max_iterations (not a multiple of the epoch): MAX_ITERATIONS_REACHED path
     "lasso_maxiter_17": ("lasso", (80, 120), {"seed": 12}, {"max_iterations": 17}),
+    # epigraph form (use_epigraph=true): NORM_1 epigraph operator over (z, t) + AFFINE on a copy of t
+    "l1_epigraph_denoise_300": ("l1_epigraph_denoise", (300,), {"seed": 1}, {"max_iterations": 400}),
 }
 
 
@@ -143,7 +145,81 @@ def prox_cases():
         f = ProxFunction("SUM_SQUARE", alpha=0.5, args=[Affine(m, [
             Term(x, LinearMapSpec.Dense(a, name="A")), Term(b, LinearMapSpec.Scalar(-1.0, m), name="b")])])
         out[nm] = (f, 0.7, {"x": rng.standard_normal(nn)})
+
+    # ---- multi-argument / sort-based operators (own generator: the cases above stay as they are) ----
+    rng2 = np.random.default_rng(4321)
+
+    def epi(ptype, n, **kw):
+        x, t = Variable("x", n), Variable("t", 1)
+        return ProxFunction(ptype, args=[Affine(n, [Term(x)]), Affine(1, [Term(t)])], epigraph=True, **kw)
+
+    n = 1500
+    out["max"] = (simple("MAX", n, alpha=0.9), 1.7, {"x": rng2.standard_normal(n) * 2})
+    out["max_scaled_arg"] = (simple("MAX", n, alpha=0.5, scale=-1.5), 0.8, {"x": rng2.standard_normal(n)})
+    out["max_epigraph"] = (epi("MAX", n), 1.0, {"x": rng2.standard_normal(n) * 2, "t": np.array([0.3])})
+    out["max_epigraph_inside"] = (epi("MAX", 200), 1.0, {"x": rng2.standard_normal(200), "t": np.array([10.0])})
+    out["sum_largest"] = (simple("SUM_LARGEST", n, alpha=0.8, sum_largest_k=7), 1.3,
+                          {"x": rng2.standard_normal(n) * 2})
+    out["sum_square_epigraph"] = (epi("SUM_SQUARE", n), 1.0, {"x": rng2.standard_normal(n), "t": np.array([3.0])})
+    out["sum_square_epigraph_inside"] = (epi("SUM_SQUARE", 20), 1.0,
+                                         {"x": rng2.standard_normal(20) * 0.1, "t": np.array([30.0])})
+    out["norm_1_epigraph"] = (epi("NORM_1", n), 1.0, {"x": rng2.standard_normal(n) * 2, "t": np.array([5.0])})
+    out["norm_1_epigraph_inside"] = (epi("NORM_1", 100), 1.0, {"x": rng2.standard_normal(100) * 0.01,
+                                                             "t": np.array([5.0])})
+    out["sum_hinge_epigraph"] = (epi("SUM_HINGE", n), 1.0, {"x": rng2.standard_normal(n) * 2, "t": np.array([2.0])})
+    out["sum_deadzone_epigraph"] = (epi("SUM_DEADZONE", n, zone_m=0.5), 1.0,
+                                    {"x": rng2.standard_normal(n) * 2, "t": np.array([1.0])})
+    out["sum_quantile_epigraph"] = (epi("SUM_QUANTILE", n, quantile_alpha=np.array([0.3]),
+                                        quantile_beta=np.array([0.7])), 1.0,
+                                    {"x": rng2.standard_normal(n) * 2, "t": np.array([4.0])})
+    xk, yk = Variable("x", 800), Variable("y", 800)
+    out["sum_kl_div"] = (ProxFunction("SUM_KL_DIV", alpha=1.2, args=[Affine(800, [Term(xk)]), Affine(800, [Term(yk)])]),
+                         0.8, {"x": rng2.random(800) * 3 + 0.1, "y": rng2.random(800) * 3 + 0.1})
     return out
+
+
+def solve_case(name, ref_runner):
+    prob, info, params = make_problem(name)
+    r = ref_runner.run(prob, params=params, mode="trace")
+    stock = ref_runner.run(prob, params=params, mode="solve")
+    # the stepped run must end exactly where the stock Solve() ends
+    for k in TRACE_KEYS:
+        assert r["status"][k] == stock["status"][k], (name, k, r["status"], stock["status"])
+    trace = np.array([[t[k] for k in TRACE_KEYS] for t in r["trace"]], dtype=np.float64)
+    v = info["solution_var"]
+    np.savez_compressed(
+        os.path.join(HERE, name + ".npz"), trace=trace,
+        status=np.array([r["status"][k] for k in TRACE_KEYS], dtype=np.float64),
+        mnN=np.array([r["m"], r["n"], r["N"]], dtype=np.int64),
+        x=r["x"][v].astype(np.float64), objective=np.float64(info["objective"](r["x"])))
+    return {"digest": problem_digest(prob), "solution_var": v,
+                            "epochs": int(trace.shape[0]),
+                            "num_iterations": int(r["status"]["num_iterations"]),
+                            "state": int(r["status"]["state"])}
+
+
+def add_missing_prox():
+    """Run the reference only on the single-operator cases that have no fixture yet."""
+    from oracle import ref_runner
+    assert ref_runner.available(), "build oracle/_ref first: make -C oracle"
+    with open(os.path.join(HERE, "index.json")) as fh:
+        index = json.load(fh)
+    for name in SOLVE_CASES:
+        if name in index["solve"]:
+            continue
+        index["solve"][name] = solve_case(name, ref_runner)
+        print(name, index["solve"][name])
+    for name, (f, lam, v) in prox_cases().items():
+        if name in index["prox"]:
+            continue
+        x = ref_runner.run_prox(f, lam, v)
+        np.savez_compressed(os.path.join(HERE, "prox_" + name + ".npz"), lam=np.float64(lam),
+                            **{"v_" + k: val for k, val in v.items()},
+                            **{"x_" + k: val for k, val in x.items() if k in v})
+        index["prox"][name] = {"type": f.type, "n": int(sum(val.size for val in v.values()))}
+        print("prox", name, index["prox"][name])
+    with open(os.path.join(HERE, "index.json"), "w") as fh:
+        json.dump(index, fh, indent=1, sort_keys=True)
 
 
 def main():
@@ -151,23 +227,7 @@ def main():
     assert ref_runner.available(), "build oracle/_ref first: make -C oracle"
     index = {"solve": {}, "prox": {}}
     for name in SOLVE_CASES:
-        prob, info, params = make_problem(name)
-        r = ref_runner.run(prob, params=params, mode="trace")
-        stock = ref_runner.run(prob, params=params, mode="solve")
-        # the stepped run must end exactly where the stock Solve() ends
-        for k in TRACE_KEYS:
-            assert r["status"][k] == stock["status"][k], (name, k, r["status"], stock["status"])
-        trace = np.array([[t[k] for k in TRACE_KEYS] for t in r["trace"]], dtype=np.float64)
-        v = info["solution_var"]
-        np.savez_compressed(
-            os.path.join(HERE, name + ".npz"), trace=trace,
-            status=np.array([r["status"][k] for k in TRACE_KEYS], dtype=np.float64),
-            mnN=np.array([r["m"], r["n"], r["N"]], dtype=np.int64),
-            x=r["x"][v].astype(np.float64), objective=np.float64(info["objective"](r["x"])))
-        index["solve"][name] = {"digest": problem_digest(prob), "solution_var": v,
-                                "epochs": int(trace.shape[0]),
-                                "num_iterations": int(r["status"]["num_iterations"]),
-                                "state": int(r["status"]["state"])}
+        index["solve"][name] = solve_case(name, ref_runner)
         print(name, index["solve"][name])
     # two-block solver: the reference offers no stepping hook for it, so the per-epoch
     # residuals come from stock Solve() runs cut at max_iterations = k+1 (the final
@@ -207,4 +267,7 @@ def main():
 
 
 if __name__ == "__main__":
-    main()
+    if "--missing-prox" in sys.argv:
+        add_missing_prox()
+    else:
+        main()
