@@ -191,6 +191,13 @@ void KroneckerApply(Ctx* ctx, const MapData& K, bool trans, const double* x, dou
   EPS_CHECK(A.kind != MK_KRONECKER && B.kind != MK_KRONECKER, "nested Kronecker products");
   const int am = at ? A.n : A.m, an = at ? A.m : A.n;
   const int bm = bt ? B.n : B.m, bn = bt ? B.m : B.n;
+  if (A.kind == MK_SCALAR) {
+    // (s I_k) (x) B: column c of the result is s * B x_c -- the matrix-variable product A*X of
+    // the compiler (transforms/linear.py); no transposes, no temporaries
+    for (int c = 0; c < an; c++)
+      MapApply(ctx, B, bt, A.alpha, x + (size_t)c * bn, 0.0, y + (size_t)c * bm);
+    return;
+  }
   DevBuf<double> T(ctx, (size_t)bm * an), Tt(ctx, (size_t)an * bm), Yt(ctx, (size_t)am * bm);
   for (int c = 0; c < an; c++) MapApply(ctx, B, bt, 1.0, x + (size_t)c * bn, 0.0, T.p + (size_t)c * bm);
   dim3 tb(32, 8);

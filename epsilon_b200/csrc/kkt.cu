@@ -367,6 +367,55 @@ void KktSolver::Init(const std::vector<double>& g_host, const std::vector<double
     CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
   }
 
+  // ---- Kronecker structure: k identical diagonal blocks ----
+  if (alpha2 != 0.0 && H.blks.size() == 1 && H.blks[0].map->kind == MK_KRONECKER && !H.blks[0].trans &&
+      H.blks[0].map->ka->kind == MK_SCALAR && !h_sharded && H.blks[0].row_off == 0 && H.blks[0].col_off == 0 &&
+      H.blks[0].m() == rows_h && H.blks[0].n() == n && !getenv("EPS_NO_KRON_KKT")) {
+    const Blk& hb = H.blks[0];
+    const MapData& K = *hb.map;
+    const int k = K.ka->n;
+    const int64_t nb = n / k, mb = rows_h / k;
+    std::vector<double> da_all;
+    bool rep = A.GramDiagonal(&da_all);
+    for (int64_t j = 0; rep && j < n; j++) rep = da_all[j] == da_all[j % nb];
+    if (rep && k >= 1) {
+      inner = std::make_unique<KktSolver>();
+      inner->ctx = ctx;
+      inner->mode = mode;
+      inner->n = nb;
+      inner->rows_h = mb;
+      inner->rows_a = nb;
+      inner->alpha2 = alpha2;
+      inner->cg_tol = cg_tol;
+      inner->cg_max_iter = cg_max_iter;
+      inner->gram_max_n = gram_max_n;
+      inner->H.ctx = ctx; inner->H.rows = mb; inner->H.cols = nb;
+      Blk ib;
+      ib.map = K.kb;
+      ib.trans = K.kb_trans;
+      ib.scale = hb.scale * K.ka->alpha;
+      ib.row_off = 0; ib.col_off = 0;
+      inner->H.blks.push_back(ib);
+      // A'A of one block as a diagonal map sqrt(d)
+      auto dm = std::make_shared<MapData>();
+      dm->ctx = ctx; dm->kind = MK_DIAGONAL; dm->m = dm->n = (int)nb;
+      dm->h_diag.resize(nb);
+      for (int64_t j = 0; j < nb; j++) dm->h_diag[j] = std::sqrt(da_all[j]);
+      dm->diag.alloc(ctx, nb);
+      dm->diag.upload(dm->h_diag.data(), nb);
+      CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+      Blk ab;
+      ab.map = dm; ab.trans = false; ab.scale = 1.0; ab.row_off = 0; ab.col_off = 0;
+      inner->A.ctx = ctx; inner->A.rows = nb; inner->A.cols = nb;
+      inner->A.blks.push_back(ab);
+      inner->Init(std::vector<double>(), std::vector<double>());
+      kron_k = k;
+      mode = inner->mode;
+      description = Format("kron x%d of [%s]", k, inner->description.c_str());
+      return;
+    }
+  }
+
   std::vector<double> dh, da;
   const bool h_diag = (alpha2 == 0.0 || H.blks.empty()) ? (dh.assign(n, 0.0), true) : H.GramDiagonal(&dh);
   a_diag = A.GramDiagonal(&da);
@@ -522,6 +571,13 @@ void KktSolver::MatVec(const double* p, double* w, const int* skip) {
 }
 
 void KktSolver::Solve(const double* rhs, double* x) {
+  if (inner) {
+    const int64_t nb = n / kron_k;
+    const int64_t before = inner->cg_iters_total;
+    for (int c = 0; c < kron_k; c++) inner->Solve(rhs + (size_t)c * nb, x + (size_t)c * nb);
+    cg_iters_total += inner->cg_iters_total - before;
+    return;
+  }
   switch (mode) {
     case EPS_KKT_DIAGONAL:
       KktDiagSolve(ctx, n, dinv.p, rhs, x);

@@ -1,5 +1,7 @@
 // Linear-equality (KKT) prox: SumSquareProx / AffineProx of the reference.
 #pragma once
+#include <memory>
+
 #include "internal.h"
 
 namespace eps {
@@ -42,6 +44,10 @@ struct KktSolver {
   bool fused_tail = false;       // plane reduction + exchange + CG update in one kernel (CgFusedTailKernel)
   PeerBuf* peer = nullptr;       // row-sharded: the context's one-shot NVLink all-reduce buffers (not owned)
   unsigned long long pending_seq = 0;  // exchange the next consumer kernel has to complete (0: none)
+  // H = (s I_k) (x) B with A'A repeating over the k blocks (matrix variables, A*X): the system
+  // is block diagonal with k identical blocks; `inner` solves one block, Solve loops the columns
+  std::unique_ptr<KktSolver> inner;
+  int kron_k = 0;
   double cg_tol = 1e-12;
   int cg_max_iter = 500;
   int64_t cg_iters_total = 0;

@@ -48,6 +48,10 @@ SOLVE_CASES = {
     # stop by max_iterations (not a multiple of the epoch): MAX_ITERATIONS_REACHED path
     "lasso_maxiter_17": ("lasso", (80, 120), {"seed": 12}, {"max_iterations": 17}),
     # epigraph form (use_epigraph=true): NORM_1 epigraph operator over (z, t) + AFFINE on a copy of t
+    # matrix variables: A*X = (I_k (x) A) vec(X), KroneckerProductImpl (benchmark.py:46 "mv_lasso")
+    "mv_lasso_40x100x3": ("mv_lasso", (40, 100, 3), {"seed": 2}, {}),
+    "mv_lasso_120x60x4": ("mv_lasso", (120, 60, 4), {"seed": 2}, {}),
+    "mv_lasso_sparse_3000x300x5": ("mv_lasso", (3000, 300, 5), {"density": 0.02, "seed": 3}, {}),
     "l1_epigraph_denoise_300": ("l1_epigraph_denoise", (300,), {"seed": 1}, {"max_iterations": 400}),
 }
 

@@ -33,6 +33,9 @@ MODES = {
     "lasso_sparse_30000x3000": ["auto", "cg"],
     "hinge_l2_sparse_5000x300": ["auto", "cg"],
     "logreg_l1_2000x200": ["auto", "cg"],
+    "mv_lasso_40x100x3": ["auto", "cg", "gram"],
+    "mv_lasso_120x60x4": ["auto", "cg"],
+    "mv_lasso_sparse_3000x300x5": ["auto", "cg"],
 }
 
 
