@@ -17,6 +17,12 @@ namespace {
 constexpr int kBlock = 256;
 constexpr int kUnroll = 4;
 
+__device__ __forceinline__ unsigned long long GlobalTimerNs() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
 constexpr int kCgRing = 64;
 constexpr int kTailBlock = 512;
 
@@ -149,11 +155,13 @@ CgFusedTailKernel(int64_t n, int T, const double* __restrict__ planes, double al
                   double* __restrict__ w, double* __restrict__ p, double* __restrict__ x,
                   double* __restrict__ r, double* scal, double* partials, int* done,
                   KktSolver::CgResult* ring, long long seq, PeerXchg px, unsigned long long xseq,
-                  const double* __restrict__ dg) {
+                  const double* __restrict__ dg, unsigned long long* __restrict__ trace) {
   namespace cg = cooperative_groups;
   __shared__ double smem[64];
   const int G = gridDim.x;
   const int c = blockIdx.x;
+#define EPS_TT(k) if (trace && threadIdx.x == 0) trace[c * 8 + (k)] = GlobalTimerNs()
+  EPS_TT(0);
   const int parity = (int)(xseq & 1ull);
   const bool finished = *done != 0;  // uniform: only ever written by the last phase of an earlier launch
   // slice of this CTA (even length so that the rows stay 16-byte aligned)
@@ -174,8 +182,10 @@ CgFusedTailKernel(int64_t n, int T, const double* __restrict__ planes, double al
       }
     }
     __syncthreads();
+    EPS_TT(1);
     if (threadIdx.x == 0) __threadfence_system();  // cumulative: orders the CTA's remote stores
     __syncthreads();
+    EPS_TT(2);
     if (threadIdx.x < px.G)
       StReleaseSys(px.cflag[threadIdx.x] + ((size_t)parity * px.G + px.rank) * kPeerMaxCtas + c, xseq);
     if (threadIdx.x < px.G) {
@@ -183,6 +193,7 @@ CgFusedTailKernel(int64_t n, int T, const double* __restrict__ planes, double al
       while (LdAcquireSys(f) < xseq) {}
     }
     __syncthreads();
+    EPS_TT(3);
   }
   if (finished) return;
   cg::grid_group grid = cg::this_grid();
@@ -208,7 +219,9 @@ CgFusedTailKernel(int64_t n, int T, const double* __restrict__ planes, double al
   }
   BlockSum<1>(v, smem);
   if (threadIdx.x == 0) partials[blockIdx.x] = v[0];
+  EPS_TT(4);
   grid.sync();
+  EPS_TT(5);
   const double pw = SumPartials(partials, G, smem);
   const double a = pw != 0.0 ? rr / pw : 0.0;
   v[0] = 0.0;
@@ -224,6 +237,7 @@ CgFusedTailKernel(int64_t n, int T, const double* __restrict__ planes, double al
   const double rr_new = SumPartials(partials + G, G, smem);
   const double b = rr != 0.0 ? rr_new / rr : 0.0;
   for (int64_t i = lo + threadIdx.x; i < hi; i += kTailBlock) p[i] = r[i] + b * p[i];
+  EPS_TT(6);
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     const int conv = sqrt(rr_new) <= thresh ? 1 : 0;
     scal[0] = rr_new;
@@ -234,6 +248,7 @@ CgFusedTailKernel(int64_t n, int T, const double* __restrict__ planes, double al
     __threadfence_system();
     *reinterpret_cast<volatile long long*>(&e->seq) = seq;
   }
+#undef EPS_TT
 }
 
 __global__ void InvertKernel(int64_t n, const double* __restrict__ d, double* __restrict__ out, int* bad) {
@@ -654,10 +669,39 @@ void KktSolver::Solve(const double* rhs, double* x) {
           PeerXchg pxv = peer ? peer->x : PeerXchg();
           unsigned long long xs = peer ? ++peer->seq : 0ull;
           const double* dgp = ddiag.p;
-          void* args[] = {&nn, &T, &planes, &alpha, &wp, &pp, &xp, &rp, &sp, &part, &dp, &rg, &seq, &pxv, &xs, &dgp};
+          // EPS_TAIL_TRACE=<launch number>: per-CTA phase timeline of that launch on stderr (rank 0)
+          static const int trace_at = getenv("EPS_TAIL_TRACE") ? atoi(getenv("EPS_TAIL_TRACE")) : -1;
+          static int launch_no = 0;
+          static DevBuf<unsigned long long> tbuf;
+          unsigned long long* trace = nullptr;
+          if (trace_at >= 0) {
+            if (launch_no == 0) {  // allocated up front: no synchronisation next to the traced launch
+              tbuf.alloc(ctx, (size_t)tail_grid * 8);
+              tbuf.zero();
+            }
+            if (launch_no++ == trace_at) trace = tbuf.p;
+          }
+          void* args[] = {&nn, &T, &planes, &alpha, &wp, &pp, &xp, &rp, &sp, &part, &dp, &rg, &seq, &pxv, &xs, &dgp, &trace};
           CUDA_CHECK(cudaLaunchCooperativeKernel((const void*)CgFusedTailKernel, dim3(tail_grid),
                                                  dim3(kTailBlock), args, 0, ctx->stream));
           ctx->count_launch();
+          if (trace) {
+            std::vector<unsigned long long> h((size_t)tail_grid * 8);
+            tbuf.download(h.data(), h.size());
+            unsigned long long t0 = ~0ull;
+            for (int g = 0; g < tail_grid; g++) t0 = std::min(t0, h[g * 8]);
+            std::string line = Format("[tail trace] rank %d G=%d T=%d n=%lld us since first CTA (median/max):", ctx->rank,
+                                      peer ? peer->x.G : 1, T, (long long)n);
+            const char* names[7] = {"start", "pushed", "fenced", "peers-in", "dot", "sync1", "end"};
+            for (int k = 0; k < 7; k++) {
+              std::vector<double> v;
+              for (int g = 0; g < tail_grid; g++) if (h[g * 8 + k]) v.push_back((h[g * 8 + k] - t0) * 1e-3);
+              if (v.empty()) continue;
+              std::sort(v.begin(), v.end());
+              line += Format(" %s %.1f/%.1f", names[k], v[v.size() / 2], v.back());
+            }
+            fprintf(stderr, "%s\n", line.c_str());
+          }
           }
           if (wait_result(base + it).converged != 0.0) { converged = true; break; }
           continue;
