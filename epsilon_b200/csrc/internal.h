@@ -157,15 +157,15 @@ struct SellStream {
 
 struct Sell {
   bool built = false;
-  int R = 0, Cn = 0, T = 0, TW = 0, RR = 0, rows_per = 0, n_slices = 0, n_cta = 0;
+  int R = 0, Cn = 0, T = 0, TW = 0, n_slices = 0, n_cta = 0;
   int64_t nnz = 0, n_val = 0, n_idx = 0;
-  DevBuf<int32_t> sl_len, rowid, cta_begin;
-  DevBuf<int64_t> voff, ioff;
+  // a CTA walks visits = (column tile, row range); inside a visit every one of the nw warps owns
+  // one contiguous stream of slices
+  int n_visits = 0, nw = 24;
+  DevBuf<int32_t> sl_len, rowid;   // per slice, stream order: length; per lane: index into the planes
+  DevBuf<int64_t> voff;            // only while building
   DevBuf<double> val;
   DevBuf<uint16_t> idx;
-  // stream layout (version 2): a CTA walks visits = (column tile, row range); inside a visit
-  // every warp owns one contiguous stream
-  int version = 1, n_visits = 0, nw = 32;
   DevBuf<int32_t> visit_tile, cta_visit;
   DevBuf<SellStream> streams;
 };

@@ -1,14 +1,14 @@
-// Column-tiled sliced-ELL SpMV with the x tile staged in shared memory.
+// Column-tiled sliced-ELL SpMV in stream order, with the x tile staged in shared memory.
 //
 // Why: with plain CSR the gather of x goes through L1/L2 in 32-byte sectors for 8 useful
 // bytes; ncu on the 1M x 100k lasso shows DRAM at 35 % while L1/L2 throughput sits at
-// 82-88 % (profiles/r01_spmv_csr_baseline.txt).  Here the columns are cut into tiles of at
-// most kMaxTile entries so that the matching slice of x (<= 200 KB) lives in shared memory
-// (staged by one TMA bulk copy), the rows of each (tile, row-range) work item are sorted by
-// length and packed 32 at a time column-major (SELL-32-sigma) so that every load of the
-// (index, value) stream is a full coalesced line, and column indices shrink to 16 bits
-// (10 bytes per non-zero instead of 12).  Each work item writes one partial sum per row
-// and tile; a second kernel adds the tiles in a fixed order (deterministic, no atomics).
+// 82-88 %.  Here the columns are cut into tiles of at most kMaxTile entries so that the
+// matching slice of x (<= 200 KB) lives in shared memory (staged by one TMA bulk copy), rows
+// are packed 32 at a time column-major (SELL-32-sigma) so that every load of the (index,
+// value) stream is a full coalesced line, and column indices shrink to 16 bits (10 bytes per
+// non-zero instead of 12).  A visit writes one partial sum per row and tile into the planes
+// P[tile][row]; a second kernel (or the fused CG update, kkt.cu) adds the tiles in a fixed
+// order (deterministic, no atomics).
 //
 // Backs SparseMatrixImpl::Apply (src/epsilon/linear/sparse_matrix_impl.h:24) and its
 // transpose for large matrices; results differ from the reference only by summation order.
@@ -23,7 +23,6 @@ namespace eps {
 namespace {
 
 constexpr int kMaxTile = 25600;      // doubles of x per tile (200 KB of shared memory)
-constexpr int kSellThreads = 1024;
 
 __global__ void SegBoundsKernel(int R, int T, int TW, const int32_t* __restrict__ rowptr,
                                 const int32_t* __restrict__ col, int32_t* __restrict__ segstart,
@@ -46,160 +45,8 @@ __global__ void SegBoundsKernel(int R, int T, int TW, const int32_t* __restrict_
   }
 }
 
-__global__ void SellKeysKernel(int R, int T, int RR, int rows_per, const int32_t* __restrict__ seglen,
-                               uint32_t* __restrict__ keys, int32_t* __restrict__ vals) {
-  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= (size_t)T * R) return;
-  const int t = (int)(i / R), row = (int)(i % R);
-  const uint32_t item = (uint32_t)(t * RR + row / rows_per);
-  keys[i] = (item << 16) | (uint32_t)(0xFFFF - seglen[i]);
-  vals[i] = (int32_t)i;
-}
-
-__global__ void SliceLenKernel(int R, int T, int RR, int rows_per, const uint32_t* __restrict__ skeys,
-                               int32_t* __restrict__ sl_len, int64_t* __restrict__ vsize,
-                               int64_t* __restrict__ isize) {
-  const int spi = rows_per / 32;
-  const int s = blockIdx.x * blockDim.x + threadIdx.x;
-  if (s >= T * RR * spi) return;
-  const int item = s / spi, j = s % spi;
-  const int t = item / RR, rr = item % RR;
-  const int first = rr * rows_per + 32 * j;
-  int len = 0;
-  if (first < R && first < (rr + 1) * rows_per) len = 0xFFFF - (int)(skeys[(size_t)t * R + first] & 0xFFFF);
-  sl_len[s] = len;
-  vsize[s] = 32 * (int64_t)len;
-  isize[s] = 32 * (int64_t)((len + 3) / 4 * 4);
-}
-
-// one warp per slice
-__global__ void SellFillKernel(int R, int T, int RR, int rows_per, int TW, int n_slices,
-                               const int32_t* __restrict__ svals, const int32_t* __restrict__ segstart,
-                               const int32_t* __restrict__ seglen, const int32_t* __restrict__ ccol,
-                               const double* __restrict__ cval, const int32_t* __restrict__ sl_len,
-                               const int64_t* __restrict__ voff, const int64_t* __restrict__ ioff,
-                               double* __restrict__ val, uint16_t* __restrict__ idx,
-                               int32_t* __restrict__ rowid) {
-  const int s = blockIdx.x * (blockDim.x / 32) + (threadIdx.x >> 5);
-  const int lane = threadIdx.x & 31;
-  if (s >= n_slices) return;
-  const int spi = rows_per / 32;
-  const int item = s / spi, j = s % spi;
-  const int t = item / RR, rr = item % RR;
-  const int pos = rr * rows_per + 32 * j + lane;
-  int row = -1, start = 0, mylen = 0;
-  if (pos < R && pos < (rr + 1) * rows_per) {
-    const int i = svals[(size_t)t * R + pos];
-    row = i - t * R;
-    start = segstart[i];
-    mylen = seglen[i];
-  }
-  rowid[(size_t)s * 32 + lane] = row;
-  const int len = sl_len[s];
-  const int64_t vo = voff[s], io = ioff[s];
-  const int base = t * TW;
-  for (int k = 0; k < len; k++) {
-    const bool in = k < mylen;
-    val[vo + (int64_t)k * 32 + lane] = in ? cval[start + k] : 0.0;
-    idx[io + (int64_t)(k >> 2) * 128 + lane * 4 + (k & 3)] = in ? (uint16_t)(ccol[start + k] - base) : (uint16_t)0;
-  }
-  for (int k = len; k < (len + 3) / 4 * 4; k++) idx[io + (int64_t)(k >> 2) * 128 + lane * 4 + (k & 3)] = 0;
-}
-
 __device__ __forceinline__ uint32_t SmemAddr(const void* p) {
   return (uint32_t)__cvta_generic_to_shared(p);
-}
-
-// P[tile][row] = sum over the row's non-zeros inside the tile.
-// Persistent: CTA g owns the contiguous work items [cta_begin[g], cta_begin[g+1]) -- a static
-// partition balanced by stored non-zeros at build time (deterministic, no atomics).  Items
-// are ordered tile-major, so a CTA restages its x tile only when the tile changes.
-__global__ void __launch_bounds__(kSellThreads, 1)
-SellSpmvKernel(int R, int Cn, int TW, int RR, int spi, const int32_t* __restrict__ cta_begin,
-               const int32_t* __restrict__ sl_len,
-               const int64_t* __restrict__ voff, const int64_t* __restrict__ ioff,
-               const double* __restrict__ val, const uint16_t* __restrict__ idx,
-               const int32_t* __restrict__ rowid, const double* __restrict__ x,
-               double* __restrict__ P, int use_tma, const int* __restrict__ skip) {
-  extern __shared__ __align__(128) double xs[];
-  __shared__ __align__(8) unsigned long long bar;
-  if (skip && *skip) return;  // speculative launch after the CG loop converged (kkt.cu)
-  const int item_lo = cta_begin[blockIdx.x], item_hi = cta_begin[blockIdx.x + 1];
-  if (item_lo >= item_hi) return;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const uint32_t bar_a = SmemAddr(&bar);
-  if (use_tma) {
-    if (threadIdx.x == 0) {
-      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_a));
-      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
-  }
-  int cur_t = -1;
-  uint32_t phase = 0;
-  for (int item = item_lo; item < item_hi; item++) {
-    const int t = item / RR;
-    if (t != cur_t) {
-      const int c0 = t * TW;
-      const int cw = min(TW, Cn - c0);
-      __syncthreads();  // every warp is done reading the previous tile (and sees the barrier init)
-      if (use_tma) {
-        // one TMA bulk copy of the x tile (cp.async.bulk, completion on an mbarrier)
-        const uint32_t bytes = (uint32_t)cw * 8u;
-        if (threadIdx.x == 0) {
-          asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_a), "r"(bytes) : "memory");
-          asm volatile(
-              "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-              ::"r"(SmemAddr(xs)), "l"(x + c0), "r"(bytes), "r"(bar_a) : "memory");
-        }
-        uint32_t done = 0;
-        while (!done) {
-          asm volatile(
-              "{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}\n"
-              : "=r"(done) : "r"(bar_a), "r"(phase) : "memory");
-        }
-        phase ^= 1u;
-      } else {
-        for (int i = threadIdx.x; i < cw; i += kSellThreads) xs[i] = x[c0 + i];
-        __syncthreads();
-      }
-      cur_t = t;
-    }
-    const int s0 = item * spi;
-    double* Pt = P + (size_t)t * R;
-    for (int s = s0 + warp; s < s0 + spi; s += kSellThreads / 32) {
-      const int len = sl_len[s];
-      const int row = rowid[(size_t)s * 32 + lane];
-      const double* v = val + voff[s] + lane;
-      const uint16_t* ix = idx + ioff[s] + lane * 4;
-      double acc0 = 0.0, acc1 = 0.0;
-      int k = 0;
-      for (; k + 8 <= len; k += 8) {
-        const uint2 qa = *reinterpret_cast<const uint2*>(ix + (size_t)(k >> 2) * 128);
-        const uint2 qb = *reinterpret_cast<const uint2*>(ix + (size_t)((k >> 2) + 1) * 128);
-        const double v0 = LdStream(v + (size_t)(k + 0) * 32), v1 = LdStream(v + (size_t)(k + 1) * 32);
-        const double v2 = LdStream(v + (size_t)(k + 2) * 32), v3 = LdStream(v + (size_t)(k + 3) * 32);
-        const double v4 = LdStream(v + (size_t)(k + 4) * 32), v5 = LdStream(v + (size_t)(k + 5) * 32);
-        const double v6 = LdStream(v + (size_t)(k + 6) * 32), v7 = LdStream(v + (size_t)(k + 7) * 32);
-        acc0 += v0 * xs[qa.x & 0xFFFF];
-        acc1 += v1 * xs[qa.x >> 16];
-        acc0 += v2 * xs[qa.y & 0xFFFF];
-        acc1 += v3 * xs[qa.y >> 16];
-        acc0 += v4 * xs[qb.x & 0xFFFF];
-        acc1 += v5 * xs[qb.x >> 16];
-        acc0 += v6 * xs[qb.y & 0xFFFF];
-        acc1 += v7 * xs[qb.y >> 16];
-      }
-      for (; k < len; k += 4) {
-        const uint2 q = *reinterpret_cast<const uint2*>(ix + (size_t)(k >> 2) * 128);
-        const int rem = len - k;
-        acc0 += LdStream(v + (size_t)k * 32) * xs[q.x & 0xFFFF];
-        if (rem > 1) acc1 += LdStream(v + (size_t)(k + 1) * 32) * xs[q.x >> 16];
-        if (rem > 2) acc0 += LdStream(v + (size_t)(k + 2) * 32) * xs[q.y & 0xFFFF];
-        if (rem > 3) acc1 += LdStream(v + (size_t)(k + 3) * 32) * xs[q.y >> 16];
-      }
-      if (row >= 0) Pt[row] = acc0 + acc1;
-    }
-  }
 }
 
 __global__ void __launch_bounds__(256)
@@ -237,15 +84,16 @@ SellReducePublishKernel(int R, int T, const double* __restrict__ P, double alpha
 }
 
 
-// ===== stream layout (version 2) ==========================================================
+// ===== stream layout ========================================================================
 // Work is cut at (tile, row) granularity: the tile-major list of (tile, row) pairs is split
 // into n_cta contiguous ranges of equal cost; the part of a range inside one tile is a
 // "visit".  Inside a visit the rows are sorted by length, packed into 32-row slices, and the
-// slices are dealt to the 32 warps in serpentine order; the slices of one warp are stored
+// slices are dealt to the CTA's warps in serpentine order; the slices of one warp are stored
 // back to back, so a warp reads ONE contiguous stream of values and of indices per visit and
-// can keep two batches of loads in flight across slice boundaries (the version-1 kernel
-// drained its loads at the end of every 25-entry slice: long-scoreboard stalls, 77 % of the
-// HBM peak).
+// can keep two batches of loads in flight across slice boundaries (an earlier kernel that
+// walked (tile, row-range) items slice by slice drained its loads at the end of every
+// 25-entry slice: long-scoreboard stalls, 77 % of the HBM peak,
+// profiles/r01_ncu_full_SellSpmvKernel_v1_before.csv).
 
 
 struct VisitTab {
@@ -569,7 +417,6 @@ SellStreamKernel(int R, int Cn, int TW, const int32_t* __restrict__ cta_visit,
 
 static void BuildSellStream(Ctx* ctx, const Csr& A, Sell* S) {
   const int R = A.m, Cn = A.n;
-  S->version = 2;
   // 24 warps: 80 registers per thread hold two batches of loads without spills; measured on
   // B200 (1M x 100k, density 1e-3): 96.4 % of the HBM copy peak vs 96.1 % (32 warps, spills),
   // 93.8 % (20), 86.2 % (16)
@@ -706,108 +553,7 @@ static void BuildSellStream(Ctx* ctx, const Csr& A, Sell* S) {
   S->built = true;
 }
 
-void BuildSell(Ctx* ctx, const Csr& A, Sell* S) {
-  const char* ver = getenv("EPS_SELL_VERSION");
-  if (!ver || atoi(ver) != 1) {
-    BuildSellStream(ctx, A, S);
-    return;
-  }
-  const int R = A.m, Cn = A.n;
-  S->R = R; S->Cn = Cn; S->nnz = A.nnz;
-  const int T = (Cn + kMaxTile - 1) / kMaxTile;
-  int TW = (Cn + T - 1) / T;
-  TW = (TW + 1) / 2 * 2;  // keep tile starts 16-byte aligned for the bulk copy
-  S->T = T; S->TW = TW;
-  // about 8 work items per CTA so that the static partition below balances to ~1/8 of an
-  // item, but at least 1024 rows (one 32-row slice per warp) per item
-  const int64_t want_items = (int64_t)ctx->sm_count * 8;
-  int rows_per = (int)(((int64_t)R * T + want_items - 1) / want_items);
-  rows_per = std::max(1024, rows_per);
-  rows_per = std::min(rows_per, std::max(32, R));
-  rows_per = (rows_per + 31) / 32 * 32;
-  int RR = (R + rows_per - 1) / rows_per;
-  S->RR = RR; S->rows_per = rows_per;
-  const int spi = rows_per / 32;
-  const int n_slices = T * RR * spi;
-  S->n_slices = n_slices;
-  const size_t TR = (size_t)T * R;
-  EPS_CHECK(T * RR < 65536, "too many SELL work items (%d)", T * RR);
-  DevBuf<int32_t> segstart(ctx, TR), seglen(ctx, TR), vals_in(ctx, TR), vals_out(ctx, TR);
-  DevBuf<uint32_t> keys_in(ctx, TR), keys_out(ctx, TR);
-  SegBoundsKernel<<<(R + 255) / 256, 256, 0, ctx->stream>>>(R, T, TW, A.rowptr.p, A.col.p, segstart.p, seglen.p);
-  SellKeysKernel<<<(unsigned)((TR + 255) / 256), 256, 0, ctx->stream>>>(R, T, RR, rows_per, seglen.p, keys_in.p, vals_in.p);
-  size_t tmp_bytes = 0;
-  CUDA_CHECK(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys_in.p, keys_out.p, vals_in.p, vals_out.p,
-                                             (int)TR, 0, 32, ctx->stream));
-  DevBuf<char> tmp(ctx, tmp_bytes);
-  CUDA_CHECK(cub::DeviceRadixSort::SortPairs(tmp.p, tmp_bytes, keys_in.p, keys_out.p, vals_in.p, vals_out.p,
-                                             (int)TR, 0, 32, ctx->stream));
-  S->sl_len.alloc(ctx, n_slices);
-  S->voff.alloc(ctx, n_slices + 1);
-  S->ioff.alloc(ctx, n_slices + 1);
-  DevBuf<int64_t> vsize(ctx, n_slices + 1), isize(ctx, n_slices + 1);
-  vsize.zero();
-  isize.zero();
-  SliceLenKernel<<<(n_slices + 255) / 256, 256, 0, ctx->stream>>>(R, T, RR, rows_per, keys_out.p, S->sl_len.p,
-                                                                   vsize.p, isize.p);
-  size_t scan_bytes = 0;
-  CUDA_CHECK(cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, vsize.p, S->voff.p, n_slices + 1, ctx->stream));
-  DevBuf<char> tmp2(ctx, scan_bytes);
-  CUDA_CHECK(cub::DeviceScan::ExclusiveSum(tmp2.p, scan_bytes, vsize.p, S->voff.p, n_slices + 1, ctx->stream));
-  CUDA_CHECK(cub::DeviceScan::ExclusiveSum(tmp2.p, scan_bytes, isize.p, S->ioff.p, n_slices + 1, ctx->stream));
-  int64_t totals[2];
-  CUDA_CHECK(cudaMemcpyAsync(&totals[0], S->voff.p + n_slices, 8, cudaMemcpyDeviceToHost, ctx->stream));
-  CUDA_CHECK(cudaMemcpyAsync(&totals[1], S->ioff.p + n_slices, 8, cudaMemcpyDeviceToHost, ctx->stream));
-  CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
-  S->n_val = totals[0];
-  S->n_idx = totals[1];
-  S->val.alloc(ctx, std::max<int64_t>(S->n_val, 1));
-  S->idx.alloc(ctx, std::max<int64_t>(S->n_idx, 4));
-  S->rowid.alloc(ctx, (size_t)n_slices * 32);
-  {
-    // static partition of the tile-major item list over the CTAs, balanced by stored bytes
-    // (10 per non-zero) plus the x-tile staging a CTA pays when it enters a new tile
-    const int items = T * RR;
-    std::vector<int64_t> hv(n_slices + 1);
-    CUDA_CHECK(cudaMemcpyAsync(hv.data(), S->voff.p, (n_slices + 1) * sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
-    CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
-    std::vector<double> cost(items + 1, 0.0);
-    for (int i = 0; i < items; i++) {
-      double c = 10.0 * (double)(hv[(size_t)(i + 1) * spi] - hv[(size_t)i * spi]) + 12.0 * rows_per;
-      if (i % RR == 0) c += 8.0 * TW;
-      cost[i + 1] = cost[i] + c;
-    }
-    const int G = std::max(1, std::min(items, ctx->sm_count));
-    std::vector<int32_t> begin(G + 1, items);
-    begin[0] = 0;
-    int it = 0;
-    for (int g = 1; g < G; g++) {
-      const double target = cost[items] * g / G;
-      while (it < items && cost[it + 1] <= target) it++;
-      // closer boundary of the two around the target
-      int cut = it;
-      if (it < items && (target - cost[it]) > (cost[it + 1] - target)) cut = it + 1;
-      begin[g] = std::max(cut, begin[g - 1]);
-    }
-    begin[G] = items;
-    S->n_cta = G;
-    S->cta_begin.alloc(ctx, G + 1);
-    S->cta_begin.upload(begin.data(), G + 1);
-    CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
-  }
-  SellFillKernel<<<(n_slices + 7) / 8, 256, 0, ctx->stream>>>(
-      R, T, RR, rows_per, TW, n_slices, vals_out.p, segstart.p, seglen.p, A.col.p, A.val.p, S->sl_len.p,
-      S->voff.p, S->ioff.p, S->val.p, S->idx.p, S->rowid.p);
-  CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
-  CUDA_CHECK(cudaGetLastError());
-  static bool attr_set = false;
-  if (!attr_set) {
-    CUDA_CHECK(cudaFuncSetAttribute(SellSpmvKernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    kMaxTile * 8 + 64));
-    attr_set = true;
-  }
-  S->built = true;
-}
+void BuildSell(Ctx* ctx, const Csr& A, Sell* S) { BuildSellStream(ctx, A, S); }
 
 static double* SellLaunch(Ctx* ctx, const Sell& S, const double* x, int kclass, const int* skip) {
   double* P = GrowScratch(ctx, &ctx->sell_scratch, (size_t)S.T * S.R);
@@ -817,56 +563,53 @@ static double* SellLaunch(Ctx* ctx, const Sell& S, const double* x, int kclass, 
     // pointer and the width of the last tile can break that
     const int last = S.Cn - (S.T - 1) * S.TW;
     const int use_tma = ((reinterpret_cast<uintptr_t>(x) & 15) == 0 && last % 2 == 0) ? 1 : 0;
-    if (S.version == 2) {
-      // EPS_SELL_TRACE=<launch number>: per-CTA timeline of that launch on stderr (diagnostics)
-      static const int trace_at = getenv("EPS_SELL_TRACE") ? atoi(getenv("EPS_SELL_TRACE")) : -1;
-      static int launch_no = 0;
-      static DevBuf<unsigned long long> tbuf;
-      unsigned long long* trace = nullptr;
-      if (trace_at >= 0 && launch_no++ == trace_at) {
-        tbuf.alloc(ctx, (size_t)S.n_cta * 4);
-        std::vector<unsigned long long> init((size_t)S.n_cta * 4, 0ull);
-        for (int g = 0; g < S.n_cta; g++) init[g * 4 + 2] = ~0ull;
-        tbuf.upload(init.data(), init.size());
-        CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
-        trace = tbuf.p;
+    {
+    // EPS_SELL_TRACE=<launch number>: per-CTA timeline of that launch on stderr (diagnostics)
+    static const int trace_at = getenv("EPS_SELL_TRACE") ? atoi(getenv("EPS_SELL_TRACE")) : -1;
+    static int launch_no = 0;
+    static DevBuf<unsigned long long> tbuf;
+    unsigned long long* trace = nullptr;
+    if (trace_at >= 0 && launch_no++ == trace_at) {
+      tbuf.alloc(ctx, (size_t)S.n_cta * 4);
+      std::vector<unsigned long long> init((size_t)S.n_cta * 4, 0ull);
+      for (int g = 0; g < S.n_cta; g++) init[g * 4 + 2] = ~0ull;
+      tbuf.upload(init.data(), init.size());
+      CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+      trace = tbuf.p;
+    }
+    using KernT = void (*)(int, int, int, const int32_t*, const int32_t*, const SellStream*, const int32_t*,
+                           const double*, const uint16_t*, const int32_t*, const double*, double*, int, const int*,
+                           unsigned long long*);
+    KernT kern = nullptr;
+    switch (S.nw) {
+      case 16: kern = trace ? SellStreamKernel<16, 8, true> : SellStreamKernel<16, 8, false>; break;
+      case 20: kern = trace ? SellStreamKernel<20, 8, true> : SellStreamKernel<20, 8, false>; break;
+      case 24: kern = trace ? SellStreamKernel<24, 8, true> : SellStreamKernel<24, 8, false>; break;
+      default: kern = trace ? SellStreamKernel<32, 8, true> : SellStreamKernel<32, 8, false>; break;
+    }
+    kern<<<S.n_cta, S.nw * 32, (size_t)S.TW * 8 + 64, ctx->stream>>>(
+        S.R, S.Cn, S.TW, S.cta_visit.p, S.visit_tile.p, S.streams.p, S.sl_len.p, S.val.p, S.idx.p, S.rowid.p, x,
+        P, use_tma, skip, trace);
+    if (trace) {
+      std::vector<unsigned long long> h((size_t)S.n_cta * 4);
+      tbuf.download(h.data(), h.size());
+      unsigned long long t0 = ~0ull;
+      for (int g = 0; g < S.n_cta; g++) if (h[g * 4]) t0 = std::min(t0, h[g * 4]);
+      std::vector<double> a, b, c, d;
+      for (int g = 0; g < S.n_cta; g++) {
+        if (!h[g * 4]) continue;
+        a.push_back((h[g * 4] - t0) * 1e-3);
+        b.push_back((h[g * 4 + 1] - t0) * 1e-3);
+        c.push_back((h[g * 4 + 2] - t0) * 1e-3);
+        d.push_back((h[g * 4 + 3] - t0) * 1e-3);
       }
-      using KernT = void (*)(int, int, int, const int32_t*, const int32_t*, const SellStream*, const int32_t*,
-                             const double*, const uint16_t*, const int32_t*, const double*, double*, int, const int*,
-                             unsigned long long*);
-      KernT kern = nullptr;
-      switch (S.nw) {
-        case 16: kern = trace ? SellStreamKernel<16, 8, true> : SellStreamKernel<16, 8, false>; break;
-        case 20: kern = trace ? SellStreamKernel<20, 8, true> : SellStreamKernel<20, 8, false>; break;
-        case 24: kern = trace ? SellStreamKernel<24, 8, true> : SellStreamKernel<24, 8, false>; break;
-        default: kern = trace ? SellStreamKernel<32, 8, true> : SellStreamKernel<32, 8, false>; break;
-      }
-      kern<<<S.n_cta, S.nw * 32, (size_t)S.TW * 8 + 64, ctx->stream>>>(
-          S.R, S.Cn, S.TW, S.cta_visit.p, S.visit_tile.p, S.streams.p, S.sl_len.p, S.val.p, S.idx.p, S.rowid.p, x,
-          P, use_tma, skip, trace);
-      if (trace) {
-        std::vector<unsigned long long> h((size_t)S.n_cta * 4);
-        tbuf.download(h.data(), h.size());
-        unsigned long long t0 = ~0ull;
-        for (int g = 0; g < S.n_cta; g++) if (h[g * 4]) t0 = std::min(t0, h[g * 4]);
-        std::vector<double> a, b, c, d;
-        for (int g = 0; g < S.n_cta; g++) {
-          if (!h[g * 4]) continue;
-          a.push_back((h[g * 4] - t0) * 1e-3);
-          b.push_back((h[g * 4 + 1] - t0) * 1e-3);
-          c.push_back((h[g * 4 + 2] - t0) * 1e-3);
-          d.push_back((h[g * 4 + 3] - t0) * 1e-3);
-        }
-        auto q = [](std::vector<double>& v, double f) { std::sort(v.begin(), v.end()); return v.empty() ? 0.0 : v[(size_t)(f * (v.size() - 1))]; };
-        fprintf(stderr, "[sell trace] R=%d Cn=%d T=%d ctas=%zu us since first CTA start: start min/med/max %.1f %.1f %.1f | "
-                "x staged %.1f %.1f %.1f | first warp done %.1f %.1f %.1f | last warp done %.1f %.1f %.1f\n",
-                S.R, S.Cn, S.T, a.size(), q(a, 0), q(a, .5), q(a, 1), q(b, 0), q(b, .5), q(b, 1), q(c, 0), q(c, .5), q(c, 1),
-                q(d, 0), q(d, .5), q(d, 1));
-      }
-    } else
-      SellSpmvKernel<<<S.n_cta, kSellThreads, (size_t)S.TW * 8 + 64, ctx->stream>>>(
-          S.R, S.Cn, S.TW, S.RR, S.rows_per / 32, S.cta_begin.p, S.sl_len.p, S.voff.p, S.ioff.p, S.val.p, S.idx.p,
-          S.rowid.p, x, P, use_tma, skip);
+      auto q = [](std::vector<double>& v, double f) { std::sort(v.begin(), v.end()); return v.empty() ? 0.0 : v[(size_t)(f * (v.size() - 1))]; };
+      fprintf(stderr, "[sell trace] R=%d Cn=%d T=%d ctas=%zu us since first CTA start: start min/med/max %.1f %.1f %.1f | "
+              "x staged %.1f %.1f %.1f | first warp done %.1f %.1f %.1f | last warp done %.1f %.1f %.1f\n",
+              S.R, S.Cn, S.T, a.size(), q(a, 0), q(a, .5), q(a, 1), q(b, 0), q(b, .5), q(b, 1), q(c, 0), q(c, .5), q(c, 1),
+              q(d, 0), q(d, .5), q(d, 1));
+    }
+    }
     ctx->count_launch();
   }
   return P;
