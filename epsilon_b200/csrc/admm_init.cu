@@ -78,6 +78,7 @@ const char* TypeName(int t) {
     case EPS_PROX_SUM_QUANTILE: return "SUM_QUANTILE";
     case EPS_PROX_NORM_2: return "NORM_2";
     case EPS_PROX_MAX: return "MAX";
+    case EPS_PROX_SUM_LARGEST: return "SUM_LARGEST";
     case EPS_PROX_SUM_KL_DIV: return "SUM_KL_DIV";
     case EPS_PROX_TOTAL_VARIATION_1D: return "TOTAL_VARIATION_1D";
     default: return "?";
@@ -296,6 +297,10 @@ void eps_solver::Init(const eps_problem& original) {
       if (f.type == EPS_PROX_SUM_KL_DIV)
         EPS_CHECK(f.args.size() == 2 && f.args[0].rows == f.args[1].rows, "SUM_KL_DIV takes two equal-sized arguments");
       if (f.type == EPS_PROX_MAX && !f.epigraph) EPS_CHECK(f.args.size() == 1, "MAX takes one argument");
+      if (f.type == EPS_PROX_SUM_LARGEST) {
+        EPS_CHECK(f.args.size() == 1 && !f.epigraph, "SUM_LARGEST takes one argument (the epigraph form has no device operator)");
+        d.k = f.sum_largest_k;
+      }
       op.g_off = -1;
       if (!g_hosts[i].empty()) {
         op.g_off = (int64_t)consts_host.size();

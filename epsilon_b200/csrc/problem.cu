@@ -71,6 +71,13 @@ int eps_problem_prox_zone(eps_problem* p, int prox_index, double zone_m, const d
   EPS_API_END
 }
 
+int eps_problem_prox_sum_largest(eps_problem* p, int prox_index, int k) {
+  EPS_API_BEGIN
+  EPS_CHECK(p && prox_index >= 0 && prox_index < (int)p->prox.size() && k >= 0, "prox index %d, k %d", prox_index, k);
+  p->prox[prox_index].sum_largest_k = k;
+  EPS_API_END
+}
+
 int eps_problem_prox_add_arg(eps_problem* p, int prox_index, int rows, int* arg_index) {
   EPS_API_BEGIN
   EPS_CHECK(p && prox_index >= 0 && prox_index < (int)p->prox.size() && rows >= 0, "prox index %d", prox_index);

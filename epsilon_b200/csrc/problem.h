@@ -23,6 +23,7 @@ struct ProxFn {
   double alpha = 1.0;
   bool epigraph = false;
   double zone_m = 0.0;
+  int sum_largest_k = 0;
   std::vector<double> q_alpha, q_beta;
   std::vector<AffineExpr> args;
 };

@@ -72,9 +72,10 @@ struct VecOpDesc {
   int64_t rows = 0;      // all rows (n0 + 1 for the epigraph forms, 2*n0 for SUM_KL_DIV)
   double lam = 0;        // VectorProx lambda (alpha * beta^2 / gamma)
   double zone_m = 0, zone_alpha = 1, zone_beta = 1;
+  int k = 0;             // SUM_LARGEST: sum_largest_params.k
 };
 struct VecOpWork {
-  DevBuf<double> keys, keys2, vals, vals2, scan1, scan2, scal;
+  DevBuf<double> keys, keys2, vals, vals2, scan1, scan2, scal, ev, ent;
   DevBuf<int> idx;
   DevBuf<char> tmp;
 };

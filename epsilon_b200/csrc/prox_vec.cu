@@ -11,6 +11,7 @@
 // index at which the reference's loop would stop.  Results differ from the reference by the
 // summation order of the prefix sums only (~1e-16 relative).  No host synchronisation: every
 // decision stays in device scalars, so the stage can sit inside a captured iteration.
+#include <cooperative_groups.h>
 #include <cub/cub.cuh>
 #include <thrust/complex.h>
 
@@ -187,17 +188,213 @@ __global__ void ZoneApplyKernel(int64_t n, double M, double a, double b, double*
   if (blockIdx.x == 0 && threadIdx.x == 0) V[n] = s + lam;
 }
 
+// ---- SUM_LARGEST (sum_largest.cc:17-58) -------------------------------------------------------
+// The reference sweeps two pointers over the sorted values: i adds y_i ("enters the window
+// [q, q + lam)"), j adds -(y_j - lam) ("leaves it, saturated"); the larger of y_i and y_j - lam
+// goes first.  That is a merge of two descending lists: here the 2n events are sorted once
+// (stable, enters first on ties), prefix sums give the state before every event, and the first
+// event at which the reference's loop would stop is found in parallel.
+__global__ void LargestEventsKernel(int64_t n, double lam, const double* __restrict__ Y, double* __restrict__ E,
+                                    double* __restrict__ tag) {
+  for (int64_t i = (int64_t)blockIdx.x * kBlock + threadIdx.x; i < n; i += (int64_t)gridDim.x * kBlock) {
+    E[i] = Y[i];
+    tag[i] = 1.0;          // enter: +value, +1 inside
+    E[n + i] = Y[i] - lam;
+    tag[n + i] = -1.0;     // leave: -value, -1 inside
+  }
+}
+
+// acc contribution tag*E -> C; enters (tag > 0) -> ENT
+__global__ void LargestContribKernel(int64_t n2, const double* __restrict__ E, const double* __restrict__ tag,
+                                     double* __restrict__ C, double* __restrict__ ENT) {
+  for (int64_t i = (int64_t)blockIdx.x * kBlock + threadIdx.x; i < n2; i += (int64_t)gridDim.x * kBlock) {
+    C[i] = tag[i] * E[i];
+    ENT[i] = tag[i] > 0 ? 1.0 : 0.0;
+  }
+}
+
+__global__ void LargestBreakKernel(int64_t n, double lam, double klam, const double* __restrict__ Y,
+                                   const double* __restrict__ ACC, const double* __restrict__ INS,
+                                   const double* __restrict__ ENT, int* __restrict__ idx) {
+  const int64_t n2 = 2 * n;
+  for (int64_t e = (int64_t)blockIdx.x * kBlock + threadIdx.x; e < n2; e += (int64_t)gridDim.x * kBlock) {
+    const double acc = -klam + (e > 0 ? ACC[e - 1] : 0.0);
+    const double ins = e > 0 ? INS[e - 1] : 0.0;
+    const int64_t i = e > 0 ? (int64_t)ENT[e - 1] : 0;
+    const int64_t j = e - i;
+    bool stop = !(i < n && j < n);
+    if (!stop) stop = Y[i] * ins <= acc && (Y[j] - lam) * ins <= acc;
+    if (stop) atomicMin(idx, (int)e);
+  }
+}
+
+__global__ void LargestApplyKernel(int64_t n, double lam, double klam, double* __restrict__ V,
+                                   const double* __restrict__ ACC, const double* __restrict__ INS,
+                                   const int* __restrict__ idx) {
+  const int64_t e = min((int64_t)idx[0], 2 * n);
+  const double q = e > 0 ? (-klam + ACC[e - 1]) / INS[e - 1] : 0.0;
+  for (int64_t i = (int64_t)blockIdx.x * kBlock + threadIdx.x; i < n; i += (int64_t)gridDim.x * kBlock) {
+    const double v = V[i];
+    V[i] = v - fmax(0.0, fmin(lam, v - q));
+  }
+}
+
+// ---- NewtonEpigraph (newton.cc:108-185): SUM_EXP, SUM_LOGISTIC, SUM_INV_POS epigraphs --------
+// Newton on (x, t, lam) for the projection onto {f(x) <= t}; the KKT matrix is an arrowhead, so a
+// step needs sum_i g_i^2 / (1 + lam h_i) and every line-search trial the norm of the residual.
+// One cooperative kernel runs the whole iteration: a thread owns the same elements in every pass
+// (x lives in V, trial points in `xn`), the scalars (t, lam, theta, ...) are recomputed
+// identically by every CTA from per-CTA partial sums added in a fixed order after a grid sync.
+template <int TYPE>
+struct EpiFn {
+  static __device__ __forceinline__ double f(double x) {
+    if (TYPE == EPS_PROX_SUM_EXP) return exp(x);
+    if (TYPE == EPS_PROX_SUM_LOGISTIC) return log(1 + exp(x));
+    return 1 / x;
+  }
+  static __device__ __forceinline__ double grad(double x) {
+    if (TYPE == EPS_PROX_SUM_EXP) return exp(x);
+    if (TYPE == EPS_PROX_SUM_LOGISTIC) { const double e = exp(x); return e / (1 + e); }
+    return -1 / (x * x);
+  }
+  static __device__ __forceinline__ double hess(double x) {
+    if (TYPE == EPS_PROX_SUM_EXP) return exp(x);
+    if (TYPE == EPS_PROX_SUM_LOGISTIC) { const double e = exp(x); return e / ((1 + e) * (1 + e)); }
+    return 2 / (x * x * x);
+  }
+  static __device__ __forceinline__ double proj(double x) {
+    return TYPE == EPS_PROX_SUM_INV_POS ? fmax(x, 1e-6) : x;
+  }
+};
+
+constexpr int kEpiBlock = 256;
+
+// Grid-wide sums of K values per thread, identical in every thread of every CTA on return.
+template <int K>
+__device__ __forceinline__ void GridSums(double (&v)[K], double* partials, int& toggle, double* smem) {
+  namespace cg = cooperative_groups;
+  const int G = gridDim.x;
+  double* P = partials + (size_t)toggle * K * G;
+  toggle ^= 1;
+  BlockSum<K>(v, smem);
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int k = 0; k < K; k++) P[k * G + blockIdx.x] = v[k];
+  }
+  cg::this_grid().sync();
+  double acc[K];
+#pragma unroll
+  for (int k = 0; k < K; k++) {
+    double t = 0.0;
+    for (int i = threadIdx.x; i < G; i += blockDim.x) t += __ldcg(&P[k * G + i]);
+    acc[k] = t;
+  }
+  BlockSum<K>(acc, smem);
+  __shared__ double total_[K];
+  __syncthreads();
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int k = 0; k < K; k++) total_[k] = acc[k];
+  }
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < K; k++) v[k] = total_[k];
+  __syncthreads();
+}
+
+template <int TYPE>
+__global__ void __launch_bounds__(kEpiBlock)
+NewtonEpiKernel(int64_t n, double* __restrict__ V, const double* __restrict__ v0, double* __restrict__ xn,
+                double* __restrict__ partials) {
+  __shared__ double smem[3 * 32];
+  typedef EpiFn<TYPE> F;
+  const int64_t first = (int64_t)blockIdx.x * kEpiBlock + threadIdx.x;
+  const int64_t stride = (int64_t)gridDim.x * kEpiBlock;
+  const double s = V[n];
+  const double eps = fmax(1e-12, 1e-10 / (double)n);
+  int toggle = 0;
+  // x = proj_feasible(v); the easy case: v feasible and f(v) <= s
+  {
+    double a[2] = {0.0, 0.0};
+    for (int64_t i = first; i < n; i += stride) {
+      const double vi = v0[i], xi = F::proj(vi);
+      V[i] = xi;
+      a[0] += (vi - xi) * (vi - xi);
+      a[1] += F::f(xi);
+    }
+    GridSums<2>(a, partials, toggle, smem);
+    if (sqrt(a[0]) < eps && a[1] <= s) {
+      for (int64_t i = first; i < n; i += stride) V[i] = v0[i];
+      return;
+    }
+  }
+  double t = s, lam = 1.0;
+  for (int iter = 0; iter < 100; iter++) {
+    // residual at (x, t, lam) and the Newton step of the arrowhead system
+    double a[3] = {0.0, 0.0, 0.0};
+    for (int64_t i = first; i < n; i += stride) {
+      const double xi = V[i];
+      const double g = xi - v0[i] + lam * F::grad(xi);
+      a[0] += g * g;
+      a[1] += g * (g / (1.0 + lam * F::hess(xi)));
+      a[2] += F::f(xi);
+    }
+    GridSums<3>(a, partials, toggle, smem);
+    const double gn = t - s - lam, gn1 = a[2] - t, nt_res = a[1];
+    double x_res = sqrt(a[0] + gn * gn + gn1 * gn1);
+    const double scale = (-nt_res + gn + gn1) / (nt_res + 1);
+    const double step_t = gn - scale, step_l = -scale;
+    double theta = 1.0;
+    while (theta > eps) {
+      const double nt = t - theta * step_t;
+      double nlam = lam - theta * step_l;
+      if (nlam < eps) nlam = eps;
+      double b[2] = {0.0, 0.0};
+      for (int64_t i = first; i < n; i += stride) {
+        const double xi = V[i];
+        const double g = xi - v0[i] + lam * F::grad(xi);
+        const double nx = F::proj(xi - theta * ((1 + scale) * (g / (1.0 + lam * F::hess(xi)))));
+        xn[i] = nx;
+        const double r = nx - v0[i] + nlam * F::grad(nx);
+        b[0] += r * r;
+        b[1] += F::f(nx);
+      }
+      GridSums<2>(b, partials, toggle, smem);
+      const double r1 = nt - s - nlam, r2 = b[1] - nt;
+      const double nx_res = sqrt(b[0] + r1 * r1 + r2 * r2);
+      if (nx_res <= (1 - 0.001 * theta) * x_res) {
+        for (int64_t i = first; i < n; i += stride) V[i] = xn[i];
+        t = nt; lam = nlam; x_res = nx_res;
+        break;
+      }
+      theta *= 0.5;
+    }
+    if (x_res < eps) break;
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) V[n] = t;
+}
+
 }  // namespace
 
 bool IsVecOpType(int type, bool epigraph) {
   if (epigraph)
     return type == EPS_PROX_SUM_SQUARE || type == EPS_PROX_MAX || type == EPS_PROX_NORM_1 ||
-           type == EPS_PROX_SUM_HINGE || type == EPS_PROX_SUM_DEADZONE || type == EPS_PROX_SUM_QUANTILE;
-  return type == EPS_PROX_MAX || type == EPS_PROX_SUM_KL_DIV;
+           type == EPS_PROX_SUM_HINGE || type == EPS_PROX_SUM_DEADZONE || type == EPS_PROX_SUM_QUANTILE ||
+           type == EPS_PROX_SUM_EXP || type == EPS_PROX_SUM_LOGISTIC || type == EPS_PROX_SUM_INV_POS;
+  return type == EPS_PROX_MAX || type == EPS_PROX_SUM_KL_DIV || type == EPS_PROX_SUM_LARGEST;
+}
+
+static bool IsNewtonEpi(const VecOpDesc& d) {
+  return d.epigraph &&
+         (d.type == EPS_PROX_SUM_EXP || d.type == EPS_PROX_SUM_LOGISTIC || d.type == EPS_PROX_SUM_INV_POS);
 }
 
 static bool NeedsSort(const VecOpDesc& d) {
-  return d.type == EPS_PROX_MAX || (d.epigraph && d.type != EPS_PROX_SUM_SQUARE);
+  return d.type == EPS_PROX_MAX || d.type == EPS_PROX_SUM_LARGEST || (d.epigraph && d.type != EPS_PROX_SUM_SQUARE && !IsNewtonEpi(d));
+}
+
+static int NewtonEpiGrid(Ctx* ctx, int64_t n) {
+  return (int)std::max<int64_t>(1, std::min<int64_t>(ctx->sm_count, (n + kEpiBlock - 1) / kEpiBlock));
 }
 
 void VecOpInit(Ctx* ctx, const VecOpDesc& d, VecOpWork* w) {
@@ -205,11 +402,30 @@ void VecOpInit(Ctx* ctx, const VecOpDesc& d, VecOpWork* w) {
   w->scal.alloc(ctx, SC_COUNT);
   w->scal.zero();
   w->idx.alloc(ctx, 4);
+  if (IsNewtonEpi(d)) {
+    w->keys.alloc(ctx, d.n0);    // copy of v
+    w->keys2.alloc(ctx, d.n0);   // trial point of the line search
+    w->scan1.alloc(ctx, (size_t)2 * 3 * NewtonEpiGrid(ctx, d.n0));
+    return;
+  }
   if (!NeedsSort(d)) return;
   const int n = (int)d.n0;
+  size_t bytes = 0, b2 = 0;
+  if (d.type == EPS_PROX_SUM_LARGEST) {
+    // keys2 = sorted values (n) | keys/vals = events and tags (2n) | keys sorted -> vals2.. see VecOpApply
+    w->keys2.alloc(ctx, n);
+    w->keys.alloc(ctx, 2 * (size_t)n); w->vals.alloc(ctx, 2 * (size_t)n);
+    w->vals2.alloc(ctx, 2 * (size_t)n); w->scan1.alloc(ctx, 2 * (size_t)n); w->scan2.alloc(ctx, 2 * (size_t)n);
+    w->ev.alloc(ctx, 2 * (size_t)n); w->ent.alloc(ctx, 2 * (size_t)n);
+    CUDA_CHECK(cub::DeviceRadixSort::SortPairsDescending(nullptr, bytes, w->keys.p, w->ev.p, w->vals.p, w->vals2.p,
+                                                         2 * n, 0, 64, ctx->stream));
+    CUDA_CHECK(cub::DeviceScan::InclusiveSum(nullptr, b2, w->keys.p, w->scan1.p, 2 * n, ctx->stream));
+    bytes = std::max(bytes, b2);
+    w->tmp.alloc(ctx, bytes + 16);
+    return;
+  }
   w->keys.alloc(ctx, n); w->keys2.alloc(ctx, n);
   w->scan1.alloc(ctx, n);
-  size_t bytes = 0, b2 = 0;
   if (d.type == EPS_PROX_MAX) {
     CUDA_CHECK(cub::DeviceRadixSort::SortKeysDescending(nullptr, bytes, w->keys.p, w->keys2.p, n, 0, 64, ctx->stream));
   } else {
@@ -239,9 +455,45 @@ void VecOpApply(Ctx* ctx, const VecOpDesc& d, double* V, VecOpWork* w) {
     ctx->count_launch(2);
     return;
   }
+  if (IsNewtonEpi(d)) {
+    VecCopy(ctx, n, V, w->keys.p);
+    int64_t nn = n;
+    double* Vp = V;
+    const double* v0 = w->keys.p;
+    double *xn = w->keys2.p, *part = w->scan1.p;
+    void* args[] = {&nn, &Vp, &v0, &xn, &part};
+    const void* fn = d.type == EPS_PROX_SUM_EXP ? (const void*)NewtonEpiKernel<EPS_PROX_SUM_EXP>
+                     : d.type == EPS_PROX_SUM_LOGISTIC ? (const void*)NewtonEpiKernel<EPS_PROX_SUM_LOGISTIC>
+                                                       : (const void*)NewtonEpiKernel<EPS_PROX_SUM_INV_POS>;
+    CUDA_CHECK(cudaLaunchCooperativeKernel(fn, dim3(NewtonEpiGrid(ctx, n)), dim3(kEpiBlock), args, 0, st));
+    ctx->count_launch();
+    return;
+  }
   size_t bytes = w->tmp.n;
   const int ni = (int)n;
   PrepKernel<<<1, 1, 0, st>>>(n, d.epigraph ? 1 : 0, V, w->scal.p, w->idx.p);
+  if (d.type == EPS_PROX_SUM_LARGEST) {
+    const double klam = (double)d.k * d.lam;
+    const int n2 = 2 * ni;
+    CUDA_CHECK(cub::DeviceRadixSort::SortKeysDescending(w->tmp.p, bytes, V, w->keys2.p, ni, 0, 64, st));
+    LargestEventsKernel<<<Grid(n), kBlock, 0, st>>>(n, d.lam, w->keys2.p, w->keys.p, w->vals.p);
+    bytes = w->tmp.n;
+    CUDA_CHECK(cub::DeviceRadixSort::SortPairsDescending(w->tmp.p, bytes, w->keys.p, w->ev.p, w->vals.p, w->vals2.p,
+                                                         n2, 0, 64, st));
+    // keys <- signed contributions, vals <- enter indicator (the unsorted inputs are dead)
+    LargestContribKernel<<<Grid(2 * n), kBlock, 0, st>>>(2 * n, w->ev.p, w->vals2.p, w->keys.p, w->vals.p);
+    bytes = w->tmp.n;
+    CUDA_CHECK(cub::DeviceScan::InclusiveSum(w->tmp.p, bytes, w->keys.p, w->scan1.p, n2, st));   // ACC
+    bytes = w->tmp.n;
+    CUDA_CHECK(cub::DeviceScan::InclusiveSum(w->tmp.p, bytes, w->vals2.p, w->scan2.p, n2, st));  // INS
+    bytes = w->tmp.n;
+    CUDA_CHECK(cub::DeviceScan::InclusiveSum(w->tmp.p, bytes, w->vals.p, w->ent.p, n2, st));     // ENT
+    LargestBreakKernel<<<Grid(2 * n), kBlock, 0, st>>>(n, d.lam, klam, w->keys2.p, w->scan1.p, w->scan2.p, w->ent.p,
+                                                       w->idx.p);
+    LargestApplyKernel<<<Grid(n), kBlock, 0, st>>>(n, d.lam, klam, V, w->scan1.p, w->scan2.p, w->idx.p);
+    ctx->count_launch(10);
+    return;
+  }
   if (d.type == EPS_PROX_MAX) {
     CUDA_CHECK(cub::DeviceRadixSort::SortKeysDescending(w->tmp.p, bytes, V, w->keys2.p, ni, 0, 64, st));
     bytes = w->tmp.n;

@@ -40,6 +40,7 @@ PROX_TYPES = {
     "SUM_QUANTILE": 31,
     "MAX": 101,
     "NORM_2": 102,
+    "SUM_LARGEST": 105,
     "TOTAL_VARIATION_1D": 106,
 }
 

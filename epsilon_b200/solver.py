@@ -186,6 +186,8 @@ class _ProblemBuilder:
                     self.handle, fi.value, float(f.zone_m),
                     capi.dptr(qa) if qa is not None else None,
                     capi.dptr(qb) if qb is not None else None, nq))
+            if f.type == "SUM_LARGEST":
+                capi.check(self.lib.eps_problem_prox_sum_largest(self.handle, fi.value, int(f.sum_largest_k)))
             for ai_, a in enumerate(f.args):
                 ai = C.c_int()
                 capi.check(self.lib.eps_problem_prox_add_arg(self.handle, fi.value, a.rows, C.byref(ai)))

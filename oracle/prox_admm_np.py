@@ -299,6 +299,57 @@ def kl_div_prox(lam: np.ndarray, u: np.ndarray, v: np.ndarray):
         x[i] = y[i] * yhat
     return x, y
 
+
+# eval of the ElemwiseSmoothFunction classes (sum over the elements)
+SMOOTH_EVAL = {
+    "SUM_EXP": lambda x: float(np.sum(np.exp(x))),                       # sum_exp.cc:12-19
+    "SUM_LOGISTIC": lambda x: float(np.sum(np.log(1 + np.exp(x)))),      # sum_logistic.cc:10-17
+    "SUM_INV_POS": lambda x: float(np.sum(1 / x)),                       # sum_inv_pos.cc:12-19
+}
+
+
+def newton_epigraph(v: np.ndarray, s: float, evalf, gradf, hessf, proj=lambda x: x):
+    """NewtonEpigraph::ApplyVector, newton.cc:108-185: Newton on (x, t, lam) with the arrowhead
+    structure of the KKT system and a backtracking line search on the residual norm."""
+    n = v.size
+    eps = max(1e-12, 1e-10 / n)
+
+    def residual(lam, x, t):                                            # EpigraphResidual, newton.cc:16-27
+        r = np.empty(n + 2)
+        r[:n] = x - v + lam * gradf(x)
+        r[n] = t - s - lam
+        r[n + 1] = evalf(x) - t
+        return r
+
+    with np.errstate(all="ignore"):
+        x = proj(v.copy())
+        if float(np.linalg.norm(v - x)) < eps and evalf(x) <= s:
+            return v.copy(), s
+        t, lam = s, 1.0
+        for _ in range(100):
+            g = residual(lam, x, t)
+            nt_step = g[:n] / (1.0 + lam * hessf(x))
+            nt_res = float(g[:n] @ nt_step)
+            scale = (-nt_res + g[n] + g[n + 1]) / (nt_res + 1)
+            step_x = (1 + scale) * nt_step
+            step_t = g[n] - scale
+            step_l = -scale
+            theta, x_res = 1.0, float(np.linalg.norm(g))
+            while theta > eps:
+                nx = proj(x - theta * step_x)
+                nt = t - theta * step_t
+                nlam = lam - theta * step_l
+                if nlam < eps:
+                    nlam = eps
+                nx_res = float(np.linalg.norm(residual(nlam, nx, nt)))
+                if nx_res <= (1 - 0.001 * theta) * x_res:
+                    x, t, lam, x_res = nx, nt, nlam, nx_res
+                    break
+                theta *= 0.5
+            if x_res < eps:
+                break
+    return x, t
+
 # ---------------------------------------------------------------------------
 # 1-D total variation (C restatement in oracle/tv1d_dp.c; pure Python for small n)
 # ---------------------------------------------------------------------------
@@ -539,6 +590,12 @@ class _VectorProx:
             assert np.ndim(al) == 0 or np.all(al == al[0]), "epigraph with vector alpha/beta"
             a0 = float(np.ravel(al)[0]); b0 = float(np.ravel(be)[0])
             xo, to = scaled_zone_epigraph(x, s, a0, b0, M)
+        elif t in SMOOTH_EVAL:
+            if t == "SUM_LOGISTIC":
+                gradf, hessf, proj = _logistic_grad, _logistic_hess, (lambda z: z)
+            else:
+                gradf, hessf, proj = SMOOTH[t]
+            xo, to = newton_epigraph(x, s, SMOOTH_EVAL[t], gradf, hessf, proj)
         else:
             raise ValueError("no restatement for epigraph type %s" % t)
         return np.concatenate([xo, [to]])

@@ -179,6 +179,17 @@ def prox_cases():
     xk, yk = Variable("x", 800), Variable("y", 800)
     out["sum_kl_div"] = (ProxFunction("SUM_KL_DIV", alpha=1.2, args=[Affine(800, [Term(xk)]), Affine(800, [Term(yk)])]),
                          0.8, {"x": rng2.random(800) * 3 + 0.1, "y": rng2.random(800) * 3 + 0.1})
+    # NewtonEpigraph (newton.cc:108-185)
+    n = 1000
+    out["sum_exp_epigraph"] = (epi("SUM_EXP", n), 1.0, {"x": rng2.standard_normal(n), "t": np.array([300.0])})
+    out["sum_exp_epigraph_inside"] = (epi("SUM_EXP", 50), 1.0, {"x": rng2.standard_normal(50) - 3,
+                                                               "t": np.array([100.0])})
+    out["sum_logistic_epigraph"] = (epi("SUM_LOGISTIC", n), 1.0, {"x": rng2.standard_normal(n) * 2,
+                                                                 "t": np.array([400.0])})
+    out["sum_inv_pos_epigraph"] = (epi("SUM_INV_POS", n), 1.0, {"x": rng2.random(n) * 2 + 0.2,
+                                                               "t": np.array([500.0])})
+    out["sum_inv_pos_epigraph_infeasible"] = (epi("SUM_INV_POS", 100), 1.0, {"x": rng2.standard_normal(100),
+                                                                            "t": np.array([50.0])})
     return out
 
 

@@ -106,8 +106,6 @@ PROX_TOL = {"NORM_1": 0.0, "SUM_HINGE": 0.0, "SUM_DEADZONE": 0.0, "SUM_QUANTILE"
 @pytest.mark.parametrize("name", sorted(INDEX["prox"]))
 def test_prox_matches_reference_golden(ctx, name):
     f, lam, v = make_golden.prox_cases()[name]
-    if f.type == "SUM_LARGEST":
-        pytest.skip("SUM_LARGEST: oracle restatement only, no device operator yet")
     gold = np.load(os.path.join(GOLDEN, "prox_" + name + ".npz"))
     x = eval_prox(f, lam, v, ctx=ctx)
     tol = 1e-12 if (f.epigraph or f.type in ("MAX", "SUM_LARGEST", "SUM_KL_DIV")) else PROX_TOL[f.type]
