@@ -79,6 +79,7 @@ const char* TypeName(int t) {
     case EPS_PROX_NORM_2: return "NORM_2";
     case EPS_PROX_MAX: return "MAX";
     case EPS_PROX_SUM_LARGEST: return "SUM_LARGEST";
+    case EPS_PROX_SECOND_ORDER_CONE: return "SECOND_ORDER_CONE";
     case EPS_PROX_SUM_KL_DIV: return "SUM_KL_DIV";
     case EPS_PROX_TOTAL_VARIATION_1D: return "TOTAL_VARIATION_1D";
     default: return "?";
@@ -251,7 +252,49 @@ void eps_solver::Init(const eps_problem& original) {
   for (int i = 0; i < N; i++) {
     ProxOp& op = ops[i];
     const ProxFn& f = p.prox[i];
-    if (IsVecOpType(f.type, f.epigraph)) {
+    if (f.type == EPS_PROX_SECOND_ORDER_CONE) {
+      // SecondOrderConeProx::Init (second_order_cone.cc:30-104): arguments (at t + gt, ax X + gx), both scalar
+      // multiples of whole variables; A'A the same scalar on t and x.  In the stage's terms:
+      // V = P (A'w / alphaA) + [gt/at ; gx/ax] with P the variable -> argument permutation,
+      // x = P'(V' - shift).
+      BlockOp& H = Hs[i];
+      const int m = f.soc_m, n = f.soc_n;
+      EPS_CHECK(f.args.size() == 2 && f.args[0].rows == m && f.args[1].rows == (int64_t)m * n && !f.epigraph,
+                "prox %d (SECOND_ORDER_CONE): arguments (t: m, X: m x n) with m = %d, n = %d", i, m, n);
+      EPS_CHECK(H.blks.size() == 2 && rows_h[i] == op.n, "prox %d (SECOND_ORDER_CONE): one variable per argument", i);
+      double at = 0, ax = 0;
+      op.Hop.ctx = ctx; op.Hop.rows = H.rows; op.Hop.cols = H.cols;
+      for (auto& b : H.blks) {
+        EPS_CHECK(b.map->kind == MK_SCALAR, "prox %d (SECOND_ORDER_CONE): arguments must be scalar multiples of variables", i);
+        const double h = b.scale * b.map->alpha;
+        if (b.row_off == 0) at = h; else ax = h;
+        Blk pb;
+        pb.row_off = b.row_off; pb.col_off = b.col_off;
+        pb.map = IdentityMap(ctx, b.m());
+        op.Hop.blks.push_back(pb);
+      }
+      EPS_CHECK(at > 0 && ax != 0, "prox %d (SECOND_ORDER_CONE): at = %g, ax = %g", i, at, ax);
+      op.Hop.Compile();
+      std::vector<double> da;
+      EPS_CHECK(op.A.GramDiagonal(&da), "prox %d (SECOND_ORDER_CONE): A'A must be diagonal", i);
+      for (int64_t j = 0; j < op.n; j++) EPS_CHECK(da[j] == da[0] && da[0] > 0, "A'A not scalar matrix");
+      op.rows_h = rows_h[i];
+      op.vec_bg = 1 / da[0];
+      op.vec_cinv = 1.0;
+      VecOpDesc& d = op.vdesc;
+      d.type = f.type; d.epigraph = false;
+      d.n0 = m; d.rows = rows_h[i]; d.soc_n = n; d.soc_a = at / std::fabs(ax);
+      op.g_off = -1;
+      if (!g_hosts[i].empty()) {
+        op.g_off = (int64_t)consts_host.size();
+        for (int64_t j = 0; j < op.rows_h; j++) consts_host.push_back(g_hosts[i][j] / (j < m ? at : ax));
+      }
+      op.vbuf.alloc(ctx, op.rows_h);
+      op.vtmp.alloc(ctx, op.n);
+      VecOpInit(ctx, d, &op.vwork);
+      description += Format("prox %d SECOND_ORDER_CONE m=%d n=%d a=%g span=[%lld,+%lld)\n", i, m, n, d.soc_a,
+                            (long long)op.span_lo, (long long)op.span_len);
+    } else if (IsVecOpType(f.type, f.epigraph)) {
       // VectorProx::InitScalar (vector_prox.cc:51-70) with several arguments: every argument is
       // a scalar multiple of one whole variable; H'H = beta I and H A'A H' = gamma I.
       BlockOp& H = Hs[i];

@@ -24,6 +24,7 @@ struct ProxFn {
   bool epigraph = false;
   double zone_m = 0.0;
   int sum_largest_k = 0;
+  int soc_m = 0, soc_n = 0;
   std::vector<double> q_alpha, q_beta;
   std::vector<AffineExpr> args;
 };

@@ -73,6 +73,8 @@ struct VecOpDesc {
   double lam = 0;        // VectorProx lambda (alpha * beta^2 / gamma)
   double zone_m = 0, zone_alpha = 1, zone_beta = 1;
   int k = 0;             // SUM_LARGEST: sum_largest_params.k
+  int64_t soc_n = 0;     // SECOND_ORDER_CONE: columns of X (n0 = m rows)
+  double soc_a = 1;      // at / |ax|
 };
 struct VecOpWork {
   DevBuf<double> keys, keys2, vals, vals2, scan1, scan2, scal, ev, ent;

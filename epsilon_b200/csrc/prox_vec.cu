@@ -239,6 +239,30 @@ __global__ void LargestApplyKernel(int64_t n, double lam, double klam, double* _
   }
 }
 
+// ---- SECOND_ORDER_CONE (second_order_cone.cc:54-70): rows of [t X] onto ||X_i|| <= beta t_i ----
+// V = [t (m) | X (m x n, column-major)]; one thread per row, coalesced across rows.
+__global__ void SocProjectKernel(int64_t m, int64_t n, double beta, double* __restrict__ V) {
+  const int64_t i = (int64_t)blockIdx.x * kBlock + threadIdx.x;
+  if (i >= m) return;
+  double* X = V + m;
+  double ss = 0.0;
+  for (int64_t j = 0; j < n; j++) { const double x = X[i + j * m]; ss += x * x; }
+  const double vn = sqrt(ss);
+  const double beta2 = beta * beta;
+  double t = V[i];
+  double alpha = (1 / (beta2 + 1)) * (beta2 + beta * t / vn);
+  if (isnan(alpha) || alpha > 1) {
+    alpha = 1;
+  } else if (alpha < 0) {
+    alpha = 0;
+    t = 0;
+  } else {
+    t = (1 / beta) * alpha * vn;
+  }
+  V[i] = t;
+  for (int64_t j = 0; j < n; j++) X[i + j * m] = alpha * X[i + j * m];
+}
+
 // ---- NewtonEpigraph (newton.cc:108-185): SUM_EXP, SUM_LOGISTIC, SUM_INV_POS epigraphs --------
 // Newton on (x, t, lam) for the projection onto {f(x) <= t}; the KKT matrix is an arrowhead, so a
 // step needs sum_i g_i^2 / (1 + lam h_i) and every line-search trial the norm of the residual.
@@ -381,7 +405,8 @@ bool IsVecOpType(int type, bool epigraph) {
     return type == EPS_PROX_SUM_SQUARE || type == EPS_PROX_MAX || type == EPS_PROX_NORM_1 ||
            type == EPS_PROX_SUM_HINGE || type == EPS_PROX_SUM_DEADZONE || type == EPS_PROX_SUM_QUANTILE ||
            type == EPS_PROX_SUM_EXP || type == EPS_PROX_SUM_LOGISTIC || type == EPS_PROX_SUM_INV_POS;
-  return type == EPS_PROX_MAX || type == EPS_PROX_SUM_KL_DIV || type == EPS_PROX_SUM_LARGEST;
+  return type == EPS_PROX_MAX || type == EPS_PROX_SUM_KL_DIV || type == EPS_PROX_SUM_LARGEST ||
+         type == EPS_PROX_SECOND_ORDER_CONE;
 }
 
 static bool IsNewtonEpi(const VecOpDesc& d) {
@@ -443,6 +468,11 @@ void VecOpInit(Ctx* ctx, const VecOpDesc& d, VecOpWork* w) {
 void VecOpApply(Ctx* ctx, const VecOpDesc& d, double* V, VecOpWork* w) {
   const int64_t n = d.n0;
   cudaStream_t st = ctx->stream;
+  if (d.type == EPS_PROX_SECOND_ORDER_CONE) {
+    SocProjectKernel<<<Grid(n), kBlock, 0, st>>>(n, d.soc_n, d.soc_a, V);
+    ctx->count_launch();
+    return;
+  }
   if (d.type == EPS_PROX_SUM_KL_DIV && !d.epigraph) {
     KlDivKernel<<<Grid(n), kBlock, 0, st>>>(n, d.lam, V);
     ctx->count_launch();

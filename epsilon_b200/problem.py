@@ -16,7 +16,7 @@ ADD, CONSTANT, LINEAR_MAP, VARIABLE (affine.cc:102-108).
 from __future__ import annotations
 
 from dataclasses import dataclass, field
-from typing import Dict, List, Optional, Sequence, Union
+from typing import Tuple, Dict, List, Optional, Sequence, Union
 
 import numpy as np
 import scipy.sparse as sp
@@ -40,6 +40,7 @@ PROX_TYPES = {
     "SUM_QUANTILE": 31,
     "MAX": 101,
     "NORM_2": 102,
+    "SECOND_ORDER_CONE": 104,
     "SUM_LARGEST": 105,
     "TOTAL_VARIATION_1D": 106,
 }
@@ -149,6 +150,8 @@ class ProxFunction:
     quantile_beta: Optional[np.ndarray] = None
     # sum_largest_params.k for SUM_LARGEST (sum_largest.cc:12)
     sum_largest_k: int = 0
+    # SECOND_ORDER_CONE: (m, n) of the matrix argument X (arg_size(1), second_order_cone.cc:31-35)
+    soc_dims: Optional[Tuple[int, int]] = None
 
 
 @dataclass

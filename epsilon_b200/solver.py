@@ -186,6 +186,9 @@ class _ProblemBuilder:
                     self.handle, fi.value, float(f.zone_m),
                     capi.dptr(qa) if qa is not None else None,
                     capi.dptr(qb) if qb is not None else None, nq))
+            if f.type == "SECOND_ORDER_CONE":
+                capi.check(self.lib.eps_problem_prox_soc_dims(self.handle, fi.value, int(f.soc_dims[0]),
+                                                              int(f.soc_dims[1])))
             if f.type == "SUM_LARGEST":
                 capi.check(self.lib.eps_problem_prox_sum_largest(self.handle, fi.value, int(f.sum_largest_k)))
             for ai_, a in enumerate(f.args):

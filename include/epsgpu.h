@@ -55,6 +55,7 @@ enum eps_prox_type {
   EPS_PROX_SUM_QUANTILE = 31,
   EPS_PROX_MAX = 101,
   EPS_PROX_NORM_2 = 102,
+  EPS_PROX_SECOND_ORDER_CONE = 104,
   EPS_PROX_SUM_LARGEST = 105,
   EPS_PROX_TOTAL_VARIATION_1D = 106
 };
@@ -155,6 +156,9 @@ int eps_problem_prox_zone(eps_problem* p, int prox_index, double zone_m,
                           const double* q_alpha, const double* q_beta, int n_q);
 /* sum_largest_params.k for SUM_LARGEST (sum_largest.cc:10-13). */
 int eps_problem_prox_sum_largest(eps_problem* p, int prox_index, int k);
+/* SECOND_ORDER_CONE: arguments (t in R^m, X in R^{m x n} column-major); m, n = arg_size(1)
+ * (second_order_cone.cc:31-35). */
+int eps_problem_prox_soc_dims(eps_problem* p, int prox_index, int m, int n);
 int eps_problem_prox_add_arg(eps_problem* p, int prox_index, int rows, int* arg_index);
 /* Row-sharded argument (multi-GPU): the rows given to this rank are its slice of an
  * argument with `global_rows` rows; products H'H p and H'g are all-reduced. */

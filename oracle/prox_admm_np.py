@@ -642,7 +642,58 @@ class _VectorProx:
         return out
 
 
+class _SocProx:
+    """SecondOrderConeProx, second_order_cone.cc:30-110: rows of [t X] projected onto
+    ||ax x_i + bx_i|| <= at t_i + bt_i; arguments (t, X), X in R^{m x n} column-major."""
+
+    def __init__(self, f, H, g, A, arg_cols):
+        m, n = f.soc_dims
+        H, A = sp.csr_matrix(H), sp.csr_matrix(A)
+        self.m, self.n = m, n
+        # H is [at I on t ; ax I on x] up to the column order of the variables
+        Hd = H.tocoo()
+        self.tcols = np.empty(m, dtype=np.int64); self.xcols = np.empty(m * n, dtype=np.int64)
+        at = ax = None
+        for r, c, val in zip(Hd.row, Hd.col, Hd.data):
+            if r < m:
+                self.tcols[r] = c; at = val
+            else:
+                self.xcols[r - m] = c; ax = val
+        ata = _diag_if_diagonal(A.T @ A)
+        assert ata is not None and np.all(ata == ata[0]), "A'A not scalar matrix"
+        self.AT = (1.0 / ata[0]) * A.T                                   # InitConstraints :93-104
+        g = np.zeros(m + m * n) if g is None or np.size(g) == 0 else np.asarray(g, dtype=np.float64)
+        self.a = at / abs(ax)                                           # InitArgs :76-90
+        self.bx = g[m:] / ax
+        self.bt = g[:m] / abs(ax)
+        self.ncols = H.shape[1]
+
+    def apply(self, v: np.ndarray) -> np.ndarray:
+        u = np.asarray(self.AT @ v).ravel()
+        X = (u[self.xcols] + self.bx).reshape((self.m, self.n), order="F")
+        t = u[self.tcols] + self.bt / self.a
+        beta = self.a
+        with np.errstate(all="ignore"):
+            vn = np.sqrt((X * X).sum(axis=1))
+            alpha = (1 / (beta * beta + 1)) * (beta * beta + beta * t / vn)   # ApplyProjection :54-70
+        for i in range(self.m):
+            if np.isnan(alpha[i]) or alpha[i] > 1:
+                alpha[i] = 1
+            elif alpha[i] < 0:
+                alpha[i] = 0
+                t[i] = 0
+            else:
+                t[i] = (1 / beta) * alpha[i] * vn[i]
+        X = alpha[:, None] * X
+        out = np.zeros(self.ncols)
+        out[self.xcols] = X.ravel(order="F") - self.bx
+        out[self.tcols] = t - self.bt / self.a
+        return out
+
+
 def _make_operator(f, H, g, A):
+    if f.type == "SECOND_ORDER_CONE":
+        return _SocProx(f, H, g, A, None)
     if f.type in KKT_TYPES and not f.epigraph:
         return _KktProx(f, H, g, A)
     return _VectorProx(f, H, g, A)

@@ -90,8 +90,11 @@ class _RefWriter:
         pf = "prox_function_type: %s alpha: %s" % (f.type, repr(float(f.alpha)))
         if f.epigraph:
             pf += " epigraph: true"
-        for a in f.args:
-            pf += " arg_size { dim: %d dim: 1 }" % a.rows
+        for k, a in enumerate(f.args):
+            if f.type == "SECOND_ORDER_CONE" and k == 1:
+                pf += " arg_size { dim: %d dim: %d }" % tuple(f.soc_dims)
+            else:
+                pf += " arg_size { dim: %d dim: 1 }" % a.rows
         if f.type == "SUM_DEADZONE":
             pf += " scaled_zone_params { m: %s }" % repr(float(f.zone_m))
         if f.type == "SUM_LARGEST":

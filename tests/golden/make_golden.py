@@ -190,6 +190,23 @@ def prox_cases():
                                                                "t": np.array([500.0])})
     out["sum_inv_pos_epigraph_infeasible"] = (epi("SUM_INV_POS", 100), 1.0, {"x": rng2.standard_normal(100),
                                                                             "t": np.array([50.0])})
+
+    # SECOND_ORDER_CONE (second_order_cone.cc): rows of [t X]
+    def soc(m, n, at=1.0, ax=1.0, gt=None, gx=None):
+        t, x = Variable("t", m), Variable("x", m * n)
+        a0 = [Term(t) if at == 1.0 else Term(t, LinearMapSpec.Scalar(at, m))]
+        a1 = [Term(x) if ax == 1.0 else Term(x, LinearMapSpec.Scalar(ax, m * n))]
+        if gt is not None:
+            a0.append(Term(gt, name="gt"))
+        if gx is not None:
+            a1.append(Term(gx, name="gx"))
+        return ProxFunction("SECOND_ORDER_CONE", args=[Affine(m, a0), Affine(m * n, a1)], soc_dims=(m, n))
+
+    out["soc_rows"] = (soc(300, 7), 1.0, {"t": rng2.standard_normal(300), "x": rng2.standard_normal(2100)})
+    out["soc_scaled_shifted"] = (soc(40, 5, at=2.0, ax=-0.5, gt=rng2.standard_normal(40),
+                                     gx=rng2.standard_normal(200)), 0.7,
+                                 {"t": rng2.standard_normal(40), "x": rng2.standard_normal(200)})
+    out["soc_single_cone"] = (soc(1, 500), 1.0, {"t": np.array([0.5]), "x": rng2.standard_normal(500)})
     return out
 
 
