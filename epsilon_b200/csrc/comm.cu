@@ -105,13 +105,16 @@ void AllReduceSum(Ctx* ctx, double* buf, int64_t n) {
 
 // ---- one-shot peer all-reduce: buffers mapped into every rank through CUDA IPC -------------
 // Layout of each rank's block: [flags: 2*G u64 | counter at 2 KB | per-CTA flags 2*G*kPeerMaxCtas u64 at 4 KB,
-// head padded to 64 KB][receive: 2*G*n f64].
+// head padded to 64 KB][receive: 2*G*n f64][packet inboxes: 2*G*n + 2*n uint4].
 static void PeerSetup(Ctx* ctx, int64_t n, PeerBuf* out) {
   out->ready = false;
   const int G = ctx->n_ranks;
   const size_t head = 65536;
   static_assert(4096 + 2 * kMaxRanks * kPeerMaxCtas * 8 <= 65536, "peer header");
-  const size_t bytes = head + sizeof(double) * 2 * (size_t)G * n;
+  const size_t recv_bytes = sizeof(double) * 2 * (size_t)G * n;
+  const size_t ll1_bytes = sizeof(uint4) * 2 * (size_t)G * n, ll2_bytes = sizeof(uint4) * 2 * (size_t)n;
+  const bool use_ll = !getenv("EPS_PEER_LL") || atoi(getenv("EPS_PEER_LL")) != 0;
+  const size_t bytes = head + recv_bytes + (use_ll ? ll1_bytes + ll2_bytes : 0);
   CUDA_CHECK(cudaMalloc(&out->block, bytes));
   ctx->bytes_allocated += bytes;
   CUDA_CHECK(cudaMemsetAsync(out->block, 0, bytes, ctx->stream));
@@ -154,6 +157,8 @@ static void PeerSetup(Ctx* ctx, int64_t n, PeerBuf* out) {
     out->x.flag[r] = reinterpret_cast<unsigned long long*>(base);
     out->x.cflag[r] = reinterpret_cast<unsigned long long*>(base + 4096);
     out->x.recv[r] = reinterpret_cast<double*>(base + head);
+    out->x.ll1[r] = use_ll ? reinterpret_cast<uint4*>(base + head + recv_bytes) : nullptr;
+    out->x.ll2[r] = use_ll ? reinterpret_cast<uint4*>(base + head + recv_bytes + ll1_bytes) : nullptr;
   }
   out->counter = reinterpret_cast<unsigned*>(static_cast<char*>(out->block) + 2048);
   out->seq = 0;

@@ -227,6 +227,10 @@ struct PeerXchg {
   double* recv[kMaxRanks] = {};              // recv[r]: rank r's buffer [2][G][n], mapped here
   unsigned long long* flag[kMaxRanks] = {};  // flag[r]: rank r's flags [2][G]
   unsigned long long* cflag[kMaxRanks] = {}; // cflag[r]: rank r's per-CTA flags [2][G][kPeerMaxCtas]
+  // flag-in-data packets (16 B per double: {lo32, seq32, hi32, seq32}; every 8-byte half carries its
+  // own sequence number, so a packet needs no fence and no separate flag)
+  uint4* ll1[kMaxRanks] = {};                // ll1[r]: rank r's reduce-scatter inbox [2][G][n]
+  uint4* ll2[kMaxRanks] = {};                // ll2[r]: rank r's all-gather inbox [2][n]
   int G = 0, rank = 0;
   int64_t n = 0;   // slot stride (capacity); vectors of up to n entries fit
 };

@@ -168,7 +168,33 @@ CgFusedTailKernel(int64_t n, int T, const double* __restrict__ planes, double al
   int64_t per = (n + G - 1) / G;
   per = (per + 1) & ~(int64_t)1;
   const int64_t lo = min(n, (int64_t)c * per), hi = min(n, lo + per);
-  if (px.G > 1) {
+  const bool ll = px.G > 1 && px.ll1[0] != nullptr;
+  const unsigned seq32 = (unsigned)xseq;
+  if (ll) {
+    // two-shot exchange with flag-in-data packets: CTA c's slice is owned by rank c % G.  A thread
+    // keeps the same elements in every step, so there is no barrier, no fence and no flag:
+    //   (1) partial -> owner's inbox; (2) owner: wait for the G partials, add them in rank order,
+    //   result -> every rank's inbox; (3) everybody reads the result while forming w (below).
+    if (!finished) {
+      const int owner = c % px.G;
+      for (int64_t i = lo + threadIdx.x; i < hi; i += kTailBlock) {
+        double s = 0.0;
+        for (int t = 0; t < T; t++) s += planes[(size_t)t * n + i];
+        LlStore(px.ll1[owner] + ((size_t)parity * px.G + px.rank) * px.n + i, alpha * s, seq32);
+      }
+      EPS_TT(1);
+      if (px.rank == owner) {
+        for (int64_t i = lo + threadIdx.x; i < hi; i += kTailBlock) {
+          double sum = 0.0;
+          for (int q = 0; q < px.G; q++)
+            sum += LlLoad(px.ll1[px.rank] + ((size_t)parity * px.G + q) * px.n + i, seq32);
+          for (int k = 0; k < px.G; k++)
+            LlStore(px.ll2[(px.rank + k) % px.G] + (size_t)parity * px.n + i, sum, seq32);
+        }
+      }
+      EPS_TT(2);
+    }
+  } else if (px.G > 1) {
     if (!finished) {
       for (int64_t i = lo + threadIdx.x; i < hi; i += kTailBlock) {
         double s = 0.0;
@@ -200,7 +226,15 @@ CgFusedTailKernel(int64_t n, int T, const double* __restrict__ planes, double al
   const double rr = scal[0];
   const double thresh = scal[1];
   double v[1] = {0.0};
-  if (px.G > 1) {
+  if (ll) {
+    for (int64_t i = lo + threadIdx.x; i < hi; i += kTailBlock) {
+      const double pi = p[i];
+      const double wi = LlLoad(px.ll2[px.rank] + (size_t)parity * px.n + i, seq32) + dg[i] * pi;
+      w[i] = wi;
+      v[0] += pi * wi;
+    }
+    EPS_TT(3);
+  } else if (px.G > 1) {
     for (int64_t i = lo + threadIdx.x; i < hi; i += kTailBlock) {
       const double pi = p[i];
       const double wi = PeerSum(px, xseq, i) + dg[i] * pi;

@@ -46,4 +46,20 @@ __device__ __forceinline__ double PeerSum(const PeerXchg& px, unsigned long long
   return s;
 }
 
+// ---- flag-in-data packets -----------------------------------------------------------------
+__device__ __forceinline__ void LlStore(uint4* p, double v, unsigned seq) {
+  const unsigned long long b = (unsigned long long)__double_as_longlong(v);
+  asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"((unsigned)b), "r"(seq),
+               "r"((unsigned)(b >> 32)), "r"(seq) : "memory");
+}
+
+// Spins until both halves carry `seq`.
+__device__ __forceinline__ double LlLoad(const uint4* p, unsigned seq) {
+  unsigned a, fa, b, fb;
+  do {
+    asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(a), "=r"(fa), "=r"(b), "=r"(fb) : "l"(p) : "memory");
+  } while (fa != seq || fb != seq);
+  return __longlong_as_double((long long)(((unsigned long long)b << 32) | a));
+}
+
 }  // namespace eps
