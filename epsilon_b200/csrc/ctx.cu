@@ -60,6 +60,26 @@ ProfScope::~ProfScope() {
   ctx->prof[kc].bytes += bytes;
 }
 
+void* DevAlloc(Ctx* ctx, size_t bytes) {
+  void* p = nullptr;
+  if (ctx->pooled) CUDA_CHECK(cudaMallocAsync(&p, bytes, ctx->stream));
+  else CUDA_CHECK(cudaMalloc(&p, bytes));
+  ctx->bytes_allocated += (int64_t)bytes;
+  return p;
+}
+
+void DevFree(Ctx* ctx, void* p, size_t bytes) {
+  if (!p) return;
+  if (ctx && ctx->pooled) {
+    // stream-ordered: the memory returns to the pool after everything queued so far; a context
+    // that is already gone (static buffers at process exit) falls back to the blocking free
+    if (cudaFreeAsync(p, ctx->stream) != cudaSuccess) { cudaGetLastError(); cudaFree(p); }
+  } else {
+    cudaFree(p);
+  }
+  if (ctx) ctx->bytes_allocated -= (int64_t)bytes;
+}
+
 ReduceScratch GetReduceScratch(Ctx* ctx) {
   if (ctx->red_partials.n == 0) {
     ctx->red_partials.alloc(ctx, 4096);
@@ -209,6 +229,16 @@ int eps_ctx_create(int device, void* stream, eps_ctx** out) {
     } else {
       CUDA_CHECK(cudaStreamCreateWithFlags(&h->c.stream, cudaStreamNonBlocking));
       h->c.own_stream = true;
+    }
+    if (!getenv("EPS_NO_POOL")) {
+      // keep freed blocks in the device's default pool: the second solve of a process (same shapes)
+      // allocates in microseconds instead of paying cudaMalloc/cudaFree for every GB-sized buffer
+      cudaMemPool_t pool;
+      if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
+        uint64_t keep = ~0ull;
+        if (cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep) == cudaSuccess) h->c.pooled = true;
+      }
+      cudaGetLastError();
     }
     *out = h;
     return EPS_OK;

@@ -47,6 +47,11 @@ struct Ctx;
 void UploadBytes(Ctx* ctx, void* dst, const void* src, size_t bytes);
 
 // ---- device memory ----------------------------------------------------------------
+// Device memory of a context: stream-ordered allocations from the device's default pool (kept
+// across solves: release threshold = unlimited), cudaMalloc when EPS_NO_POOL is set.
+void* DevAlloc(Ctx* ctx, size_t bytes);
+void DevFree(Ctx* ctx, void* p, size_t bytes);
+
 template <typename T>
 struct DevBuf {
   T* p = nullptr;
@@ -66,11 +71,10 @@ struct DevBuf {
     release();
     ctx = c; n = count;
     if (count == 0) return;
-    CUDA_CHECK(cudaMalloc(&p, count * sizeof(T)));
-    ctx->bytes_allocated += count * sizeof(T);
+    p = static_cast<T*>(DevAlloc(c, count * sizeof(T)));
   }
   void release() {
-    if (p) { cudaFree(p); if (ctx) ctx->bytes_allocated -= n * sizeof(T); }
+    if (p) DevFree(ctx, p, n * sizeof(T));
     p = nullptr; n = 0;
   }
   void zero() { if (n) CUDA_CHECK(cudaMemsetAsync(p, 0, n * sizeof(T), ctx->stream)); }
@@ -98,6 +102,7 @@ struct Ctx {
   int device = 0;
   cudaStream_t stream = nullptr;
   bool own_stream = false;
+  bool pooled = false;   // DevAlloc uses cudaMallocAsync on `stream`
   int sm_count = 148;
   int64_t launches = 0;        // kernels launched outside graphs + graph-node replays
   int64_t bytes_allocated = 0;
