@@ -286,8 +286,12 @@ int eps_solver_create(eps_problem* p, const eps_params* params, eps_solver** out
 
 void eps_solver_destroy(eps_solver* s) {
   if (!s) return;
-  cudaSetDevice(s->ctx->device);
-  cudaStreamSynchronize(s->ctx->stream);
+  if (eps::CtxIsLive(s->ctx)) {
+    cudaSetDevice(s->ctx->device);
+    cudaStreamSynchronize(s->ctx->stream);
+  } else {
+    cudaDeviceSynchronize();
+  }
   delete s;
 }
 

@@ -77,6 +77,7 @@ const char* TypeName(int t) {
     case EPS_PROX_SUM_NEG_LOG: return "SUM_NEG_LOG";
     case EPS_PROX_SUM_QUANTILE: return "SUM_QUANTILE";
     case EPS_PROX_NORM_2: return "NORM_2";
+    case EPS_PROX_EXP: return "EXP";
     case EPS_PROX_MAX: return "MAX";
     case EPS_PROX_SUM_LARGEST: return "SUM_LARGEST";
     case EPS_PROX_SECOND_ORDER_CONE: return "SECOND_ORDER_CONE";
@@ -334,7 +335,10 @@ void eps_solver::Init(const eps_problem& original) {
         d.zone_alpha = f.q_alpha[0];
         d.zone_beta = f.q_beta[0];
       }
-      if (f.epigraph)
+      if (f.type == EPS_PROX_EXP)
+        EPS_CHECK(f.epigraph && f.args.size() == 2 && f.args[1].rows == f.args[0].rows,
+                  "prox %d (EXP): elementwise epigraph form over (x, t) of equal size", i);
+      else if (f.epigraph)
         EPS_CHECK(f.args.size() == 2 && f.args[1].rows == 1, "prox %d (%s): epigraph form takes (x, t)", i,
                   TypeName(f.type));
       if (f.type == EPS_PROX_SUM_KL_DIV)

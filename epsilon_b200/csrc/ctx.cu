@@ -4,6 +4,9 @@
 
 #include <thread>
 
+#include <mutex>
+#include <unordered_set>
+
 #include "internal.h"
 
 namespace eps {
@@ -26,7 +29,29 @@ std::string Format(const char* fmt, ...) {
 void SetLastError(const std::string& msg) { g_last_error = msg; }
 const std::string& LastError() { return g_last_error; }
 
+namespace {
+// Contexts that are still alive: buffers can outlive their context (a host language may finalise
+// objects in any order at exit); they must then be freed without touching it.
+std::mutex g_live_mu;
+std::unordered_set<const Ctx*> g_live;
+bool IsLive(const Ctx* c) {
+  std::lock_guard<std::mutex> lk(g_live_mu);
+  return g_live.count(c) != 0;
+}
+}  // namespace
+
+bool CtxIsLive(const Ctx* c) { return IsLive(c); }
+
+void RegisterCtx(const Ctx* c) {
+  std::lock_guard<std::mutex> lk(g_live_mu);
+  g_live.insert(c);
+}
+
 Ctx::~Ctx() {
+  {
+    std::lock_guard<std::mutex> lk(g_live_mu);
+    g_live.erase(this);
+  }
   if (comm) CommDestroy(this);
   for (int i = 0; i < 2; i++)
     if (prof_ev[i]) cudaEventDestroy(prof_ev[i]);
@@ -70,6 +95,7 @@ void* DevAlloc(Ctx* ctx, size_t bytes) {
 
 void DevFree(Ctx* ctx, void* p, size_t bytes) {
   if (!p) return;
+  if (ctx && !IsLive(ctx)) ctx = nullptr;  // context already destroyed: blocking free, no accounting
   if (ctx && ctx->pooled) {
     // stream-ordered: the memory returns to the pool after everything queued so far; a context
     // that is already gone (static buffers at process exit) falls back to the blocking free
@@ -240,6 +266,7 @@ int eps_ctx_create(int device, void* stream, eps_ctx** out) {
       }
       cudaGetLastError();
     }
+    RegisterCtx(&h->c);
     *out = h;
     return EPS_OK;
   } catch (const Error& e) {

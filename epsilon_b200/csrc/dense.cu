@@ -258,6 +258,14 @@ void DenseGramNT(Ctx* ctx, const double* A, int64_t lda, int m, int64_t n, const
   ctx->count_launch();
 }
 
+void DenseGemmRhs(Ctx* ctx, const double* A, int64_t lda, int m, int n, bool trans, double alpha,
+                  const double* X, int64_t ldx, int k, double beta, double* Y, int64_t ldy) {
+  // C[i + j ldy] = sum_kk a(i, kk) x(j, kk): a(i,kk) = A[i + kk lda] (AK = false) or A[kk + i lda] (A', AK = true);
+  // x(j,kk) = X[kk + j ldx] (BK = true)
+  if (!trans) Gemm<false, true>(ctx, m, k, n, alpha, A, lda, X, ldx, nullptr, beta, Y, ldy, false, false);
+  else Gemm<true, true>(ctx, n, k, m, alpha, A, lda, X, ldx, nullptr, beta, Y, ldy, false, false);
+}
+
 void DenseAddDiagonal(Ctx* ctx, double* M, int64_t ld, int n, const double* d, double a) {
   if (n <= 0) return;
   AddDiagKernel<<<(n + 255) / 256, 256, 0, ctx->stream>>>(n, M, ld, d, a);

@@ -49,6 +49,7 @@ void UploadBytes(Ctx* ctx, void* dst, const void* src, size_t bytes);
 // ---- device memory ----------------------------------------------------------------
 // Device memory of a context: stream-ordered allocations from the device's default pool (kept
 // across solves: release threshold = unlimited), cudaMalloc when EPS_NO_POOL is set.
+bool CtxIsLive(const Ctx* ctx);  // false once eps_ctx_destroy has run (objects may outlive their context)
 void* DevAlloc(Ctx* ctx, size_t bytes);
 void DevFree(Ctx* ctx, void* p, size_t bytes);
 
@@ -326,6 +327,10 @@ struct BlockOp {
 // C(n x n, ldc) (+)= alpha * A' A, A m x n column-major (lda).  fp64 tensor cores (DMMA).
 void DenseGramTN(Ctx* ctx, const double* A, int64_t lda, int64_t m, int n, double alpha,
                  double* C, int64_t ldc, bool accumulate);
+// Y(rows x k, ldy) = beta*Y + alpha * op(A) X(cols x k, ldx) for a few right-hand sides, on the fp64 tensor
+// path (DMMA); op(A) = A (m x n) or A' (trans).  The matrix is read once for all k columns.
+void DenseGemmRhs(Ctx* ctx, const double* A, int64_t lda, int m, int n, bool trans, double alpha,
+                  const double* X, int64_t ldx, int k, double beta, double* Y, int64_t ldy);
 // C(m x m) (+)= alpha * A diag(w) A', A m x n column-major; w may be null (ones).
 void DenseGramNT(Ctx* ctx, const double* A, int64_t lda, int m, int64_t n, const double* w,
                  double alpha, double* C, int64_t ldc, bool accumulate);

@@ -619,10 +619,40 @@ void KktSolver::MatVec(const double* p, double* w, const int* skip) {
   }
 }
 
+bool KktSolver::SolveMulti(const double* rhs, double* x, int k) {
+  if (mode == EPS_KKT_GRAM) {
+    if (mn1.n < (size_t)n * k) mn1.alloc(ctx, (size_t)n * k);
+    DenseGemmRhs(ctx, W.p, n, (int)n, (int)n, false, 1.0, rhs, n, k, 0.0, mn1.p, n);
+    DenseGemmRhs(ctx, W.p, n, (int)n, (int)n, true, 1.0, mn1.p, n, k, 0.0, x, n);
+    return true;
+  }
+  if (mode == EPS_KKT_WOODBURY) {
+    const bool single_dense = H.blks.size() == 1 && H.blks[0].map->kind == MK_DENSE && H.blks[0].row_off == 0 &&
+                              H.blks[0].col_off == 0 && H.blks[0].m() == rows_h && H.blks[0].n() == n;
+    if (!single_dense) return false;
+    const Blk& b = H.blks[0];
+    const MapData& M = *b.map;
+    if (mn1.n < (size_t)n * k) { mn1.alloc(ctx, (size_t)n * k); mn2.alloc(ctx, (size_t)n * k); }
+    if (mh1.n < (size_t)rows_h * k) { mh1.alloc(ctx, (size_t)rows_h * k); mh2.alloc(ctx, (size_t)rows_h * k); }
+    // X = D^-1 R - D^-1 H' S^-1 H D^-1 R,  S^-1 = W'W   (the single-column path of Solve, k columns at once)
+    DiagMulti(ctx, n, k, dinv.p, rhs, 0.0, nullptr, mn1.p);
+    DenseGemmRhs(ctx, M.dense.p, M.m, M.m, M.n, b.trans, b.scale, mn1.p, n, k, 0.0, mh1.p, rows_h);
+    DenseGemmRhs(ctx, W.p, rows_h, (int)rows_h, (int)rows_h, false, 1.0, mh1.p, rows_h, k, 0.0, mh2.p, rows_h);
+    DenseGemmRhs(ctx, W.p, rows_h, (int)rows_h, (int)rows_h, true, 1.0, mh2.p, rows_h, k, 0.0, mh1.p, rows_h);
+    DenseGemmRhs(ctx, M.dense.p, M.m, M.m, M.n, !b.trans, b.scale, mh1.p, rows_h, k, 0.0, mn2.p, n);
+    DiagMulti(ctx, n, k, dinv.p, mn2.p, -1.0, mn1.p, mn2.p);   // d.*(H'z) - tn1 = -x
+    VecScale(ctx, n * k, -1.0, mn2.p, x);
+    return true;
+  }
+  return false;
+}
+
 void KktSolver::Solve(const double* rhs, double* x) {
   if (inner) {
     const int64_t nb = n / kron_k;
     const int64_t before = inner->cg_iters_total;
+    static const bool no_multi = getenv("EPS_NO_KRON_GEMM") != nullptr;
+    if (!no_multi && kron_k > 1 && inner->SolveMulti(rhs, x, kron_k)) return;
     for (int c = 0; c < kron_k; c++) inner->Solve(rhs + (size_t)c * nb, x + (size_t)c * nb);
     cg_iters_total += inner->cg_iters_total - before;
     return;

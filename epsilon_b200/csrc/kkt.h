@@ -60,6 +60,10 @@ struct KktSolver {
   // x <- solution for rhs (both device, n).  x holds the warm start on entry (CG).
   void Solve(const double* rhs, double* x);
   void MatVec(const double* p, double* w, const int* skip = nullptr);  // w = (2a H'H + A'A) p
+  // k systems at once (columns of rhs / x, leading dimension n): the factor and a dense H are
+  // read once for all columns (DMMA GEMMs); returns false when this mode has no such path
+  bool SolveMulti(const double* rhs, double* x, int k);
+  DevBuf<double> mn1, mn2, mh1, mh2;  // work for SolveMulti: n*k, n*k, rows_h*k, rows_h*k
 };
 
 }  // namespace eps

@@ -85,6 +85,8 @@ bool IsVecOpType(int type, bool epigraph);
 void VecOpInit(Ctx* ctx, const VecOpDesc& d, VecOpWork* w);
 void VecOpApply(Ctx* ctx, const VecOpDesc& d, double* V, VecOpWork* w);
 
+// out[i + c n] = d[i] * in[i + c n] + b * y[i + c n]  for c < k   (y may be null)
+void DiagMulti(Ctx* ctx, int64_t n, int k, const double* d, const double* in, double b, const double* y, double* out);
 // x = dinv .* rhs
 void KktDiagSolve(Ctx* ctx, int64_t n, const double* dinv, const double* rhs, double* x);
 

@@ -242,6 +242,12 @@ void TwoBlockDualStep(Ctx* ctx, int64_t n, const double* x, const double* v, con
   ctx->count_launch();
 }
 
+void DiagMulti(Ctx* ctx, int64_t n, int k, const double* d, const double* in, double b, const double* y, double* out) {
+  LaunchElem1(ctx, n * k, KC_VEC, 32.0 * n * k, [=] __device__(int64_t i) {
+    out[i] = d[i % n] * in[i] + (y ? b * y[i] : 0.0);
+  });
+}
+
 void KktDiagSolve(Ctx* ctx, int64_t n, const double* dinv, const double* rhs, double* x) {
   LaunchElem1(ctx, n, KC_VEC, 24.0 * n, [=] __device__(int64_t i) { x[i] = dinv[i] * rhs[i]; });
 }

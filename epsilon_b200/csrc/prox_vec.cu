@@ -263,6 +263,31 @@ __global__ void SocProjectKernel(int64_t m, int64_t n, double beta, double* __re
   for (int64_t j = 0; j < n; j++) X[i + j * m] = alpha * X[i + j * m];
 }
 
+// ---- EXP epigraph (exp.cc:12-78): elementwise projection onto {exp(x_i) <= t_i} ---------------
+// V = [v (n) | s (n)] -> [x | t].  The reference iterates all elements together until the largest
+// residual is below 1e-12; here every element stops on its own residuals (same Newton steps, a
+// converged element would only move by rounding afterwards).
+__global__ void ExpEpiKernel(int64_t n, double* __restrict__ V) {
+  const double eps = 1e-12;
+  for (int64_t i = (int64_t)blockIdx.x * kBlock + threadIdx.x; i < n; i += (int64_t)gridDim.x * kBlock) {
+    const double v = V[i], s = V[n + i];
+    if (exp(v) <= s) continue;  // already feasible (exp.cc:68-74)
+    double x = v, t = s, l = 1.0;
+    for (int it = 0; it < 100; it++) {
+      const double ex = exp(x);
+      const double r0 = (x - v) + l * ex, r1 = t - s - l, r2 = ex - t;
+      if (fabs(r0) < eps && fabs(r1) < eps && fabs(r2) < eps) break;
+      const double h = 1 + l * ex, d = ex;
+      const double dl = (-d * r0 + h * (r1 + r2)) / (d * d + h);
+      const double dx = -(d * dl + r0) / h;
+      const double dt = dl - r1;
+      x += dx; t += dt; l += dl;
+    }
+    V[i] = x;
+    V[n + i] = t;
+  }
+}
+
 // ---- NewtonEpigraph (newton.cc:108-185): SUM_EXP, SUM_LOGISTIC, SUM_INV_POS epigraphs --------
 // Newton on (x, t, lam) for the projection onto {f(x) <= t}; the KKT matrix is an arrowhead, so a
 // step needs sum_i g_i^2 / (1 + lam h_i) and every line-search trial the norm of the residual.
@@ -404,7 +429,8 @@ bool IsVecOpType(int type, bool epigraph) {
   if (epigraph)
     return type == EPS_PROX_SUM_SQUARE || type == EPS_PROX_MAX || type == EPS_PROX_NORM_1 ||
            type == EPS_PROX_SUM_HINGE || type == EPS_PROX_SUM_DEADZONE || type == EPS_PROX_SUM_QUANTILE ||
-           type == EPS_PROX_SUM_EXP || type == EPS_PROX_SUM_LOGISTIC || type == EPS_PROX_SUM_INV_POS;
+           type == EPS_PROX_SUM_EXP || type == EPS_PROX_SUM_LOGISTIC || type == EPS_PROX_SUM_INV_POS ||
+           type == EPS_PROX_EXP;
   return type == EPS_PROX_MAX || type == EPS_PROX_SUM_KL_DIV || type == EPS_PROX_SUM_LARGEST ||
          type == EPS_PROX_SECOND_ORDER_CONE;
 }
@@ -468,6 +494,11 @@ void VecOpInit(Ctx* ctx, const VecOpDesc& d, VecOpWork* w) {
 void VecOpApply(Ctx* ctx, const VecOpDesc& d, double* V, VecOpWork* w) {
   const int64_t n = d.n0;
   cudaStream_t st = ctx->stream;
+  if (d.type == EPS_PROX_EXP) {
+    ExpEpiKernel<<<Grid(n), kBlock, 0, st>>>(n, V);
+    ctx->count_launch();
+    return;
+  }
   if (d.type == EPS_PROX_SECOND_ORDER_CONE) {
     SocProjectKernel<<<Grid(n), kBlock, 0, st>>>(n, d.soc_n, d.soc_a, V);
     ctx->count_launch();

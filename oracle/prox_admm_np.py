@@ -350,6 +350,30 @@ def newton_epigraph(v: np.ndarray, s: float, evalf, gradf, hessf, proj=lambda x:
                 break
     return x, t
 
+
+def exp_epigraph(v: np.ndarray, s: np.ndarray):
+    """ExpEpigraph::ApplyVector, exp.cc:12-78: elementwise projection onto {exp(x_i) <= t_i},
+    Newton on (x, t, l) for all elements at once until every residual is below 1e-12."""
+    x, t, l = v.copy(), s.copy(), np.ones(v.size)
+    eps = 1e-12
+    with np.errstate(all="ignore"):
+        for _ in range(100):
+            ex = np.exp(x)
+            r0 = (x - v) + l * ex
+            r1 = t - s - l
+            r2 = ex - t
+            if np.abs(r0).max() < eps and np.abs(r1).max() < eps and np.abs(r2).max() < eps:
+                break
+            h = 1 + l * ex
+            d = ex
+            dl = (-d * r0 + h * (r1 + r2)) / (d * d + h)
+            dx = -(d * dl + r0) / h
+            dt = dl - r1
+            x, t, l = x + dx, t + dt, l + dl
+        easy = np.exp(v) <= s
+    x[easy], t[easy] = v[easy], s[easy]
+    return x, t
+
 # ---------------------------------------------------------------------------
 # 1-D total variation (C restatement in oracle/tv1d_dp.c; pure Python for small n)
 # ---------------------------------------------------------------------------
@@ -579,6 +603,10 @@ class _VectorProx:
         """Epigraph operators: arguments [x (n) | t (1)], projection onto {f(x) <= t}."""
         t = self.f.type
         n = self.f.args[0].rows
+        if t == "EXP":                                   # elementwise: arguments [x (n) | t (n)]
+            assert len(self.f.args) == 2 and self.f.args[1].rows == n
+            xo, to = exp_epigraph(v[:n], v[n:])
+            return np.concatenate([xo, to])
         assert len(self.f.args) == 2 and self.f.args[1].rows == 1
         x, s = v[:n], float(v[n])
         if t == "SUM_SQUARE":

@@ -207,6 +207,9 @@ def prox_cases():
                                      gx=rng2.standard_normal(200)), 0.7,
                                  {"t": rng2.standard_normal(40), "x": rng2.standard_normal(200)})
     out["soc_single_cone"] = (soc(1, 500), 1.0, {"t": np.array([0.5]), "x": rng2.standard_normal(500)})
+    xe, te = Variable("x", 700), Variable("t", 700)
+    out["exp_epigraph"] = (ProxFunction("EXP", epigraph=True, args=[Affine(700, [Term(xe)]), Affine(700, [Term(te)])]),
+                           1.0, {"x": rng2.standard_normal(700) * 2, "t": rng2.standard_normal(700) * 2 + 1})
     return out
 
 

@@ -108,3 +108,26 @@ def test_sparse_sell_skewed_rows(ctx, monkeypatch):
     cols = np.concatenate([rng.choice(n, k, replace=False) for k in lens if k]) if lens.sum() else np.zeros(0, int)
     a = sp.csc_matrix((rng.standard_normal(rows.size), (rows, cols)), shape=(m, n))
     _check(ctx, LinearMapSpec.Sparse(a), rng)
+
+
+def test_buffers_may_outlive_their_context():
+    """A host language finalises objects in any order: maps and solvers destroyed after their
+    context must free their device memory without touching it (stream-ordered pool, ctx.cu)."""
+    from epsilon_b200 import problems
+    from epsilon_b200.solver import Context, ProxADMMSolver
+    c = Context(0)
+    rng = np.random.default_rng(3)
+    a = sp.random(4000, 3000, density=0.03, random_state=np.random.RandomState(4), format="csc")
+    lm = LinearMap(c, LinearMapSpec.Sparse(a))
+    assert np.isfinite(lm.apply(rng.standard_normal(3000))).all()
+    prob, _ = problems.lasso(200, 50, seed=1)
+    s = ProxADMMSolver(prob, {}, ctx=c)
+    s.solve()
+    c.close()
+    lm.close()
+    s.close()
+    c2 = Context(0)                       # the device is still usable
+    lm2 = LinearMap(c2, LinearMapSpec.Sparse(a))
+    assert np.isfinite(lm2.apply(rng.standard_normal(3000))).all()
+    lm2.close()
+    c2.close()

@@ -26,7 +26,7 @@ sys.path.insert(0, ROOT)
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("config", choices=["tv1d", "logreg", "hinge", "group_lasso", "lasso_dense", "lasso_sparse"])
+    ap.add_argument("config", choices=["tv1d", "logreg", "hinge", "group_lasso", "lasso_dense", "lasso_sparse", "mv_lasso"])
     ap.add_argument("--m", type=int, default=0)
     ap.add_argument("--n", type=int, default=0)
     ap.add_argument("--density", type=float, default=1.0)
@@ -52,6 +52,8 @@ def main():
         prob, info = problems.hinge_l2(a.m, a.n, a.density, seed=0)
     elif a.config == "group_lasso":
         prob, info = problems.group_lasso(a.m, a.group, a.K, seed=0)
+    elif a.config == "mv_lasso":
+        prob, info = problems.mv_lasso(a.m, a.n, a.K, a.density, seed=0)
     elif a.config == "lasso_dense":
         prob, info = problems.lasso(a.m, a.n, 1.0, seed=0)
     else:
