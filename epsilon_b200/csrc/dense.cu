@@ -33,7 +33,16 @@ template <bool AK, bool BK>
 __global__ void __launch_bounds__(kGemmThreads)
 GemmKernel(int M, int N, int K, double alpha, const double* __restrict__ A, int64_t lda,
            const double* __restrict__ B, int64_t ldb, const double* __restrict__ kscale,
-           double beta, double* __restrict__ C, int64_t ldc, int lower_only, int b_lower_tri) {
+           double beta, double* __restrict__ C, int64_t ldc, int lower_only, int b_lower_tri,
+           int kchunk = 0, int64_t cstride = 0) {
+  // split-K (kchunk > 0): CTA z contracts k in [z*kchunk, (z+1)*kchunk) into its own plane of C
+  const int Kfull = K;
+  int kz0 = 0;
+  if (kchunk > 0) {
+    kz0 = blockIdx.z * kchunk;
+    K = min(Kfull, kz0 + kchunk);
+    C += (int64_t)blockIdx.z * cstride;
+  }
   __shared__ double sA[BM][BKK + SPAD];
   __shared__ double sB[BN][BKK + SPAD];
   const int m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
@@ -83,7 +92,7 @@ GemmKernel(int M, int N, int K, double alpha, const double* __restrict__ A, int6
     }
   };
 
-  int kbeg = 0;
+  int kbeg = kz0;
   if (b_lower_tri) kbeg = (n0 / BKK) * BKK;
   if (kbeg < K) {
     load_tiles(kbeg);
@@ -258,12 +267,52 @@ void DenseGramNT(Ctx* ctx, const double* A, int64_t lda, int m, int64_t n, const
   ctx->count_launch();
 }
 
+__global__ void __launch_bounds__(256)
+GemmSplitReduceKernel(int64_t len, int rows, int splits, const double* __restrict__ part, int64_t stride,
+                      double alpha, double beta, double* __restrict__ Y, int64_t ldy) {
+  const int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x;
+  if (i >= len) return;
+  double s = 0.0;
+  for (int z = 0; z < splits; z++) s += part[(int64_t)z * stride + i];
+  double* y = Y + (i % rows) + (i / rows) * ldy;
+  *y = (beta == 0.0 ? 0.0 : beta * *y) + alpha * s;
+}
+
 void DenseGemmRhs(Ctx* ctx, const double* A, int64_t lda, int m, int n, bool trans, double alpha,
                   const double* X, int64_t ldx, int k, double beta, double* Y, int64_t ldy) {
   // C[i + j ldy] = sum_kk a(i, kk) x(j, kk): a(i,kk) = A[i + kk lda] (AK = false) or A[kk + i lda] (A', AK = true);
-  // x(j,kk) = X[kk + j ldx] (BK = true)
-  if (!trans) Gemm<false, true>(ctx, m, k, n, alpha, A, lda, X, ldx, nullptr, beta, Y, ldy, false, false);
-  else Gemm<true, true>(ctx, n, k, m, alpha, A, lda, X, ldx, nullptr, beta, Y, ldy, false, false);
+  // x(j,kk) = X[kk + j ldx] (BK = true).  With a few columns the output has only rows/64 tiles: the
+  // contraction is split over gridDim.z so that ~2 CTAs per SM stream the matrix, partial planes are
+  // added in a fixed order.
+  const int M = trans ? n : m, K = trans ? m : n;
+  if (M <= 0 || k <= 0) return;
+  const int tiles = ((M + BM - 1) / BM) * ((k + BN - 1) / BN);
+  int splits = std::max(1, std::min((2 * ctx->sm_count + tiles - 1) / tiles, (K + 4 * BKK - 1) / (4 * BKK)));
+  int kchunk = (K + splits - 1) / splits;
+  kchunk = (kchunk + BKK - 1) / BKK * BKK;
+  splits = (K + kchunk - 1) / kchunk;
+  if (splits <= 1) {
+    if (!trans) Gemm<false, true>(ctx, m, k, n, alpha, A, lda, X, ldx, nullptr, beta, Y, ldy, false, false);
+    else Gemm<true, true>(ctx, n, k, m, alpha, A, lda, X, ldx, nullptr, beta, Y, ldy, false, false);
+    return;
+  }
+  const int64_t plane = (int64_t)M * k;
+  double* part = GrowScratch(ctx, &ctx->split_scratch, (size_t)plane * splits);
+  dim3 grid((M + BM - 1) / BM, (k + BN - 1) / BN, splits);
+  {
+    ProfScope ps(ctx, KC_KKT_DENSE, 8.0 * m * n);
+    if (!trans)
+      GemmKernel<false, true><<<grid, kGemmThreads, 0, ctx->stream>>>(M, k, K, 1.0, A, lda, X, ldx, nullptr, 0.0, part, M,
+                                                                       0, 0, kchunk, plane);
+    else
+      GemmKernel<true, true><<<grid, kGemmThreads, 0, ctx->stream>>>(M, k, K, 1.0, A, lda, X, ldx, nullptr, 0.0, part, M,
+                                                                      0, 0, kchunk, plane);
+    ctx->count_launch();
+  }
+  ProfScope ps(ctx, KC_VEC, 8.0 * plane * splits);
+  GemmSplitReduceKernel<<<(unsigned)((plane + 255) / 256), 256, 0, ctx->stream>>>(plane, M, splits, part, plane, alpha,
+                                                                                 beta, Y, ldy);
+  ctx->count_launch();
 }
 
 void DenseAddDiagonal(Ctx* ctx, double* M, int64_t ld, int n, const double* d, double a) {
