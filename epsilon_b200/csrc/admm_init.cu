@@ -80,6 +80,7 @@ const char* TypeName(int t) {
     case EPS_PROX_EXP: return "EXP";
     case EPS_PROX_MAX: return "MAX";
     case EPS_PROX_SUM_LARGEST: return "SUM_LARGEST";
+    case EPS_PROX_LOG_SUM_EXP: return "LOG_SUM_EXP";
     case EPS_PROX_SECOND_ORDER_CONE: return "SECOND_ORDER_CONE";
     case EPS_PROX_SUM_KL_DIV: return "SUM_KL_DIV";
     case EPS_PROX_TOTAL_VARIATION_1D: return "TOTAL_VARIATION_1D";
@@ -338,14 +339,17 @@ void eps_solver::Init(const eps_problem& original) {
       if (f.type == EPS_PROX_EXP)
         EPS_CHECK(f.epigraph && f.args.size() == 2 && f.args[1].rows == f.args[0].rows,
                   "prox %d (EXP): elementwise epigraph form over (x, t) of equal size", i);
+      else if (f.type == EPS_PROX_SUM_KL_DIV)
+        EPS_CHECK(f.args.size() == (f.epigraph ? 3u : 2u) && f.args[0].rows == f.args[1].rows &&
+                      (!f.epigraph || f.args[2].rows == 1),
+                  "SUM_KL_DIV takes two equal-sized arguments (and t in the epigraph form)");
       else if (f.epigraph)
         EPS_CHECK(f.args.size() == 2 && f.args[1].rows == 1, "prox %d (%s): epigraph form takes (x, t)", i,
                   TypeName(f.type));
-      if (f.type == EPS_PROX_SUM_KL_DIV)
-        EPS_CHECK(f.args.size() == 2 && f.args[0].rows == f.args[1].rows, "SUM_KL_DIV takes two equal-sized arguments");
+      if (f.type == EPS_PROX_LOG_SUM_EXP && !f.epigraph) EPS_CHECK(f.args.size() == 1, "LOG_SUM_EXP takes one argument");
       if (f.type == EPS_PROX_MAX && !f.epigraph) EPS_CHECK(f.args.size() == 1, "MAX takes one argument");
       if (f.type == EPS_PROX_SUM_LARGEST) {
-        EPS_CHECK(f.args.size() == 1 && !f.epigraph, "SUM_LARGEST takes one argument (the epigraph form has no device operator)");
+        EPS_CHECK(f.args.size() == (f.epigraph ? 2u : 1u), "SUM_LARGEST takes one argument (and t in the epigraph form)");
         d.k = f.sum_largest_k;
       }
       op.g_off = -1;

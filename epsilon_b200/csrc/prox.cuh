@@ -77,7 +77,7 @@ struct VecOpDesc {
   double soc_a = 1;      // at / |ax|
 };
 struct VecOpWork {
-  DevBuf<double> keys, keys2, vals, vals2, scan1, scan2, scal, ev, ent;
+  DevBuf<double> keys, keys2, vals, vals2, scan1, scan2, scal, ev, ent, v0;
   DevBuf<int> idx;
   DevBuf<char> tmp;
 };

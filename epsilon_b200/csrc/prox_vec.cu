@@ -30,24 +30,29 @@ enum { SC_NORM2 = 0, SC_T = 1, SC_LAM = 2, SC_FVAL = 3, SC_SKIP = 4, SC_COUNT = 
 inline int Grid(int64_t n) { return (int)std::max<int64_t>(1, std::min<int64_t>((n + kBlock - 1) / kBlock, 148 * 8)); }
 
 // ---- SUM_KL_DIV: per-element Newton on yhat (sum_kl_div.cc:6-52) -------------------------
-__global__ void KlDivKernel(int64_t n, double lam, double* __restrict__ V) {
+__device__ __forceinline__ void KlProxElem(double lam, double u, double v, double* x, double* y) {
   const double eps = 1e-13;
+  if (fabs(u) < eps * eps && fabs(v) < eps * eps) { *x = u; *y = v; return; }
+  double yhat = fmax((0.5 + lam - v) / lam, eps);
+  for (int it = 0; it < 1000; it++) {
+    const double f = lam * yhat * yhat + (v - lam) * yhat - u + lam * log(yhat);
+    const double F = 2 * lam * yhat + (v - lam) + lam / yhat;
+    const double res = f / F;
+    if (fabs(res) < eps || (yhat <= eps * 2 && res > 0) || (lam * yhat + v - lam <= eps * 2 && res > 0)) break;
+    yhat = yhat - res;
+    if (yhat < eps) yhat = eps;
+    if (lam * yhat + v - lam < eps) yhat = (eps + lam - v) / lam;
+  }
+  *y = lam * yhat + v - lam;
+  *x = *y * yhat;
+}
+
+__global__ void KlDivKernel(int64_t n, double lam, double* __restrict__ V) {
   for (int64_t i = (int64_t)blockIdx.x * kBlock + threadIdx.x; i < n; i += (int64_t)gridDim.x * kBlock) {
-    const double u = V[i], v = V[n + i];
-    if (fabs(u) < eps * eps && fabs(v) < eps * eps) continue;  // x = u, y = v
-    double yhat = fmax((0.5 + lam - v) / lam, eps);
-    for (int it = 0; it < 1000; it++) {
-      const double f = lam * yhat * yhat + (v - lam) * yhat - u + lam * log(yhat);
-      const double F = 2 * lam * yhat + (v - lam) + lam / yhat;
-      const double res = f / F;
-      if (fabs(res) < eps || (yhat <= eps * 2 && res > 0) || (lam * yhat + v - lam <= eps * 2 && res > 0)) break;
-      yhat = yhat - res;
-      if (yhat < eps) yhat = eps;
-      if (lam * yhat + v - lam < eps) yhat = (eps + lam - v) / lam;
-    }
-    const double y = lam * yhat + v - lam;
+    double x, y;
+    KlProxElem(lam, V[i], V[n + i], &x, &y);
+    V[i] = x;
     V[n + i] = y;
-    V[i] = y * yhat;
   }
 }
 
@@ -317,13 +322,15 @@ struct EpiFn {
 };
 
 constexpr int kEpiBlock = 256;
+constexpr int kGridSumsMaxK = 4;
 
 // Grid-wide sums of K values per thread, identical in every thread of every CTA on return.
 template <int K>
 __device__ __forceinline__ void GridSums(double (&v)[K], double* partials, int& toggle, double* smem) {
   namespace cg = cooperative_groups;
+  static_assert(K <= kGridSumsMaxK, "partials hold kGridSumsMaxK planes per buffer");
   const int G = gridDim.x;
-  double* P = partials + (size_t)toggle * K * G;
+  double* P = partials + (size_t)toggle * kGridSumsMaxK * G;   // same two buffers whatever K (no overlap between calls)
   toggle ^= 1;
   BlockSum<K>(v, smem);
   if (threadIdx.x == 0) {
@@ -423,6 +430,284 @@ NewtonEpiKernel(int64_t n, double* __restrict__ V, const double* __restrict__ v0
   if (blockIdx.x == 0 && threadIdx.x == 0) V[n] = t;
 }
 
+// ---- implicit epigraph operators: scalar Newton on the multiplier lambda around the plain prox ---
+// Each is one cooperative kernel; lambda and the stopping decisions are recomputed identically by
+// every CTA from the grid-wide sums.
+
+// SumNegLogEpigraph (sum_neg_log.cc:41-88): g(lam) = -sum log x_i(lam) - lam - s with the closed-form prox.
+__global__ void __launch_bounds__(kEpiBlock)
+NegLogEpiKernel(int64_t n, double* __restrict__ V, double* __restrict__ partials) {
+  __shared__ double smem[3 * 32];
+  const int64_t first = (int64_t)blockIdx.x * kEpiBlock + threadIdx.x;
+  const int64_t stride = (int64_t)gridDim.x * kEpiBlock;
+  const double s = V[n];
+  int toggle = 0;
+  double lam = 1.0;
+  for (int iter = 0; iter < 1000; iter++) {
+    double a[2] = {0.0, 0.0};
+    for (int64_t i = first; i < n; i += stride) {
+      const double v = V[i], z = sqrt(v * v + 4 * lam);
+      if (v >= 0) {
+        a[0] -= log((v + z) / 2);
+        a[1] += 1.0 / (v * (v + z) / 2 + 2 * lam);
+      } else {
+        a[0] += log((-v + z) / (2 * lam));
+        a[1] += 1.0 / (v * 2 * lam / (-v + z) + 2 * lam);
+      }
+    }
+    GridSums<2>(a, partials, toggle, smem);
+    const double g = -lam - s + a[0];
+    double h = -1.0 - a[1];
+    if (fabs(g) <= 1e-10) break;
+    if (h >= -1e-10) h = -1e-10;
+    lam -= g / h;
+    if (lam <= 1e-10) lam = 1e-10;
+  }
+  for (int64_t i = first; i < n; i += stride) {
+    const double v = V[i], z = sqrt(v * v + 4 * lam);
+    V[i] = v >= 0 ? (v + z) / 2 : 2 * lam / (-v + z);   // ApplyNegLogProx, sum_neg_log.cc:10-26
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) V[n] = s + lam;
+}
+
+// SumKLDivEpigraph (sum_kl_div.cc:68-118): arguments [u (n) | v (n) | s]
+__global__ void __launch_bounds__(kEpiBlock)
+KlDivEpiKernel(int64_t n, double* __restrict__ V, double* __restrict__ partials) {
+  __shared__ double smem[3 * 32];
+  const int64_t first = (int64_t)blockIdx.x * kEpiBlock + threadIdx.x;
+  const int64_t stride = (int64_t)gridDim.x * kEpiBlock;
+  const double s = V[2 * n], eps = 1e-10;
+  int toggle = 0;
+  double lam = 1.0;
+  for (int iter = 0; iter < 100; iter++) {
+    double a[2] = {0.0, 0.0};
+    for (int64_t i = first; i < n; i += stride) {
+      double x, y;
+      KlProxElem(lam, V[i], V[n + i], &x, &y);
+      a[0] += x * log(x / y) - x + y;
+      const double g0 = log(x / y), g1 = -x / y + 1;
+      const double h00 = 1 + lam / x, h01 = -lam / y, h11 = 1 + lam * x / (y * y);
+      a[1] += (g0 * (h11 * g0 - h01 * g1) + g1 * (h00 * g1 - h01 * g0)) / (h00 * h11 - h01 * h01);
+    }
+    GridSums<2>(a, partials, toggle, smem);
+    const double glam = -s - lam + a[0], hlam = -1.0 - a[1];
+    if (fabs(glam) < eps || (lam <= eps * 2 && glam / hlam > 0)) break;
+    lam = lam - glam / hlam;
+    if (lam < eps) lam = eps;
+  }
+  for (int64_t i = first; i < n; i += stride) {
+    double x, y;
+    KlProxElem(lam, V[i], V[n + i], &x, &y);
+    V[i] = x;
+    V[n + i] = y;
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) V[2 * n] = s + lam;
+}
+
+// ImplicitNewtonEpigraph (newton.cc:192-238) over an elementwise function, with ApplyNewtonProx
+// (newton.cc:47-91, global backtracking on the residual norm) as the inner solve.
+struct NegEntrFn {
+  static __device__ __forceinline__ double f(double x) { return x <= 0 ? 0.0 : x * log(x); }  // sum_neg_entr.cc:12-21
+  static __device__ __forceinline__ double grad(double x) { return 1 + log(x); }
+  static __device__ __forceinline__ double hess(double x) { return 1 / x; }
+  static __device__ __forceinline__ double proj(double x) { return fmax(x, 1e-6); }
+};
+
+template <class F>
+__device__ void NewtonProxGrid(int64_t n, double lam, double eps, double* __restrict__ X,
+                               const double* __restrict__ v0, double* __restrict__ xn, double* partials,
+                               int& toggle, double* smem) {
+  const int64_t first = (int64_t)blockIdx.x * kEpiBlock + threadIdx.x;
+  const int64_t stride = (int64_t)gridDim.x * kEpiBlock;
+  for (int64_t i = first; i < n; i += stride) X[i] = F::proj(v0[i]);
+  for (int iter = 0; iter < 100; iter++) {
+    double a[1] = {0.0};
+    for (int64_t i = first; i < n; i += stride) {
+      const double xi = X[i], g = xi - v0[i] + lam * F::grad(xi);
+      a[0] += g * g;
+    }
+    GridSums<1>(a, partials, toggle, smem);
+    double x_res = sqrt(a[0]), theta = 1.0;
+    while (theta > eps) {
+      double b[1] = {0.0};
+      for (int64_t i = first; i < n; i += stride) {
+        const double xi = X[i], g = xi - v0[i] + lam * F::grad(xi);
+        const double nx = F::proj(xi - theta * (g / (1.0 + lam * F::hess(xi))));
+        xn[i] = nx;
+        const double r = nx - v0[i] + lam * F::grad(nx);
+        b[0] += r * r;
+      }
+      GridSums<1>(b, partials, toggle, smem);
+      const double nx_res = sqrt(b[0]);
+      if (nx_res <= (1 - 0.001 * theta) * x_res) {
+        for (int64_t i = first; i < n; i += stride) X[i] = xn[i];
+        x_res = nx_res;
+        break;
+      }
+      theta *= 0.5;
+    }
+    if (x_res < eps) break;
+  }
+}
+
+template <class F>
+__global__ void __launch_bounds__(kEpiBlock)
+ImplicitNewtonEpiKernel(int64_t n, double* __restrict__ V, const double* __restrict__ v0, double* __restrict__ xn,
+                        double* __restrict__ partials) {
+  __shared__ double smem[3 * 32];
+  const int64_t first = (int64_t)blockIdx.x * kEpiBlock + threadIdx.x;
+  const int64_t stride = (int64_t)gridDim.x * kEpiBlock;
+  const double s = V[n];
+  const double eps = fmax(1e-12, 1e-10 / (double)n);
+  int toggle = 0;
+  {
+    double a[1] = {0.0};
+    for (int64_t i = first; i < n; i += stride) {
+      const double xi = F::proj(v0[i]);
+      V[i] = xi;
+      a[0] += F::f(xi);
+    }
+    GridSums<1>(a, partials, toggle, smem);
+    if (a[0] <= s) return;   // x = proj_feasible(v), t = s
+  }
+  double lam = 1.0;
+  for (int iter = 0; iter < 100; iter++) {
+    NewtonProxGrid<F>(n, lam, eps, V, v0, xn, partials, toggle, smem);
+    double a[2] = {0.0, 0.0};
+    for (int64_t i = first; i < n; i += stride) {
+      const double xi = V[i], gx = F::grad(xi);
+      a[0] += F::f(xi);
+      a[1] += gx / (1.0 + lam * F::hess(xi)) * gx;
+    }
+    GridSums<2>(a, partials, toggle, smem);
+    const double glam = a[0] - lam - s, hlam = -a[1] - 1;
+    if (fabs(glam) < 1e-10) break;
+    lam = lam - glam / hlam;
+    if (lam < 0) lam = 1e-6;
+  }
+  NewtonProxGrid<F>(n, lam, eps, V, v0, xn, partials, toggle, smem);
+  if (blockIdx.x == 0 && threadIdx.x == 0) V[n] = s + lam;
+}
+
+// ---- LOG_SUM_EXP (log_sum_exp.cc): NewtonProx / NewtonEpigraph with a full Hessian ---------------
+// f = log sum exp(x_i), grad = w = softmax(x), (I + lam (diag(w) - w w'))^{-1} g by Sherman-Morrison
+// (log_sum_exp.cc:41-64).  Every evaluation point needs max(x) and sum exp(x - max) over the grid.
+__device__ __forceinline__ double GridMax(double v, double* partials, int& toggle, double* smem) {
+  namespace cg = cooperative_groups;
+  const int G = gridDim.x;
+  double* P = partials + (size_t)toggle * kGridSumsMaxK * G;
+  toggle ^= 1;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xFFFFFFFFu, v, o));
+  __syncthreads();
+  if (lane == 0) smem[warp] = v;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double m = smem[0];
+    for (int w = 1; w < kEpiBlock / 32; w++) m = fmax(m, smem[w]);
+    P[blockIdx.x] = m;
+  }
+  cg::this_grid().sync();
+  double m = -INFINITY;
+  for (int i = lane; i < G; i += 32) m = fmax(m, __ldcg(&P[i]));
+  for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_xor_sync(0xFFFFFFFFu, m, o));
+  return m;
+}
+
+// max and sum exp(x - max) of X[0..n)
+__device__ __forceinline__ void LseStats(int64_t n, const double* __restrict__ X, double* mx, double* z,
+                                         double* partials, int& toggle, double* smem) {
+  const int64_t first = (int64_t)blockIdx.x * kEpiBlock + threadIdx.x;
+  const int64_t stride = (int64_t)gridDim.x * kEpiBlock;
+  double m = -INFINITY;
+  for (int64_t i = first; i < n; i += stride) m = fmax(m, X[i]);
+  m = GridMax(m, partials, toggle, smem);
+  double a[1] = {0.0};
+  for (int64_t i = first; i < n; i += stride) a[0] += exp(X[i] - m);
+  GridSums<1>(a, partials, toggle, smem);
+  *mx = m;
+  *z = a[0];
+}
+
+template <bool EPI>
+__global__ void __launch_bounds__(kEpiBlock)
+LogSumExpKernel(int64_t n, double lam_prox, double* __restrict__ V, const double* __restrict__ v0,
+                double* __restrict__ xn, double* __restrict__ dx, double* __restrict__ partials) {
+  __shared__ double smem[4 * 32];
+  const int64_t first = (int64_t)blockIdx.x * kEpiBlock + threadIdx.x;
+  const int64_t stride = (int64_t)gridDim.x * kEpiBlock;
+  const double s = EPI ? V[n] : 0.0;
+  const double eps = fmax(1e-12, 1e-10 / (double)n);
+  int toggle = 0;
+  double mx, z;
+  LseStats(n, V, &mx, &z, partials, toggle, smem);   // x = v
+  if (EPI && mx + log(z) <= s) return;               // easy case: already inside
+  double t = s, lam = EPI ? 1.0 : lam_prox;
+  for (int iter = 0; iter < 100; iter++) {
+    // residual g = x - v + lam w and the sums of hess_inv; (mx, z) describe the current x
+    double a[4] = {0.0, 0.0, 0.0, 0.0};
+    for (int64_t i = first; i < n; i += stride) {
+      const double xi = V[i], w = exp(xi - mx) / z, g = xi - v0[i] + lam * w, d = 1 + lam * w;
+      a[0] += g * g;
+      a[1] += w * w / d;
+      a[2] += g * w / d;
+      a[3] += g * g / d;
+    }
+    GridSums<4>(a, partials, toggle, smem);
+    const double sc = lam * a[2] / (1 - lam * a[1]);
+    double mul = 1.0, step_t = 0.0, step_l = 0.0, x_res = sqrt(a[0]);
+    if (EPI) {
+      const double gn = t - s - lam, gn1 = mx + log(z) - t;
+      const double nt_res = a[3] + sc * a[2];
+      const double scale = (-nt_res + gn + gn1) / (nt_res + 1);
+      mul = 1 + scale; step_t = gn - scale; step_l = -scale;
+      x_res = sqrt(a[0] + gn * gn + gn1 * gn1);
+    }
+    for (int64_t i = first; i < n; i += stride) {
+      const double xi = V[i], w = exp(xi - mx) / z, g = xi - v0[i] + lam * w, d = 1 + lam * w;
+      dx[i] = mul * (g / d + w / d * sc);
+    }
+    double theta = 1.0;
+    while (theta > eps) {
+      const double nt = t - theta * step_t;
+      double nlam = lam - theta * step_l;
+      if (EPI && nlam < eps) nlam = eps;
+      for (int64_t i = first; i < n; i += stride) xn[i] = V[i] - theta * dx[i];
+      double nmx, nz;
+      LseStats(n, xn, &nmx, &nz, partials, toggle, smem);
+      double b[1] = {0.0};
+      for (int64_t i = first; i < n; i += stride) {
+        const double r = xn[i] - v0[i] + nlam * (exp(xn[i] - nmx) / nz);
+        b[0] += r * r;
+      }
+      GridSums<1>(b, partials, toggle, smem);
+      double nx_res = sqrt(b[0]);
+      if (EPI) {
+        const double r1 = nt - s - nlam, r2 = nmx + log(nz) - nt;
+        nx_res = sqrt(b[0] + r1 * r1 + r2 * r2);
+      }
+      if (nx_res <= (1 - 0.001 * theta) * x_res) {
+        for (int64_t i = first; i < n; i += stride) V[i] = xn[i];
+        t = nt; lam = nlam; x_res = nx_res; mx = nmx; z = nz;
+        break;
+      }
+      theta *= 0.5;
+    }
+    if (x_res < eps) break;
+  }
+  if (EPI && blockIdx.x == 0 && threadIdx.x == 0) V[n] = t;
+}
+
+// ---- BisectionEpigraph around SumLargestProx (newton.cc:240-286, sum_largest.cc:60-85) ---------
+// sum of the k largest: Y sorted descending
+__global__ void TopKSumKernel(int k, const double* __restrict__ Y, double* __restrict__ out) {
+  double t = 0.0;
+  for (int i = 0; i < k; i++) t += Y[i];
+  *out = t;
+}
+
+__global__ void SetScalarKernel(double* __restrict__ p, double v) { *p = v; }
+
 }  // namespace
 
 bool IsVecOpType(int type, bool epigraph) {
@@ -430,9 +715,10 @@ bool IsVecOpType(int type, bool epigraph) {
     return type == EPS_PROX_SUM_SQUARE || type == EPS_PROX_MAX || type == EPS_PROX_NORM_1 ||
            type == EPS_PROX_SUM_HINGE || type == EPS_PROX_SUM_DEADZONE || type == EPS_PROX_SUM_QUANTILE ||
            type == EPS_PROX_SUM_EXP || type == EPS_PROX_SUM_LOGISTIC || type == EPS_PROX_SUM_INV_POS ||
-           type == EPS_PROX_EXP;
+           type == EPS_PROX_EXP || type == EPS_PROX_SUM_NEG_LOG || type == EPS_PROX_SUM_NEG_ENTR ||
+           type == EPS_PROX_SUM_KL_DIV || type == EPS_PROX_LOG_SUM_EXP || type == EPS_PROX_SUM_LARGEST;
   return type == EPS_PROX_MAX || type == EPS_PROX_SUM_KL_DIV || type == EPS_PROX_SUM_LARGEST ||
-         type == EPS_PROX_SECOND_ORDER_CONE;
+         type == EPS_PROX_SECOND_ORDER_CONE || type == EPS_PROX_LOG_SUM_EXP;
 }
 
 static bool IsNewtonEpi(const VecOpDesc& d) {
@@ -440,12 +726,83 @@ static bool IsNewtonEpi(const VecOpDesc& d) {
          (d.type == EPS_PROX_SUM_EXP || d.type == EPS_PROX_SUM_LOGISTIC || d.type == EPS_PROX_SUM_INV_POS);
 }
 
+// one cooperative kernel iterating on grid-wide sums (work: copy of v, trial point, step)
+static bool IsGridNewton(const VecOpDesc& d) {
+  return IsNewtonEpi(d) || d.type == EPS_PROX_LOG_SUM_EXP ||
+         (d.epigraph && (d.type == EPS_PROX_SUM_NEG_LOG || d.type == EPS_PROX_SUM_NEG_ENTR || d.type == EPS_PROX_SUM_KL_DIV));
+}
+
 static bool NeedsSort(const VecOpDesc& d) {
-  return d.type == EPS_PROX_MAX || d.type == EPS_PROX_SUM_LARGEST || (d.epigraph && d.type != EPS_PROX_SUM_SQUARE && !IsNewtonEpi(d));
+  return d.type == EPS_PROX_MAX || d.type == EPS_PROX_SUM_LARGEST ||
+         (d.epigraph && d.type != EPS_PROX_SUM_SQUARE && d.type != EPS_PROX_EXP && !IsGridNewton(d));
 }
 
 static int NewtonEpiGrid(Ctx* ctx, int64_t n) {
   return (int)std::max<int64_t>(1, std::min<int64_t>(ctx->sm_count, (n + kEpiBlock - 1) / kEpiBlock));
+}
+
+static void SumLargestProxRun(Ctx* ctx, const VecOpDesc& d, double lam, double* V, VecOpWork* w) {
+    const int64_t n = d.n0;
+    const int ni = (int)n;
+    cudaStream_t st = ctx->stream;
+    size_t bytes = w->tmp.n;
+    const double klam = (double)d.k * lam;
+    const int n2 = 2 * ni;
+    CUDA_CHECK(cub::DeviceRadixSort::SortKeysDescending(w->tmp.p, bytes, V, w->keys2.p, ni, 0, 64, st));
+    LargestEventsKernel<<<Grid(n), kBlock, 0, st>>>(n, lam, w->keys2.p, w->keys.p, w->vals.p);
+    bytes = w->tmp.n;
+    CUDA_CHECK(cub::DeviceRadixSort::SortPairsDescending(w->tmp.p, bytes, w->keys.p, w->ev.p, w->vals.p, w->vals2.p,
+                                                         n2, 0, 64, st));
+    // keys <- signed contributions, vals <- enter indicator (the unsorted inputs are dead)
+    LargestContribKernel<<<Grid(2 * n), kBlock, 0, st>>>(2 * n, w->ev.p, w->vals2.p, w->keys.p, w->vals.p);
+    bytes = w->tmp.n;
+    CUDA_CHECK(cub::DeviceScan::InclusiveSum(w->tmp.p, bytes, w->keys.p, w->scan1.p, n2, st));   // ACC
+    bytes = w->tmp.n;
+    CUDA_CHECK(cub::DeviceScan::InclusiveSum(w->tmp.p, bytes, w->vals2.p, w->scan2.p, n2, st));  // INS
+    bytes = w->tmp.n;
+    CUDA_CHECK(cub::DeviceScan::InclusiveSum(w->tmp.p, bytes, w->vals.p, w->ent.p, n2, st));     // ENT
+    LargestBreakKernel<<<Grid(2 * n), kBlock, 0, st>>>(n, lam, klam, w->keys2.p, w->scan1.p, w->scan2.p, w->ent.p,
+                                                       w->idx.p);
+    LargestApplyKernel<<<Grid(n), kBlock, 0, st>>>(n, lam, klam, V, w->scan1.p, w->scan2.p, w->idx.p);
+    ctx->count_launch(10);
+}
+
+// BisectionEpigraph::ApplyVector (newton.cc:240-286): the doubling / halving decisions depend on the
+// sign of g = f(prox_lam(v)) - lam - s, one scalar read back per round (the only host-synchronous
+// operator; lam runs over dyadic rationals, so the rounds are those of the reference).
+static void SumLargestEpigraphRun(Ctx* ctx, const VecOpDesc& d, double* V, VecOpWork* w) {
+  const int64_t n = d.n0;
+  const int ni = (int)n;
+  cudaStream_t st = ctx->stream;
+  EPS_CHECK(d.k >= 0 && d.k <= n, "SUM_LARGEST: k = %d of %lld", d.k, (long long)n);
+  auto eval = [&](const double* X) {   // SumLargestProx::Eval, sum_largest.cc:60-73
+    size_t bytes = w->tmp.n;
+    CUDA_CHECK(cub::DeviceRadixSort::SortKeysDescending(w->tmp.p, bytes, X, w->keys2.p, ni, 0, 64, st));
+    TopKSumKernel<<<1, 1, 0, st>>>(d.k, w->keys2.p, w->scal.p + SC_FVAL);
+    ctx->count_launch(2);
+    double f = 0.0;
+    CUDA_CHECK(cudaMemcpyAsync(&f, w->scal.p + SC_FVAL, sizeof(double), cudaMemcpyDeviceToHost, st));
+    CUDA_CHECK(cudaStreamSynchronize(st));
+    return f;
+  };
+  double s = 0.0;
+  CUDA_CHECK(cudaMemcpyAsync(&s, V + n, sizeof(double), cudaMemcpyDeviceToHost, st));
+  if (eval(V) <= s) return;   // x = v, t = s
+  VecCopy(ctx, n, V, w->v0.p);
+  double lam = 1.0, upper = 1.0, lower = 0.0, t = NAN;
+  bool upper_fixed = false;
+  for (int iter = 0; iter < 100; iter++) {
+    if (iter > 0) VecCopy(ctx, n, w->v0.p, V);
+    PrepKernel<<<1, 1, 0, st>>>(n, 0, V, w->scal.p, w->idx.p);
+    SumLargestProxRun(ctx, d, lam, V, w);
+    const double g = eval(V) - (lam + s);
+    if (fabs(g) <= 1e-5) { t = lam + s; break; }
+    if (g > 0 && !upper_fixed) { lam *= 2; upper = lam; }
+    else if (g > 0) { lower = lam; lam = (lam + upper) / 2; }
+    else { upper = lam; lam = (lam + lower) / 2; upper_fixed = true; }
+  }
+  SetScalarKernel<<<1, 1, 0, st>>>(V + n, t);   // left unset by the reference after 100 rounds: NaN here
+  ctx->count_launch();
 }
 
 void VecOpInit(Ctx* ctx, const VecOpDesc& d, VecOpWork* w) {
@@ -453,10 +810,11 @@ void VecOpInit(Ctx* ctx, const VecOpDesc& d, VecOpWork* w) {
   w->scal.alloc(ctx, SC_COUNT);
   w->scal.zero();
   w->idx.alloc(ctx, 4);
-  if (IsNewtonEpi(d)) {
+  if (IsGridNewton(d)) {
     w->keys.alloc(ctx, d.n0);    // copy of v
     w->keys2.alloc(ctx, d.n0);   // trial point of the line search
-    w->scan1.alloc(ctx, (size_t)2 * 3 * NewtonEpiGrid(ctx, d.n0));
+    if (d.type == EPS_PROX_LOG_SUM_EXP) w->vals.alloc(ctx, d.n0);   // Newton step
+    w->scan1.alloc(ctx, (size_t)2 * kGridSumsMaxK * NewtonEpiGrid(ctx, d.n0));
     return;
   }
   if (!NeedsSort(d)) return;
@@ -468,6 +826,7 @@ void VecOpInit(Ctx* ctx, const VecOpDesc& d, VecOpWork* w) {
     w->keys.alloc(ctx, 2 * (size_t)n); w->vals.alloc(ctx, 2 * (size_t)n);
     w->vals2.alloc(ctx, 2 * (size_t)n); w->scan1.alloc(ctx, 2 * (size_t)n); w->scan2.alloc(ctx, 2 * (size_t)n);
     w->ev.alloc(ctx, 2 * (size_t)n); w->ent.alloc(ctx, 2 * (size_t)n);
+    if (d.epigraph) w->v0.alloc(ctx, n);
     CUDA_CHECK(cub::DeviceRadixSort::SortPairsDescending(nullptr, bytes, w->keys.p, w->ev.p, w->vals.p, w->vals2.p,
                                                          2 * n, 0, 64, ctx->stream));
     CUDA_CHECK(cub::DeviceScan::InclusiveSum(nullptr, b2, w->keys.p, w->scan1.p, 2 * n, ctx->stream));
@@ -516,6 +875,32 @@ void VecOpApply(Ctx* ctx, const VecOpDesc& d, double* V, VecOpWork* w) {
     ctx->count_launch(2);
     return;
   }
+  if (IsGridNewton(d) && !IsNewtonEpi(d)) {
+    int64_t nn = n;
+    double* Vp = V;
+    const double* v0 = w->keys.p;
+    double *xn = w->keys2.p, *dx = w->vals.p, *part = w->scan1.p;
+    double lam = d.lam;
+    const dim3 grid(NewtonEpiGrid(ctx, n)), block(kEpiBlock);
+    if (d.type == EPS_PROX_SUM_NEG_LOG) {
+      void* args[] = {&nn, &Vp, &part};
+      CUDA_CHECK(cudaLaunchCooperativeKernel((const void*)NegLogEpiKernel, grid, block, args, 0, st));
+    } else if (d.type == EPS_PROX_SUM_KL_DIV) {
+      void* args[] = {&nn, &Vp, &part};
+      CUDA_CHECK(cudaLaunchCooperativeKernel((const void*)KlDivEpiKernel, grid, block, args, 0, st));
+    } else if (d.type == EPS_PROX_SUM_NEG_ENTR) {
+      VecCopy(ctx, n, V, w->keys.p);
+      void* args[] = {&nn, &Vp, &v0, &xn, &part};
+      CUDA_CHECK(cudaLaunchCooperativeKernel((const void*)ImplicitNewtonEpiKernel<NegEntrFn>, grid, block, args, 0, st));
+    } else {
+      VecCopy(ctx, n, V, w->keys.p);
+      void* args[] = {&nn, &lam, &Vp, &v0, &xn, &dx, &part};
+      const void* fn = d.epigraph ? (const void*)LogSumExpKernel<true> : (const void*)LogSumExpKernel<false>;
+      CUDA_CHECK(cudaLaunchCooperativeKernel(fn, grid, block, args, 0, st));
+    }
+    ctx->count_launch();
+    return;
+  }
   if (IsNewtonEpi(d)) {
     VecCopy(ctx, n, V, w->keys.p);
     int64_t nn = n;
@@ -533,26 +918,12 @@ void VecOpApply(Ctx* ctx, const VecOpDesc& d, double* V, VecOpWork* w) {
   size_t bytes = w->tmp.n;
   const int ni = (int)n;
   PrepKernel<<<1, 1, 0, st>>>(n, d.epigraph ? 1 : 0, V, w->scal.p, w->idx.p);
+  if (d.type == EPS_PROX_SUM_LARGEST && !d.epigraph) {
+    SumLargestProxRun(ctx, d, d.lam, V, w);
+    return;
+  }
   if (d.type == EPS_PROX_SUM_LARGEST) {
-    const double klam = (double)d.k * d.lam;
-    const int n2 = 2 * ni;
-    CUDA_CHECK(cub::DeviceRadixSort::SortKeysDescending(w->tmp.p, bytes, V, w->keys2.p, ni, 0, 64, st));
-    LargestEventsKernel<<<Grid(n), kBlock, 0, st>>>(n, d.lam, w->keys2.p, w->keys.p, w->vals.p);
-    bytes = w->tmp.n;
-    CUDA_CHECK(cub::DeviceRadixSort::SortPairsDescending(w->tmp.p, bytes, w->keys.p, w->ev.p, w->vals.p, w->vals2.p,
-                                                         n2, 0, 64, st));
-    // keys <- signed contributions, vals <- enter indicator (the unsorted inputs are dead)
-    LargestContribKernel<<<Grid(2 * n), kBlock, 0, st>>>(2 * n, w->ev.p, w->vals2.p, w->keys.p, w->vals.p);
-    bytes = w->tmp.n;
-    CUDA_CHECK(cub::DeviceScan::InclusiveSum(w->tmp.p, bytes, w->keys.p, w->scan1.p, n2, st));   // ACC
-    bytes = w->tmp.n;
-    CUDA_CHECK(cub::DeviceScan::InclusiveSum(w->tmp.p, bytes, w->vals2.p, w->scan2.p, n2, st));  // INS
-    bytes = w->tmp.n;
-    CUDA_CHECK(cub::DeviceScan::InclusiveSum(w->tmp.p, bytes, w->vals.p, w->ent.p, n2, st));     // ENT
-    LargestBreakKernel<<<Grid(2 * n), kBlock, 0, st>>>(n, d.lam, klam, w->keys2.p, w->scan1.p, w->scan2.p, w->ent.p,
-                                                       w->idx.p);
-    LargestApplyKernel<<<Grid(n), kBlock, 0, st>>>(n, d.lam, klam, V, w->scan1.p, w->scan2.p, w->idx.p);
-    ctx->count_launch(10);
+    SumLargestEpigraphRun(ctx, d, V, w);
     return;
   }
   if (d.type == EPS_PROX_MAX) {

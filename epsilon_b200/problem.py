@@ -39,6 +39,7 @@ PROX_TYPES = {
     "SUM_NEG_LOG": 29,
     "SUM_QUANTILE": 31,
     "EXP": 32,
+    "LOG_SUM_EXP": 100,
     "MAX": 101,
     "NORM_2": 102,
     "SECOND_ORDER_CONE": 104,

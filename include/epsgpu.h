@@ -54,6 +54,7 @@ enum eps_prox_type {
   EPS_PROX_SUM_NEG_LOG = 29,
   EPS_PROX_SUM_QUANTILE = 31,
   EPS_PROX_EXP = 32,
+  EPS_PROX_LOG_SUM_EXP = 100,
   EPS_PROX_MAX = 101,
   EPS_PROX_NORM_2 = 102,
   EPS_PROX_SECOND_ORDER_CONE = 104,

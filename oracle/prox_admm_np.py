@@ -308,7 +308,7 @@ SMOOTH_EVAL = {
 }
 
 
-def newton_epigraph(v: np.ndarray, s: float, evalf, gradf, hessf, proj=lambda x: x):
+def newton_epigraph(v: np.ndarray, s: float, evalf, gradf, hessf, proj=lambda x: x, hinv=None):
     """NewtonEpigraph::ApplyVector, newton.cc:108-185: Newton on (x, t, lam) with the arrowhead
     structure of the KKT system and a backtracking line search on the residual norm."""
     n = v.size
@@ -328,7 +328,7 @@ def newton_epigraph(v: np.ndarray, s: float, evalf, gradf, hessf, proj=lambda x:
         t, lam = s, 1.0
         for _ in range(100):
             g = residual(lam, x, t)
-            nt_step = g[:n] / (1.0 + lam * hessf(x))
+            nt_step = hinv(lam, x, g[:n]) if hinv else g[:n] / (1.0 + lam * hessf(x))
             nt_res = float(g[:n] @ nt_step)
             scale = (-nt_res + g[n] + g[n + 1]) / (nt_res + 1)
             step_x = (1 + scale) * nt_step
@@ -373,6 +373,158 @@ def exp_epigraph(v: np.ndarray, s: np.ndarray):
         easy = np.exp(v) <= s
     x[easy], t[easy] = v[easy], s[easy]
     return x, t
+
+
+def neg_log_epigraph(v: np.ndarray, s: float):
+    """SumNegLogEpigraph::ApplyVector, sum_neg_log.cc:41-88: scalar Newton on the multiplier lambda of
+    -sum log x_i(lambda) - lambda - s = 0 with x(lambda) the closed-form prox; no easy case."""
+    lam = 1.0
+    with np.errstate(all="ignore"):
+        for _ in range(1000):
+            z = np.sqrt(v * v + 4 * lam)
+            pos = v >= 0
+            gi = np.where(pos, -np.log((v + z) / 2), np.log((-v + z) / (2 * lam)))
+            hi = np.where(pos, 1.0 / (v * (v + z) / 2 + 2 * lam), 1.0 / (v * 2 * lam / (-v + z) + 2 * lam))
+            g, h = -lam - s, -1.0
+            for i in range(v.size):                      # the reference accumulates element by element
+                g += gi[i]; h -= hi[i]
+            if abs(g) <= 1e-10:
+                break
+            if h >= -1e-10:
+                h = -1e-10
+            lam -= g / h
+            if lam <= 1e-10:
+                lam = 1e-10
+    return neg_log_prox(v, np.full(v.size, lam)), s + lam
+
+
+def implicit_newton_epigraph(v: np.ndarray, s: float, evalf, gradf, hessf, proj=lambda x: x):
+    """ImplicitNewtonEpigraph::ApplyVector, newton.cc:192-238: Newton on lambda of f(prox_{lambda f}(v)) - lambda - s."""
+    x = proj(v.copy())
+    with np.errstate(all="ignore"):
+        if evalf(x) <= s:
+            return x, s
+        lam = 1.0
+        for _ in range(100):
+            x = newton_prox(v, np.full(v.size, lam), gradf, hessf, proj)
+            gx = gradf(x)
+            glam = evalf(x) - lam - s
+            hlam = -float((gx / (1.0 + lam * hessf(x))) @ gx) - 1
+            if abs(glam) < 1e-10:
+                break
+            lam = lam - glam / hlam
+            if lam < 0:
+                lam = 1e-6
+        return newton_prox(v, np.full(v.size, lam), gradf, hessf, proj), s + lam
+
+
+def _neg_entr_eval(x):                                   # sum_neg_entr.cc:12-21 (skips x_i <= 0)
+    with np.errstate(all="ignore"):
+        return float(np.sum(np.where(x > 0, x * np.log(np.where(x > 0, x, 1.0)), 0.0)))
+
+
+def kl_div_epigraph(u: np.ndarray, v: np.ndarray, s: float):
+    """SumKLDivEpigraph::ApplyVector, sum_kl_div.cc:68-118."""
+    eps, n, lam = 1e-10, u.size, 1.0
+    with np.errstate(all="ignore"):
+        for _ in range(100):
+            x, y = kl_div_prox(np.full(n, lam), u, v)
+            glam, hlam = -s - lam, -1.0
+            for i in range(n):
+                glam += x[i] * np.log(x[i] / y[i]) - x[i] + y[i]
+                g0, g1 = np.log(x[i] / y[i]), -x[i] / y[i] + 1
+                h00 = 1 + lam / x[i]; h01 = -lam / y[i]; h11 = 1 + lam * x[i] / (y[i] * y[i])
+                det = h00 * h11 - h01 * h01
+                hlam -= (g0 * (h11 * g0 - h01 * g1) + g1 * (h00 * g1 - h01 * g0)) / det
+            if abs(glam) < eps or (lam <= eps * 2 and glam / hlam > 0):
+                break
+            lam = lam - glam / hlam
+            if lam < eps:
+                lam = eps
+        x, y = kl_div_prox(np.full(n, lam), u, v)
+    return x, y, s + lam
+
+
+def _lse_eval(x):                                        # log_sum_exp.cc:22-30
+    m = x.max()
+    return float(m + np.log(np.exp(x - m).sum()))
+
+
+def _lse_grad(x):                                        # log_sum_exp.cc:31-40
+    w = np.exp(x - x.max())
+    return w / w.sum()
+
+
+def _lse_hess_inv(lam: float, x: np.ndarray, v: np.ndarray) -> np.ndarray:
+    """LogSumExp::hess_inv, log_sum_exp.cc:41-64: (I + lam (diag(w) - w w'))^{-1} v; lam = lambda_(0)."""
+    w = _lse_grad(x)
+    t = r = 0.0
+    for i in range(x.size):
+        t += w[i] * w[i] / (1 + lam * w[i])
+        r += v[i] * w[i] / (1 + lam * w[i])
+    sc = lam * r / (1 - lam * t)
+    return v / (1 + lam * w) + w / (1 + lam * w) * sc
+
+
+def log_sum_exp_prox(v: np.ndarray, lam: float) -> np.ndarray:
+    """ApplyNewtonProx (newton.cc:47-91) with the LogSumExp function (full Hessian through hess_inv)."""
+    n = v.size
+    eps = max(1e-12, 1e-10 / n)
+    x = v.copy()
+    for _ in range(100):
+        gx = x - v + lam * _lse_grad(x)
+        dx = _lse_hess_inv(lam, x, gx)
+        theta, x_res = 1.0, float(np.linalg.norm(gx))
+        while theta > eps:
+            nx = x - theta * dx
+            nx_res = float(np.linalg.norm(nx - v + lam * _lse_grad(nx)))
+            if nx_res <= (1 - 0.001 * theta) * x_res:
+                x, x_res = nx, nx_res
+                break
+            theta *= 0.5
+        if x_res < eps:
+            break
+    return x
+
+
+def log_sum_exp_epigraph(v: np.ndarray, s: float):
+    """NewtonEpigraph::ApplyVector (newton.cc:108-185) with LogSumExp: the x block of the arrowhead
+    step goes through LogSumExp::hess_inv."""
+    return newton_epigraph(v, s, _lse_eval, _lse_grad, None, hinv=_lse_hess_inv)
+
+
+def bisection_epigraph(v: np.ndarray, s: float, prox, evalf):
+    """BisectionEpigraph::ApplyVector, newton.cc:240-286: doubling then bisection on lambda of
+    f(prox_{lambda f}(v)) - lambda - s to |g| <= 1e-5.  (After 100 rounds without reaching it the
+    reference leaves t unset; reported here as nan.)"""
+    if evalf(v) <= s:
+        return v.copy(), s
+    lam, upper, lower, upper_fixed = 1.0, 1.0, 0.0, False
+    x = v
+    for _ in range(100):
+        x = prox(v, lam)
+        g = evalf(x) - (lam + s)
+        if abs(g) <= 1e-5:
+            return x, lam + s
+        if g > 0 and not upper_fixed:
+            lam *= 2
+            upper = lam
+        elif g > 0:
+            lower = lam
+            lam = (lam + upper) / 2
+        else:
+            upper = lam
+            lam = (lam + lower) / 2
+            upper_fixed = True
+    return x, float("nan")
+
+
+def _sum_largest_eval(x: np.ndarray, k: int) -> float:   # SumLargestProx::Eval, sum_largest.cc:60-73
+    y = np.sort(x)[::-1]
+    tot = 0.0
+    for i in range(k):
+        tot += y[i]
+    return tot
 
 # ---------------------------------------------------------------------------
 # 1-D total variation (C restatement in oracle/tv1d_dp.c; pure Python for small n)
@@ -607,9 +759,23 @@ class _VectorProx:
             assert len(self.f.args) == 2 and self.f.args[1].rows == n
             xo, to = exp_epigraph(v[:n], v[n:])
             return np.concatenate([xo, to])
+        if t == "SUM_KL_DIV":                            # arguments [x (n) | y (n) | t (1)]
+            assert len(self.f.args) == 3 and self.f.args[1].rows == n and self.f.args[2].rows == 1
+            xo, yo, to = kl_div_epigraph(v[:n], v[n:2 * n], float(v[2 * n]))
+            return np.concatenate([xo, yo, [to]])
         assert len(self.f.args) == 2 and self.f.args[1].rows == 1
         x, s = v[:n], float(v[n])
-        if t == "SUM_SQUARE":
+        if t == "SUM_NEG_LOG":
+            xo, to = neg_log_epigraph(x, s)
+        elif t == "SUM_NEG_ENTR":
+            xo, to = implicit_newton_epigraph(x, s, _neg_entr_eval, *SMOOTH[t])
+        elif t == "LOG_SUM_EXP":
+            xo, to = log_sum_exp_epigraph(x, s)
+        elif t == "SUM_LARGEST":
+            k = int(self.f.sum_largest_k)
+            xo, to = bisection_epigraph(x, s, lambda z, lam: sum_largest_prox(z, lam, k),
+                                        lambda z: _sum_largest_eval(z, k))
+        elif t == "SUM_SQUARE":
             xo, to = sum_square_epigraph(x, s)
         elif t == "MAX":
             xo, to = max_epigraph(x, s)
@@ -654,6 +820,8 @@ class _VectorProx:
         arg = lambda k: v[offs[k]:offs[k + 1]]
         if t == "MAX":
             return max_prox(v, float(self.lam[0]))
+        if t == "LOG_SUM_EXP":
+            return log_sum_exp_prox(v, float(self.lam[0]))
         if t == "SUM_LARGEST":
             return sum_largest_prox(v, float(self.lam[0]), int(self.f.sum_largest_k))
         if t == "SUM_KL_DIV":

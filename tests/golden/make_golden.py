@@ -210,6 +210,30 @@ def prox_cases():
     xe, te = Variable("x", 700), Variable("t", 700)
     out["exp_epigraph"] = (ProxFunction("EXP", epigraph=True, args=[Affine(700, [Term(xe)]), Affine(700, [Term(te)])]),
                            1.0, {"x": rng2.standard_normal(700) * 2, "t": rng2.standard_normal(700) * 2 + 1})
+    # implicit epigraph operators: Newton / bisection on the multiplier around the plain prox
+    rng3 = np.random.default_rng(9876)
+    n = 900
+    out["sum_neg_log_epigraph"] = (epi("SUM_NEG_LOG", n), 1.0, {"x": rng3.standard_normal(n) * 2,
+                                                                "t": np.array([-200.0])})
+    out["sum_neg_log_epigraph_loose"] = (epi("SUM_NEG_LOG", 60), 1.0, {"x": rng3.random(60) * 3 + 0.5,
+                                                                       "t": np.array([40.0])})
+    out["sum_neg_entr_epigraph"] = (epi("SUM_NEG_ENTR", n), 1.0, {"x": rng3.random(n) * 3 + 0.05,
+                                                                  "t": np.array([100.0])})
+    out["sum_neg_entr_epigraph_inside"] = (epi("SUM_NEG_ENTR", 80), 1.0, {"x": rng3.random(80) + 0.1,
+                                                                          "t": np.array([50.0])})
+    xk, yk, tk = Variable("x", 600), Variable("y", 600), Variable("t", 1)
+    out["sum_kl_div_epigraph"] = (ProxFunction("SUM_KL_DIV", epigraph=True, args=[
+        Affine(600, [Term(xk)]), Affine(600, [Term(yk)]), Affine(1, [Term(tk)])]), 1.0,
+        {"x": rng3.random(600) * 3 + 0.1, "y": rng3.random(600) * 3 + 0.1, "t": np.array([20.0])})
+    out["log_sum_exp"] = (simple("LOG_SUM_EXP", n, alpha=1.3), 0.9, {"x": rng3.standard_normal(n) * 3})
+    out["log_sum_exp_scaled_arg"] = (simple("LOG_SUM_EXP", 300, alpha=0.4, scale=2.0), 1.1,
+                                     {"x": rng3.standard_normal(300)})
+    out["log_sum_exp_epigraph"] = (epi("LOG_SUM_EXP", n), 1.0, {"x": rng3.standard_normal(n) * 2,
+                                                                "t": np.array([3.0])})
+    out["log_sum_exp_epigraph_inside"] = (epi("LOG_SUM_EXP", 40), 1.0, {"x": rng3.standard_normal(40),
+                                                                        "t": np.array([30.0])})
+    out["sum_largest_epigraph"] = (epi("SUM_LARGEST", n, sum_largest_k=7), 1.0,
+                                   {"x": rng3.standard_normal(n) * 2, "t": np.array([5.0])})
     return out
 
 

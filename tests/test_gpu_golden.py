@@ -108,7 +108,7 @@ def test_prox_matches_reference_golden(ctx, name):
     f, lam, v = make_golden.prox_cases()[name]
     gold = np.load(os.path.join(GOLDEN, "prox_" + name + ".npz"))
     x = eval_prox(f, lam, v, ctx=ctx)
-    tol = 1e-10 if f.type == "EXP" else 1e-12 if (f.epigraph or f.type in ("MAX", "SUM_LARGEST", "SUM_KL_DIV", "SECOND_ORDER_CONE")) else PROX_TOL[f.type]
+    tol = 1e-10 if f.type == "EXP" else 1e-12 if (f.epigraph or f.type in ("MAX", "SUM_LARGEST", "SUM_KL_DIV", "SECOND_ORDER_CONE", "LOG_SUM_EXP")) else PROX_TOL[f.type]
     for k in v:
         g = gold["x_" + k]
         if tol == 0.0:
