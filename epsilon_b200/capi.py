@@ -101,6 +101,7 @@ SIGNATURES = {
     "eps_problem_add_prox": (C.c_int, [_P, C.c_int, C.c_double, C.c_int, C.POINTER(C.c_int)]),
     "eps_problem_prox_sum_largest": (C.c_int, [_P, C.c_int, C.c_int]),
     "eps_problem_prox_soc_dims": (C.c_int, [_P, C.c_int, C.c_int, C.c_int]),
+    "eps_problem_prox_mat_dims": (C.c_int, [_P, C.c_int, C.c_int, C.c_int]),
     "eps_problem_prox_zone": (C.c_int, [_P, C.c_int, C.c_double, _DP, _DP, C.c_int]),
     "eps_problem_prox_add_arg": (C.c_int, [_P, C.c_int, C.c_int, C.POINTER(C.c_int)]),
     "eps_problem_prox_arg_sharded": (C.c_int, [_P, C.c_int, C.c_int, C.c_int64]),

@@ -81,6 +81,10 @@ const char* TypeName(int t) {
     case EPS_PROX_MAX: return "MAX";
     case EPS_PROX_SUM_LARGEST: return "SUM_LARGEST";
     case EPS_PROX_LOG_SUM_EXP: return "LOG_SUM_EXP";
+    case EPS_PROX_LAMBDA_MAX: return "LAMBDA_MAX";
+    case EPS_PROX_NEG_LOG_DET: return "NEG_LOG_DET";
+    case EPS_PROX_NORM_NUCLEAR: return "NORM_NUCLEAR";
+    case EPS_PROX_SEMIDEFINITE: return "SEMIDEFINITE";
     case EPS_PROX_SECOND_ORDER_CONE: return "SECOND_ORDER_CONE";
     case EPS_PROX_SUM_KL_DIV: return "SUM_KL_DIV";
     case EPS_PROX_TOTAL_VARIATION_1D: return "TOTAL_VARIATION_1D";
@@ -336,6 +340,7 @@ void eps_solver::Init(const eps_problem& original) {
         d.zone_alpha = f.q_alpha[0];
         d.zone_beta = f.q_beta[0];
       }
+      d.mat_m = f.mat_m; d.mat_n = f.mat_n;
       if (f.type == EPS_PROX_EXP)
         EPS_CHECK(f.epigraph && f.args.size() == 2 && f.args[1].rows == f.args[0].rows,
                   "prox %d (EXP): elementwise epigraph form over (x, t) of equal size", i);

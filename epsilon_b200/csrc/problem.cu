@@ -87,6 +87,15 @@ int eps_problem_prox_soc_dims(eps_problem* p, int prox_index, int m, int n) {
   EPS_API_END
 }
 
+int eps_problem_prox_mat_dims(eps_problem* p, int prox_index, int m, int n) {
+  EPS_API_BEGIN
+  EPS_CHECK(p && prox_index >= 0 && prox_index < (int)p->prox.size() && m > 0 && n > 0, "prox index %d, %d x %d",
+            prox_index, m, n);
+  p->prox[prox_index].mat_m = m;
+  p->prox[prox_index].mat_n = n;
+  EPS_API_END
+}
+
 int eps_problem_prox_add_arg(eps_problem* p, int prox_index, int rows, int* arg_index) {
   EPS_API_BEGIN
   EPS_CHECK(p && prox_index >= 0 && prox_index < (int)p->prox.size() && rows >= 0, "prox index %d", prox_index);

@@ -25,6 +25,7 @@ struct ProxFn {
   double zone_m = 0.0;
   int sum_largest_k = 0;
   int soc_m = 0, soc_n = 0;
+  int mat_m = 0, mat_n = 0;
   std::vector<double> q_alpha, q_beta;
   std::vector<AffineExpr> args;
 };

@@ -75,15 +75,24 @@ struct VecOpDesc {
   int k = 0;             // SUM_LARGEST: sum_largest_params.k
   int64_t soc_n = 0;     // SECOND_ORDER_CONE: columns of X (n0 = m rows)
   double soc_a = 1;      // at / |ax|
+  int mat_m = 0, mat_n = 0;  // matrix functions: mat(arg0, m, n), column-major (arg_size(0))
 };
 struct VecOpWork {
   DevBuf<double> keys, keys2, vals, vals2, scan1, scan2, scal, ev, ent, v0;
+  // matrix functions (prox_mat.cu): S / M, eigenvectors, result, spectrum, operator output, weights
+  DevBuf<double> mS, mQ, mX, md, mx, mw;
+  VecOpDesc inner_desc;
+  std::unique_ptr<VecOpWork> inner;
   DevBuf<int> idx;
   DevBuf<char> tmp;
 };
 bool IsVecOpType(int type, bool epigraph);
 void VecOpInit(Ctx* ctx, const VecOpDesc& d, VecOpWork* w);
 void VecOpApply(Ctx* ctx, const VecOpDesc& d, double* V, VecOpWork* w);
+// orthogonally invariant matrix functions (prox_mat.cu), reached through VecOpInit / VecOpApply
+bool IsMatOpType(int type);
+void MatOpInit(Ctx* ctx, const VecOpDesc& d, VecOpWork* w);
+void MatOpApply(Ctx* ctx, const VecOpDesc& d, double* V, VecOpWork* w);
 
 // out[i + c n] = d[i] * in[i + c n] + b * y[i + c n]  for c < k   (y may be null)
 void DiagMulti(Ctx* ctx, int64_t n, int k, const double* d, const double* in, double b, const double* y, double* out);

@@ -711,6 +711,7 @@ __global__ void SetScalarKernel(double* __restrict__ p, double v) { *p = v; }
 }  // namespace
 
 bool IsVecOpType(int type, bool epigraph) {
+  if (IsMatOpType(type)) return !epigraph || type != EPS_PROX_SEMIDEFINITE;
   if (epigraph)
     return type == EPS_PROX_SUM_SQUARE || type == EPS_PROX_MAX || type == EPS_PROX_NORM_1 ||
            type == EPS_PROX_SUM_HINGE || type == EPS_PROX_SUM_DEADZONE || type == EPS_PROX_SUM_QUANTILE ||
@@ -810,6 +811,10 @@ void VecOpInit(Ctx* ctx, const VecOpDesc& d, VecOpWork* w) {
   w->scal.alloc(ctx, SC_COUNT);
   w->scal.zero();
   w->idx.alloc(ctx, 4);
+  if (IsMatOpType(d.type)) {
+    MatOpInit(ctx, d, w);
+    return;
+  }
   if (IsGridNewton(d)) {
     w->keys.alloc(ctx, d.n0);    // copy of v
     w->keys2.alloc(ctx, d.n0);   // trial point of the line search
@@ -853,6 +858,10 @@ void VecOpInit(Ctx* ctx, const VecOpDesc& d, VecOpWork* w) {
 void VecOpApply(Ctx* ctx, const VecOpDesc& d, double* V, VecOpWork* w) {
   const int64_t n = d.n0;
   cudaStream_t st = ctx->stream;
+  if (IsMatOpType(d.type)) {
+    MatOpApply(ctx, d, V, w);
+    return;
+  }
   if (d.type == EPS_PROX_EXP) {
     ExpEpiKernel<<<Grid(n), kBlock, 0, st>>>(n, V);
     ctx->count_launch();

@@ -45,6 +45,10 @@ PROX_TYPES = {
     "SECOND_ORDER_CONE": 104,
     "SUM_LARGEST": 105,
     "TOTAL_VARIATION_1D": 106,
+    "LAMBDA_MAX": 200,
+    "NEG_LOG_DET": 202,
+    "NORM_NUCLEAR": 203,
+    "SEMIDEFINITE": 204,
 }
 
 # linear_map::ImplType order, src/epsilon/linear/linear_map.h (DENSE < SPARSE < DIAGONAL < SCALAR < KRONECKER).
@@ -154,6 +158,9 @@ class ProxFunction:
     sum_largest_k: int = 0
     # SECOND_ORDER_CONE: (m, n) of the matrix argument X (arg_size(1), second_order_cone.cc:31-35)
     soc_dims: Optional[Tuple[int, int]] = None
+    # matrix functions (LAMBDA_MAX, NEG_LOG_DET, NORM_NUCLEAR, SEMIDEFINITE): (m, n) of the matrix argument
+    # mat(x, m, n), column-major (arg_size(0), ortho_invariant.cc:12-16)
+    mat_dims: Optional[Tuple[int, int]] = None
 
 
 @dataclass

@@ -189,6 +189,9 @@ class _ProblemBuilder:
             if f.type == "SECOND_ORDER_CONE":
                 capi.check(self.lib.eps_problem_prox_soc_dims(self.handle, fi.value, int(f.soc_dims[0]),
                                                               int(f.soc_dims[1])))
+            if f.mat_dims is not None:
+                capi.check(self.lib.eps_problem_prox_mat_dims(self.handle, fi.value, int(f.mat_dims[0]),
+                                                              int(f.mat_dims[1])))
             if f.type == "SUM_LARGEST":
                 capi.check(self.lib.eps_problem_prox_sum_largest(self.handle, fi.value, int(f.sum_largest_k)))
             for ai_, a in enumerate(f.args):

@@ -59,7 +59,11 @@ enum eps_prox_type {
   EPS_PROX_NORM_2 = 102,
   EPS_PROX_SECOND_ORDER_CONE = 104,
   EPS_PROX_SUM_LARGEST = 105,
-  EPS_PROX_TOTAL_VARIATION_1D = 106
+  EPS_PROX_TOTAL_VARIATION_1D = 106,
+  EPS_PROX_LAMBDA_MAX = 200,
+  EPS_PROX_NEG_LOG_DET = 202,
+  EPS_PROX_NORM_NUCLEAR = 203,
+  EPS_PROX_SEMIDEFINITE = 204
 };
 
 /* SolverStatus.State, proto/epsilon/solver.proto:4-16. */
@@ -161,6 +165,9 @@ int eps_problem_prox_sum_largest(eps_problem* p, int prox_index, int k);
 /* SECOND_ORDER_CONE: arguments (t in R^m, X in R^{m x n} column-major); m, n = arg_size(1)
  * (second_order_cone.cc:31-35). */
 int eps_problem_prox_soc_dims(eps_problem* p, int prox_index, int m, int n);
+/* Matrix functions (LAMBDA_MAX, NEG_LOG_DET, NORM_NUCLEAR, SEMIDEFINITE): the first argument is
+ * mat(x, m, n), column-major; m, n = ProxFunction.arg_size(0).dim (src/epsilon/prox/ortho_invariant.cc:12-16). */
+int eps_problem_prox_mat_dims(eps_problem* p, int prox_index, int m, int n);
 int eps_problem_prox_add_arg(eps_problem* p, int prox_index, int rows, int* arg_index);
 /* Row-sharded argument (multi-GPU): the rows given to this rank are its slice of an
  * argument with `global_rows` rows; products H'H p and H'g are all-reduced. */

@@ -526,6 +526,55 @@ def _sum_largest_eval(x: np.ndarray, k: int) -> float:   # SumLargestProx::Eval,
         tot += y[i]
     return tot
 
+# orthogonally invariant matrix functions: type -> (vector operator on the spectrum, symmetric_part, add_residual)
+ORTHO_INVARIANT = {
+    "LAMBDA_MAX": ("MAX", True, False),             # lambda_max.cc
+    "NEG_LOG_DET": ("SUM_NEG_LOG", True, False),    # neg_log_det.cc
+    "NORM_NUCLEAR": ("NORM_1", False, False),       # norm_nuclear.cc
+    "SEMIDEFINITE": ("NON_NEGATIVE", True, True),   # semidefinite.cc
+}
+
+
+def ortho_invariant(ptype: str, epigraph: bool, m: int, n: int, lam: float, y: np.ndarray, s: float = 0.0):
+    """OrthoInvariantProx::ApplyVector, ortho_invariant.cc:18-73.  The nested "eigen prox" is a VectorProx with
+    H = I, A = (1/sqrt(lam)) I fed with d/sqrt(lam) (InitEigenProx :75-97, ApplyEigenProx :99-104), i.e.
+    prox_{lam f}(d); in the epigraph form it is the plain projection of (d, s).  Eigen's
+    SelfAdjointEigenSolver is LAPACK's eigh here: X = U f(d) V' does not depend on the eigenvector signs."""
+    inner, symmetric_part, add_residual = ORTHO_INVARIANT[ptype]
+    Y = y.reshape((m, n), order="F")
+    if symmetric_part:
+        d, V = np.linalg.eigh((Y + Y.T) / 2)
+        U = V
+    else:
+        d, V = np.linalg.eigh(Y.T @ Y + 1e-15 * np.eye(n))
+        d = np.sqrt(np.maximum(d, 0.0))
+        dinv = np.where(d != 0, 1.0 / np.where(d != 0, d, 1.0), 0.0)
+        U = Y @ V @ np.diag(dinv)
+    t = None
+    if epigraph:
+        if inner == "MAX":
+            xt, t = max_epigraph(d, s)
+        elif inner == "SUM_NEG_LOG":
+            xt, t = neg_log_epigraph(d, s)
+        else:
+            xt, t = scaled_zone_epigraph(d, s, 1.0, 1.0, 0.0)
+    elif inner == "MAX":
+        xt = max_prox(d, lam)
+    elif inner == "SUM_NEG_LOG":
+        xt = neg_log_prox(d, np.full(d.size, lam))
+    elif inner == "NORM_1":
+        xt = scaled_zone(d, np.full(d.size, lam), 1.0, 1.0, 0.0)
+    else:
+        xt = np.maximum(d, 0.0)
+    X = U @ np.diag(xt) @ V.T
+    if not epigraph:
+        if add_residual:
+            X = X + (Y - Y.T) / 2
+        elif symmetric_part:
+            X = (X + X.T) / 2
+    return X.ravel(order="F"), t
+
+
 # ---------------------------------------------------------------------------
 # 1-D total variation (C restatement in oracle/tv1d_dp.c; pure Python for small n)
 # ---------------------------------------------------------------------------
@@ -755,6 +804,10 @@ class _VectorProx:
         """Epigraph operators: arguments [x (n) | t (1)], projection onto {f(x) <= t}."""
         t = self.f.type
         n = self.f.args[0].rows
+        if t in ORTHO_INVARIANT:
+            m, k = self.f.mat_dims
+            xo, to = ortho_invariant(t, True, m, k, 1.0, v[:n], float(v[n]))
+            return np.concatenate([xo, [to]])
         if t == "EXP":                                   # elementwise: arguments [x (n) | t (n)]
             assert len(self.f.args) == 2 and self.f.args[1].rows == n
             xo, to = exp_epigraph(v[:n], v[n:])
@@ -818,6 +871,9 @@ class _VectorProx:
         sizes = [a.rows for a in self.f.args]
         offs = np.concatenate([[0], np.cumsum(sizes)])
         arg = lambda k: v[offs[k]:offs[k + 1]]
+        if t in ORTHO_INVARIANT:
+            m, k = self.f.mat_dims
+            return ortho_invariant(t, False, m, k, float(self.lam[0]), v)[0]
         if t == "MAX":
             return max_prox(v, float(self.lam[0]))
         if t == "LOG_SUM_EXP":

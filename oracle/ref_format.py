@@ -93,6 +93,8 @@ class _RefWriter:
         for k, a in enumerate(f.args):
             if f.type == "SECOND_ORDER_CONE" and k == 1:
                 pf += " arg_size { dim: %d dim: %d }" % tuple(f.soc_dims)
+            elif f.mat_dims is not None and k == 0:
+                pf += " arg_size { dim: %d dim: %d }" % tuple(f.mat_dims)
             else:
                 pf += " arg_size { dim: %d dim: 1 }" % a.rows
         if f.type == "SUM_DEADZONE":

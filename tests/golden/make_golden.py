@@ -53,6 +53,8 @@ SOLVE_CASES = {
     "mv_lasso_120x60x4": ("mv_lasso", (120, 60, 4), {"seed": 2}, {}),
     "mv_lasso_sparse_3000x300x5": ("mv_lasso", (3000, 300, 5), {"density": 0.02, "seed": 3}, {}),
     "l1_epigraph_denoise_300": ("l1_epigraph_denoise", (300,), {"seed": 1}, {"max_iterations": 400}),
+    "nuclear_denoise_30x12": ("nuclear_denoise", (30, 12), {"seed": 2}, {"max_iterations": 400, "rel_tol": 1e-5, "abs_tol": 1e-6}),
+    "covsel_12": ("sparse_inverse_covariance", (12,), {"seed": 3}, {"max_iterations": 600, "rel_tol": 1e-5, "abs_tol": 1e-6}),
 }
 
 
@@ -234,6 +236,35 @@ def prox_cases():
                                                                         "t": np.array([30.0])})
     out["sum_largest_epigraph"] = (epi("SUM_LARGEST", n, sum_largest_k=7), 1.0,
                                    {"x": rng3.standard_normal(n) * 2, "t": np.array([5.0])})
+    # orthogonally invariant matrix functions (ortho_invariant.cc): eigen-decomposition + a vector operator
+    rng4 = np.random.default_rng(2468)
+
+    def mat(ptype, m, n, epigraph=False, alpha=1.0):
+        X = Variable("x", m * n)
+        args = [Affine(m * n, [Term(X)])]
+        if epigraph:
+            args.append(Affine(1, [Term(Variable("t", 1))]))
+        return ProxFunction(ptype, args=args, alpha=alpha, epigraph=epigraph, mat_dims=(m, n))
+
+    def sym(n, shift=0.0):
+        a = rng4.standard_normal((n, n))
+        return ((a + a.T) / 2 + shift * np.eye(n)).ravel(order="F")
+
+    out["lambda_max"] = (mat("LAMBDA_MAX", 12, 12, alpha=1.5), 0.8, {"x": sym(12)})
+    out["lambda_max_epigraph"] = (mat("LAMBDA_MAX", 10, 10, epigraph=True), 1.0,
+                                  {"x": sym(10), "t": np.array([0.5])})
+    out["neg_log_det"] = (mat("NEG_LOG_DET", 15, 15, alpha=0.7), 1.2, {"x": sym(15, 1.0)})
+    out["neg_log_det_epigraph"] = (mat("NEG_LOG_DET", 9, 9, epigraph=True), 1.0,
+                                   {"x": sym(9, 2.0), "t": np.array([-20.0])})
+    out["norm_nuclear_tall"] = (mat("NORM_NUCLEAR", 20, 8, alpha=1.1), 0.9,
+                                {"x": rng4.standard_normal(160)})
+    # (a 6 x 14 case was drawn here: for m < n the reference sizes its nested prox min(m, n) while the spectrum
+    # of Y'Y has n entries, ortho_invariant.cc:77 vs :41-46, and returns its input; not a fixture)
+    rng4.standard_normal(84)
+    out["norm_nuclear_epigraph"] = (mat("NORM_NUCLEAR", 16, 11, epigraph=True), 1.0,
+                                    {"x": rng4.standard_normal(176), "t": np.array([8.0])})
+    out["semidefinite"] = (mat("SEMIDEFINITE", 16, 16), 1.0, {"x": rng4.standard_normal(256)})
+    out["semidefinite_64"] = (mat("SEMIDEFINITE", 64, 64), 1.0, {"x": rng4.standard_normal(4096)})
     return out
 
 

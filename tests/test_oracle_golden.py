@@ -74,7 +74,7 @@ def test_prox_matches_reference(name):
     for k in v:
         assert np.array_equal(v[k], gold["v_" + k]), "generator drift"
     x = onp.eval_prox(f, lam, v)
-    tol = 1e-10 if f.type == "EXP" else 1e-12 if (f.epigraph or f.type in ("MAX", "SUM_LARGEST", "SUM_KL_DIV", "SECOND_ORDER_CONE", "LOG_SUM_EXP")) else PROX_TOL[f.type]
+    tol = 1e-10 if f.type in ("EXP", "LAMBDA_MAX", "NEG_LOG_DET", "NORM_NUCLEAR", "SEMIDEFINITE") else 1e-12 if (f.epigraph or f.type in ("MAX", "SUM_LARGEST", "SUM_KL_DIV", "SECOND_ORDER_CONE", "LOG_SUM_EXP")) else PROX_TOL[f.type]
     for k in v:
         g = gold["x_" + k]
         if tol == 0.0:
