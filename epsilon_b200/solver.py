@@ -91,7 +91,9 @@ class LinearMap:
             a = np.asfortranarray(spec.dense, dtype=np.float64)
             capi.check(self.lib.eps_map_dense(ctx.handle, a.shape[0], a.shape[1], capi.dptr(a), h))
         elif spec.kind == MAP_SPARSE:
-            a = sp.csc_matrix(spec.sparse)
+            # a CSC matrix is taken as it is: re-wrapping it would drop scipy's cached "indices are
+            # sorted" flag and sort_indices() would rescan all nnz entries on the host (60 ms at nnz = 1e8)
+            a = spec.sparse if sp.isspmatrix_csc(spec.sparse) else sp.csc_matrix(spec.sparse)
             a.sort_indices()
             indptr = np.ascontiguousarray(a.indptr, dtype=np.int32)
             indices = np.ascontiguousarray(a.indices, dtype=np.int32)
