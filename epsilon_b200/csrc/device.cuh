@@ -22,6 +22,14 @@ __device__ __forceinline__ double GroupSum(double v) {
   return v;
 }
 
+// Programmatic dependent launch (PTX griddepcontrol): a kernel launched with
+// cudaLaunchAttributeProgrammaticStreamSerialization may start while its predecessor in the stream is
+// still running; GridDepWait() returns once that predecessor has completed and its writes are visible
+// (a no-op for a normal launch).  GridDepLaunch() in the predecessor lets the dependent CTAs be
+// scheduled as soon as resources free up instead of at its very end.
+__device__ __forceinline__ void GridDepWait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void GridDepLaunch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // Block-wide sum of NV values per thread; result valid in thread 0.  smem: NV*32 doubles.
 template <int NV>
 __device__ __forceinline__ void BlockSum(double (&v)[NV], double* smem) {

@@ -162,6 +162,8 @@ CgFusedTailKernel(int64_t n, int T, const double* __restrict__ planes, double al
   const int c = blockIdx.x;
 #define EPS_TT(k) if (trace && threadIdx.x == 0) trace[c * 8 + (k)] = GlobalTimerNs()
   EPS_TT(0);
+  GridDepLaunch();  // the next SpMV pass may start prefetching its matrix streams (sell.cu)
+  GridDepWait();    // no-op unless launched with programmatic serialization behind the SpMV pass
   const int parity = (int)(xseq & 1ull);
   const bool finished = *done != 0;  // uniform: only ever written by the last phase of an earlier launch
   // slice of this CTA (even length so that the rows stay 16-byte aligned)
@@ -746,8 +748,34 @@ void KktSolver::Solve(const double* rhs, double* x) {
             if (launch_no++ == trace_at) trace = tbuf.p;
           }
           void* args[] = {&nn, &T, &planes, &alpha, &wp, &pp, &xp, &rp, &sp, &part, &dp, &rg, &seq, &pxv, &xs, &dgp, &trace};
-          CUDA_CHECK(cudaLaunchCooperativeKernel((const void*)CgFusedTailKernel, dim3(tail_grid),
-                                                 dim3(kTailBlock), args, 0, ctx->stream));
+          // EPS_TAIL_PDL=1: cooperative + programmatic serialization (set-up overlaps the SpMV drain)
+          static int tail_pdl = getenv("EPS_TAIL_PDL") ? atoi(getenv("EPS_TAIL_PDL")) : 0;
+          bool launched = false;
+          if (tail_pdl) {
+            cudaLaunchConfig_t cfg = {};
+            cfg.gridDim = dim3(tail_grid);
+            cfg.blockDim = dim3(kTailBlock);
+            cfg.stream = ctx->stream;
+            cudaLaunchAttribute attr[2];
+            attr[0].id = cudaLaunchAttributeCooperative;
+            attr[0].val.cooperative = 1;
+            attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+            attr[1].val.programmaticStreamSerializationAllowed = 1;
+            cfg.attrs = attr;
+            cfg.numAttrs = 2;
+            cudaError_t e = cudaLaunchKernelExC(&cfg, (const void*)CgFusedTailKernel, args);
+            if (e == cudaSuccess) {
+              launched = true;
+            } else {
+              (void)cudaGetLastError();
+              fprintf(stderr, "[eps] cooperative + programmatic launch refused (%s): plain cooperative launch\n",
+                      cudaGetErrorString(e));
+              tail_pdl = 0;
+            }
+          }
+          if (!launched)
+            CUDA_CHECK(cudaLaunchCooperativeKernel((const void*)CgFusedTailKernel, dim3(tail_grid),
+                                                   dim3(kTailBlock), args, 0, ctx->stream));
           ctx->count_launch();
           if (trace) {
             std::vector<unsigned long long> h((size_t)tail_grid * 8);

@@ -53,6 +53,8 @@ __global__ void __launch_bounds__(256)
 SellReduceKernel(int R, int T, const double* __restrict__ P, double alpha, double beta,
                  double* __restrict__ y, const int* __restrict__ skip,
                  const double* __restrict__ ep_d, const double* __restrict__ ep_p) {
+  GridDepLaunch();  // the next SpMV pass may start prefetching its matrix streams
+  GridDepWait();    // launched with programmatic serialization behind the SpMV pass that writes P
   if (skip && *skip) return;
   const int row = blockIdx.x * 256 + threadIdx.x;
   if (row >= R) return;
@@ -320,8 +322,11 @@ SellStreamKernel(int R, int Cn, int TW, const int32_t* __restrict__ cta_visit,
   constexpr int kBatch = KB;
   extern __shared__ __align__(128) double xs[];
   __shared__ __align__(8) unsigned long long bar;
-  if (skip && *skip) return;  // speculative launch after the CG loop converged (kkt.cu)
+  // Launched with programmatic stream serialization (SellLaunch): everything up to GridDepWait() only
+  // touches the matrix streams, which the preceding kernel does not write, and may run while that
+  // kernel drains; x, P and the skip flag are read / written after it.
   if (TRACE && threadIdx.x == 0) trace[blockIdx.x * 4 + 0] = GlobalTimer();
+  GridDepLaunch();  // the plane reduction behind this pass is set up while the streams drain
   const int v_lo = cta_visit[blockIdx.x], v_hi = cta_visit[blockIdx.x + 1];
   if (v_lo >= v_hi) return;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -340,7 +345,7 @@ SellStreamKernel(int R, int Cn, int TW, const int32_t* __restrict__ cta_visit,
     if (restage) {
       // every warp is done reading the previous tile; nothing to wait for on the first visit
       if (vi != v_lo) __syncthreads();
-      if (use_tma && threadIdx.x == 0) {
+      if (vi != v_lo && use_tma && threadIdx.x == 0) {
         // one TMA bulk copy of the x tile (cp.async.bulk, completion on an mbarrier), issued
         // before anything else so that it overlaps the first loads of the streams
         const uint32_t bytes = (uint32_t)cw * 8u;
@@ -367,6 +372,18 @@ SellStreamKernel(int R, int Cn, int TW, const int32_t* __restrict__ cta_visit,
     c.sl_len = sl_len; c.rowid = rowid; c.P = P;
     c.cur = c.end = 0;
     if (sd.ss_cnt > 0) c.Start(sd.ss_begin, sd.ss_cnt);
+    if (vi == v_lo) {
+      // first visit: the loads above are in flight; now order behind the producer of x
+      GridDepWait();
+      if (skip && *skip) return;  // speculative launch after the CG loop converged (kkt.cu)
+      if (use_tma && threadIdx.x == 0) {
+        const uint32_t bytes = (uint32_t)cw * 8u;
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_a), "r"(bytes) : "memory");
+        asm volatile(
+            "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+            ::"r"(SmemAddr(xs)), "l"(x + c0), "r"(bytes), "r"(bar_a) : "memory");
+      }
+    }
     if (restage) {
       if (use_tma) {
         if (vi == v_lo) __syncthreads();  // the barrier init is visible to every thread
@@ -587,9 +604,25 @@ static double* SellLaunch(Ctx* ctx, const Sell& S, const double* x, int kclass, 
       case 24: kern = trace ? SellStreamKernel<24, 8, true> : SellStreamKernel<24, 8, false>; break;
       default: kern = trace ? SellStreamKernel<32, 8, true> : SellStreamKernel<32, 8, false>; break;
     }
-    kern<<<S.n_cta, S.nw * 32, (size_t)S.TW * 8 + 64, ctx->stream>>>(
-        S.R, S.Cn, S.TW, S.cta_visit.p, S.visit_tile.p, S.streams.p, S.sl_len.p, S.val.p, S.idx.p, S.rowid.p, x,
-        P, use_tma, skip, trace);
+    // programmatic stream serialization: the prologue (matrix prefetch) overlaps the tail of the
+    // kernel that produces x (EPS_NO_PDL=1: plain launch)
+    static const bool pdl = getenv("EPS_NO_PDL") == nullptr;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(S.n_cta);
+    cfg.blockDim = dim3(S.nw * 32);
+    cfg.dynamicSmemBytes = (size_t)S.TW * 8 + 64;
+    cfg.stream = ctx->stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    const int32_t *a_cv = S.cta_visit.p, *a_vt = S.visit_tile.p, *a_sl = S.sl_len.p, *a_ri = S.rowid.p;
+    const SellStream* a_st = S.streams.p;
+    const double* a_val = S.val.p;
+    const uint16_t* a_idx = S.idx.p;
+    CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, S.R, S.Cn, S.TW, a_cv, a_vt, a_st, a_sl, a_val, a_idx, a_ri, x, P,
+                                  use_tma, skip, trace));
     if (trace) {
       std::vector<unsigned long long> h((size_t)S.n_cta * 4);
       tbuf.download(h.data(), h.size());
@@ -634,8 +667,19 @@ void SellApply(Ctx* ctx, const Sell& S, double alpha, const double* x, double be
     return;
   }
   ProfScope ps(ctx, KC_VEC, 8.0 * S.T * S.R + 8.0 * S.R);
-  SellReduceKernel<<<(S.R + 255) / 256, 256, 0, ctx->stream>>>(S.R, S.T, P, alpha, beta, y, skip,
-                                                                ex ? ex->ep_d : nullptr, ex ? ex->ep_p : nullptr);
+  static const bool pdl = getenv("EPS_NO_PDL") == nullptr;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((S.R + 255) / 256);
+  cfg.blockDim = dim3(256);
+  cfg.stream = ctx->stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl ? 1 : 0;
+  const double* Pc = P;
+  const double *ep_d = ex ? ex->ep_d : nullptr, *ep_p = ex ? ex->ep_p : nullptr;
+  CUDA_CHECK(cudaLaunchKernelEx(&cfg, SellReduceKernel, S.R, S.T, Pc, alpha, beta, y, skip, ep_d, ep_p));
   ctx->count_launch();
 }
 
