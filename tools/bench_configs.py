@@ -37,7 +37,6 @@ def main():
     ap.add_argument("--kkt-mode", default="auto")
     ap.add_argument("--max-iterations", type=int, default=2000)
     ap.add_argument("--no-solve", action="store_true")
-    ap.add_argument("--check-oracle", action="store_true", help="compare the solution with the CPU oracle")
     a = ap.parse_args()
 
     from epsilon_b200 import problems
@@ -85,15 +84,6 @@ def main():
                         "objective": info["objective"](x), "r_norm": st["r_norm"], "s_norm": st["s_norm"],
                         "cg_iterations": st["cg_iterations"]}
         out["solver"] = s.describe().strip().split("\n")
-        if a.check_oracle:
-            from oracle import prox_admm_np as onp
-            t0 = time.time()
-            o = onp.ProxADMM(prob, {"max_iterations": a.max_iterations}).solve()
-            v = info["solution_var"]
-            out["oracle"] = {"num_iterations": o["status"]["num_iterations"], "state": o["status"]["state"],
-                             "objective": info["objective"](o["x"]), "seconds": round(time.time() - t0, 2),
-                             "x_max_abs_diff": float(np.abs(o["x"][v] - x[v]).max()),
-                             "r_norm": o["status"]["r_norm"], "s_norm": o["status"]["s_norm"]}
         s.close()
 
     s = ProxADMMSolver(prob, params, ctx=ctx)
