@@ -61,6 +61,7 @@ class Status(C.Structure):
         ("init_ms", C.c_double),
         ("loop_ms", C.c_double),
         ("cg_iterations", C.c_int64),
+        ("cg_unconverged", C.c_int64),
     ]
 
     def as_dict(self) -> dict:

@@ -303,8 +303,9 @@ int eps_solver_solve(eps_solver* s, eps_status* out, eps_trace_fn trace, void* u
   ctx->profile = s->params.profile != 0;
   if (!s->params.warm_start || !s->started) s->ResetVariables();
   s->started = true;
-  int64_t cg0 = 0;
-  for (auto& op : s->ops) if (op.kkt) cg0 += op.kkt->cg_iters_total;
+  int64_t cg0 = 0, un0 = 0;
+  for (auto& op : s->ops) if (op.kkt) { cg0 += op.kkt->cg_iters_total; un0 += op.kkt->cg_unconverged; }
+  if (s->proj) { cg0 += s->proj->cg_iters_total; un0 += s->proj->cg_unconverged; }
   cudaEvent_t e0, e1;
   CUDA_CHECK(cudaEventCreate(&e0));
   CUDA_CHECK(cudaEventCreate(&e1));
@@ -340,9 +341,11 @@ int eps_solver_solve(eps_solver* s, eps_status* out, eps_trace_fn trace, void* u
   CUDA_CHECK(cudaGetLastError());
   s->status.loop_ms = ms;
   s->status.iterations_run = run;
-  int64_t cg1 = 0;
-  for (auto& op : s->ops) if (op.kkt) cg1 += op.kkt->cg_iters_total;
+  int64_t cg1 = 0, un1 = 0;
+  for (auto& op : s->ops) if (op.kkt) { cg1 += op.kkt->cg_iters_total; un1 += op.kkt->cg_unconverged; }
+  if (s->proj) { cg1 += s->proj->cg_iters_total; un1 += s->proj->cg_unconverged; }
   s->status.cg_iterations = cg1 - cg0;
+  s->status.cg_unconverged = un1 - un0;
   ctx->profile = false;
   if (out) *out = s->status;
   EPS_API_END
@@ -355,8 +358,9 @@ int eps_solver_iterate(eps_solver* s, int iterations, float* elapsed_ms) {
   CUDA_CHECK(cudaSetDevice(ctx->device));
   ctx->profile = s->params.profile != 0;
   s->started = true;
-  int64_t cg0 = 0;
-  for (auto& op : s->ops) if (op.kkt) cg0 += op.kkt->cg_iters_total;
+  int64_t cg0 = 0, un0 = 0;
+  for (auto& op : s->ops) if (op.kkt) { cg0 += op.kkt->cg_iters_total; un0 += op.kkt->cg_unconverged; }
+  if (s->proj) { cg0 += s->proj->cg_iters_total; un0 += s->proj->cg_unconverged; }
   cudaEvent_t e0, e1;
   CUDA_CHECK(cudaEventCreate(&e0));
   CUDA_CHECK(cudaEventCreate(&e1));
@@ -373,9 +377,11 @@ int eps_solver_iterate(eps_solver* s, int iterations, float* elapsed_ms) {
   cudaEventDestroy(e0);
   cudaEventDestroy(e1);
   CUDA_CHECK(cudaGetLastError());
-  int64_t cg1 = 0;
-  for (auto& op : s->ops) if (op.kkt) cg1 += op.kkt->cg_iters_total;
+  int64_t cg1 = 0, un1 = 0;
+  for (auto& op : s->ops) if (op.kkt) { cg1 += op.kkt->cg_iters_total; un1 += op.kkt->cg_unconverged; }
+  if (s->proj) { cg1 += s->proj->cg_iters_total; un1 += s->proj->cg_unconverged; }
   s->status.cg_iterations = cg1 - cg0;
+  s->status.cg_unconverged = un1 - un0;
   s->status.iterations_run = iterations;
   s->status.loop_ms = ms;
   ctx->profile = false;

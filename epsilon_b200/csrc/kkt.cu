@@ -60,7 +60,8 @@ CgStartKernel(int64_t n, const double* __restrict__ rhs, const double* __restric
     acc[1] += b * b;
   }
   if (GridSumLast<2>(acc, smem, partials, counter)) {
-    const double thresh = tol * sqrt(acc[1]);
+    // rhs == 0 (exact solution 0): measure against the initial residual instead of a zero threshold
+    const double thresh = tol * sqrt(acc[1] > 0.0 ? acc[1] : acc[0]);
     const int conv = sqrt(acc[0]) <= thresh ? 1 : 0;
     scal[0] = acc[0];
     scal[1] = thresh;
@@ -657,6 +658,7 @@ void KktSolver::Solve(const double* rhs, double* x) {
     if (!no_multi && kron_k > 1 && inner->SolveMulti(rhs, x, kron_k)) return;
     for (int c = 0; c < kron_k; c++) inner->Solve(rhs + (size_t)c * nb, x + (size_t)c * nb);
     cg_iters_total += inner->cg_iters_total - before;
+    cg_unconverged = inner->cg_unconverged;
     return;
   }
   switch (mode) {
@@ -817,7 +819,10 @@ void KktSolver::Solve(const double* rhs, double* x) {
         }
         if (wait_result(base + it).converged != 0.0) { converged = true; break; }
       }
-      if (!converged) wait_result(base + it);  // it == cg_max_iter: drain the last iteration
+      if (!converged) {
+        // it == cg_max_iter: drain the last iteration; an inexact KKT solve is counted, never silent
+        if (wait_result(base + it).converged == 0.0) cg_unconverged++;
+      }
       cg_seq = base + cg_max_iter + 2;
       cg_iters_total += it;
       break;

@@ -51,6 +51,7 @@ struct KktSolver {
   double cg_tol = 1e-12;
   int cg_max_iter = 500;
   int64_t cg_iters_total = 0;
+  int64_t cg_unconverged = 0;    // inner solves that hit cg_max_iter above cg_tol (eps_status.cg_unconverged)
   int64_t gram_max_n = 60000;
   std::string description;
 

@@ -300,6 +300,28 @@ __global__ void GatherKernel(int64_t nnz, const int32_t* __restrict__ perm,
   val_out[k] = vals[p];
 }
 
+// Ingest validation of the wire CSC (the reference trusts Eigen's Map of the same arrays,
+// vector_util.cc:261-281; here a malformed matrix must come back as EPS_ERR_INVALID, not as an
+// out-of-bounds device access).  flag bit 0: colptr not monotone / row index outside [0, m);
+// bit 1: row indices not ascending inside a column (legal, but the kernels need them sorted).
+__global__ void CscValidateKernel(int m, int n, int64_t nnz, const int32_t* __restrict__ colptr,
+                                  const int32_t* __restrict__ rowidx, int* __restrict__ flag) {
+  const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k < n && colptr[k] > colptr[k + 1]) atomicOr(flag, 1);
+  if (k >= nnz) return;
+  const int r = rowidx[k];
+  if (r < 0 || r >= m) { atomicOr(flag, 1); return; }
+  if (k > 0 && rowidx[k - 1] > r) {
+    // a descent is fine exactly at a column start: find the column of k
+    int lo = 0, hi = n;
+    while (hi - lo > 1) {
+      const int mid = (lo + hi) >> 1;
+      if ((int64_t)colptr[mid] <= k) lo = mid; else hi = mid;
+    }
+    if ((int64_t)colptr[lo] != k) atomicOr(flag, 2);
+  }
+}
+
 __global__ void DiagScaleKernel(int n, const double* __restrict__ d, double alpha,
                                 const double* __restrict__ x, double beta, double* __restrict__ y) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -336,6 +358,37 @@ void BuildCsrFromHost(Ctx* ctx, int m, int n, int64_t nnz, const int64_t* rowptr
   out->col.upload(col, nnz);
   out->val.upload(val, nnz);
   CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+}
+
+// Returns after the wire CSC on the device has been checked; sorts the row indices of every column
+// when they arrive unsorted.  Throws EPS_ERR_INVALID for a malformed matrix.
+static void ValidateCscOnDevice(Ctx* ctx, Csr* At) {
+  const int n = At->m, m = At->n;
+  const int64_t nnz = At->nnz;
+  DevBuf<int> flag(ctx, 1);
+  flag.zero();
+  const int64_t work = std::max<int64_t>(nnz, n);
+  if (work == 0) return;
+  CscValidateKernel<<<(unsigned)((work + 255) / 256), 256, 0, ctx->stream>>>(m, n, nnz, At->rowptr.p, At->col.p, flag.p);
+  ctx->count_launch();
+  int h = 0;
+  flag.download(&h, 1);
+  if (h & 1) throw Error(EPS_ERR_INVALID, Format("malformed CSC matrix (%d x %d, nnz %lld): colptr is not "
+                                                 "non-decreasing or a row index lies outside [0, %d)", m, n,
+                                                 (long long)nnz, m));
+  if (h & 2) {
+    DevBuf<int32_t> keys(ctx, nnz);
+    DevBuf<double> vals(ctx, nnz);
+    size_t bytes = 0;
+    CUDA_CHECK(cub::DeviceSegmentedSort::SortPairs(nullptr, bytes, At->col.p, keys.p, At->val.p, vals.p, (int)nnz, n,
+                                                   At->rowptr.p, At->rowptr.p + 1, ctx->stream));
+    DevBuf<char> tmp(ctx, bytes);
+    CUDA_CHECK(cub::DeviceSegmentedSort::SortPairs(tmp.p, bytes, At->col.p, keys.p, At->val.p, vals.p, (int)nnz, n,
+                                                   At->rowptr.p, At->rowptr.p + 1, ctx->stream));
+    CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+    At->col = std::move(keys);
+    At->val = std::move(vals);
+  }
 }
 
 // CSC (= CSR of A') on the device -> CSR of A, by a stable radix sort on the row index
@@ -436,6 +489,7 @@ extern "C" {
 int eps_map_dense(eps_ctx* ctx, int m, int n, const double* colmajor, eps_map** out) {
   EPS_API_BEGIN
   EPS_CHECK(ctx && out && m >= 0 && n >= 0, "eps_map_dense arguments");
+  EPS_CHECK(colmajor || (size_t)m * n == 0, "eps_map_dense: null data pointer");
   CUDA_CHECK(cudaSetDevice(ctx->c.device));
   auto d = std::make_shared<MapData>();
   d->ctx = &ctx->c; d->kind = MK_DENSE; d->m = m; d->n = n;
@@ -458,6 +512,7 @@ int eps_map_csc(eps_ctx* ctx, int m, int n, int64_t nnz, const int32_t* colptr,
                 const int32_t* rowidx, const double* vals, eps_map** out) {
   EPS_API_BEGIN
   EPS_CHECK(ctx && out && m >= 0 && n >= 0 && nnz >= 0, "eps_map_csc arguments");
+  EPS_CHECK(colptr && (nnz == 0 || (rowidx && vals)), "eps_map_csc: null colptr / rowidx / vals");
   EPS_CHECK(nnz < (int64_t)2147483647, "nnz %lld does not fit int32 offsets (shard the rows)",
             (long long)nnz);
   EPS_CHECK(colptr[0] == 0 && colptr[n] == nnz, "colptr[0]=%d colptr[n]=%d nnz=%lld", colptr[0],
@@ -481,7 +536,7 @@ int eps_map_csc(eps_ctx* ctx, int m, int n, int64_t nnz, const int32_t* colptr,
   t.rowptr.upload(colptr, n + 1);
   t.col.upload(rowidx, nnz);
   t.val.upload(vals, nnz);
-  CUDA_CHECK(cudaStreamSynchronize(ctx->c.stream));
+  ValidateCscOnDevice(&ctx->c, &t);   // synchronises; EPS_ERR_INVALID instead of a device fault
   const auto t1 = timing ? now() : t0;
   TransposeCsrOnDevice(&ctx->c, t, &d->csr);
   const auto t2 = timing ? now() : t0;
@@ -509,6 +564,7 @@ int eps_map_csc(eps_ctx* ctx, int m, int n, int64_t nnz, const int32_t* colptr,
 int eps_map_diagonal(eps_ctx* ctx, int n, const double* dvals, eps_map** out) {
   EPS_API_BEGIN
   EPS_CHECK(ctx && out && n >= 0, "eps_map_diagonal arguments");
+  EPS_CHECK(dvals || n == 0, "eps_map_diagonal: null data pointer");
   CUDA_CHECK(cudaSetDevice(ctx->c.device));
   auto d = std::make_shared<MapData>();
   d->ctx = &ctx->c; d->kind = MK_DIAGONAL; d->m = n; d->n = n;

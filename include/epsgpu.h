@@ -211,6 +211,8 @@ typedef struct eps_status {
   double init_ms;           /* host wall time of eps_solver_create */
   double loop_ms;           /* CUDA-event time of the iteration loop of the last call */
   int64_t cg_iterations;    /* inner CG iterations of the last call (all KKT solves) */
+  int64_t cg_unconverged;   /* inner CG solves of the last call that stopped at cg_max_iterations
+                               above cg_tol: the KKT prox was inexact there (0 in a healthy run) */
 } eps_status;
 
 /* Per-epoch callback: the reference offers status callbacks only at the end

@@ -38,6 +38,11 @@ SOLVE_CASES = {
     "lasso_config1_1000x5000": ("lasso", (1000, 5000), {}, {}),
     "lasso_sparse_4000x400": ("lasso", (4000, 400), {"density": 0.02, "seed": 3}, {}),
     "lasso_sparse_30000x3000": ("lasso", (30000, 3000), {"density": 0.001, "seed": 8}, {}),
+    # at / above the 2^18-nnz threshold from which the device packs sparse maps as stream-SELL (the
+    # headline kernels), still small enough for the reference to factor (n^2 dense inverse)
+    "lasso_sparse_120000x4000": ("lasso", (120000, 4000), {"density": 0.001, "seed": 13}, {}),
+    "logreg_l1_sparse_60000x2000": ("logreg_l1", (60000, 2000), {"density": 0.005, "seed": 14}, {"max_iterations": 200}),
+    "hinge_l2_sparse_80000x3000": ("hinge_l2", (80000, 3000), {"density": 0.002, "seed": 15}, {"max_iterations": 300}),
     "logreg_l1_2000x200": ("logreg_l1", (2000, 200), {"density": 0.05, "seed": 4}, {"max_iterations": 200}),
     "logreg_l1_dense_500x80": ("logreg_l1", (500, 80), {"seed": 9}, {"max_iterations": 200}),
     "hinge_l2_1500x100": ("hinge_l2", (1500, 100), {"seed": 5}, {"max_iterations": 300}),

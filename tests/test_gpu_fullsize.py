@@ -1,9 +1,15 @@
 """Parity at BASELINE.json's full size (sparse lasso 1M x 100k, nnz 1e8), where the compiled
 reference cannot run (it would form and invert a dense 100k x 100k matrix,
 src/epsilon/linear/sparse_matrix_impl.cc:60-78): the linear maps are checked against scipy on
-the same bytes and through size-independent properties (adjointness, linearity), the whole
-solve through the agreement of two independent device paths (stream-SELL kernels + fused CG
-update vs plain CSR kernels + unfused CG) and the optimality conditions of the lasso."""
+the same bytes and through size-independent properties (adjointness, linearity); the whole
+solve -- stream-SELL kernels + fused CG update, and plain CSR kernels + unfused CG -- against
+tests/golden/lasso_sparse_1Mx100k.npz: the pinned CPU oracle run matrix-free on exactly this
+instance (tests/golden/make_fullsize.py), per-epoch residuals, iteration count, solution and
+objective; and the optimality conditions of the lasso."""
+import hashlib
+import json
+import os
+
 import numpy as np
 import pytest
 
@@ -14,6 +20,8 @@ from epsilon_b200.solver import LinearMap, ProxADMMSolver
 pytestmark = pytest.mark.gpu
 
 M, N, DENSITY = 1_000_000, 100_000, 1e-3
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+TRACE_KEYS = ("state", "num_iterations", "r_norm", "s_norm", "epsilon_primal", "epsilon_dual")
 
 
 @pytest.fixture(scope="module")
@@ -48,31 +56,57 @@ def test_spmv_full_size_vs_scipy_and_adjoint(ctx, full):
     assert np.array_equal(lm.apply(x), ax)
 
 
-def test_lasso_full_size_two_device_paths_agree(ctx, full, monkeypatch):
+def _check_against_fixture(x, st, trace, info, desc):
+    gold = np.load(os.path.join(GOLDEN, "lasso_sparse_1Mx100k.npz"))
+    assert [st["m"], st["n"], st["N"]] == gold["mnN"].tolist(), desc
+    assert len(trace) == gold["trace"].shape[0], (len(trace), desc)
+    for t, g in zip(trace, gold["trace"]):
+        gd = dict(zip(TRACE_KEYS, g))
+        assert t["num_iterations"] == int(gd["num_iterations"]) and t["state"] == int(gd["state"]), (t, gd)
+        for k in TRACE_KEYS[2:]:
+            assert t[k] == pytest.approx(gd[k], rel=1e-7), (k, t, gd, desc)
+    gst = dict(zip(TRACE_KEYS, gold["status"]))
+    assert st["num_iterations"] == int(gst["num_iterations"]) and st["state"] == int(gst["state"]) == 3
+    assert st["cg_unconverged"] == 0
+    xv = x["x"]
+    assert np.abs(xv - gold["x"]).max() <= 1e-7 * max(1.0, np.abs(gold["x"]).max())
+    assert info["objective"](x) == pytest.approx(float(gold["objective"]), rel=1e-9)
+
+
+def test_generator_reproduces_the_fixture_inputs(full):
+    """The oracle fixture only means something on identical input bytes."""
+    _, info = full
+    meta = json.load(open(os.path.join(GOLDEN, "lasso_sparse_1Mx100k.json")))
+    a = info["A"]
+    h = hashlib.sha256()
+    h.update(a.indptr.astype(np.int32).tobytes())
+    h.update(a.indices.astype(np.int32).tobytes())
+    h.update(a.data.astype(np.float64).tobytes())
+    h.update(np.asarray(info["b"], dtype=np.float64).tobytes())
+    h.update(np.float64(info["lam"]).tobytes())
+    assert h.hexdigest() == meta["digest"]
+
+
+@pytest.mark.parametrize("fmt", ["sell", "csr"])
+def test_lasso_full_size_matches_oracle_fixture(ctx, full, fmt, monkeypatch):
+    """sell: SellStreamKernel + SellReduceKernel + CgFusedTailKernel (the kernels bench.py times);
+    csr: CsrSpmvKernel + CgStartKernel/CgTailKernel."""
     prob, info = full
+    monkeypatch.setenv("EPS_SPARSE_FORMAT", fmt)
     with ProxADMMSolver(prob, {"cg_tol": 1e-12}, ctx=ctx) as s:
-        x1 = s.solve()
-        st1, tr1 = s.status.as_dict(), list(s.trace)
-    monkeypatch.setenv("EPS_SPARSE_FORMAT", "csr")     # CSR kernels, CgStart/CgTail pair
-    with ProxADMMSolver(prob, {"cg_tol": 1e-12}, ctx=ctx) as s:
-        x2 = s.solve()
-        st2, tr2 = s.status.as_dict(), list(s.trace)
-    monkeypatch.delenv("EPS_SPARSE_FORMAT")
-    assert st1["state"] == st2["state"] == 3                     # OPTIMAL
-    assert st1["num_iterations"] == st2["num_iterations"]
-    assert len(tr1) == len(tr2)
-    for a, b in zip(tr1, tr2):
-        for k in ("r_norm", "s_norm", "epsilon_primal", "epsilon_dual"):
-            assert a[k] == pytest.approx(b[k], rel=1e-7), (k, a, b)
-    xv1, xv2 = x1["x"], x2["x"]
-    assert np.abs(xv1 - xv2).max() <= 1e-8 * max(1.0, np.abs(xv1).max())
-    assert info["objective"](x1) == pytest.approx(info["objective"](x2), rel=1e-9)
+        x = s.solve()
+        st, trace, desc = s.status.as_dict(), list(s.trace), s.describe()
+    assert ("fused-tail" in desc) == (fmt == "sell"), desc
+    _check_against_fixture(x, st, trace, info, desc)
+    if fmt == "csr":
+        return
     # optimality of the lasso at the ADMM tolerance: on the support the gradient of the smooth
     # part balances lam * sign(x); off the support it stays inside [-lam, lam]
+    xv = x["x"]
     a, b, lam = info["A"], info["b"], info["lam"]
-    g = 2 * np.asarray(a.T @ (np.asarray(a @ xv1).ravel() - b)).ravel()
+    g = 2 * np.asarray(a.T @ (np.asarray(a @ xv).ravel() - b)).ravel()
     tol = 0.05 * lam                                              # rel_tol 1e-2 of the solver
-    on = xv1 != 0
+    on = xv != 0
     assert on.sum() > 0
-    assert np.abs(g[on] + lam * np.sign(xv1[on])).max() <= tol
+    assert np.abs(g[on] + lam * np.sign(xv[on])).max() <= tol
     assert np.abs(g[~on]).max() <= lam + tol

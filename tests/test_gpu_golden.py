@@ -36,13 +36,26 @@ MODES = {
     "mv_lasso_40x100x3": ["auto", "cg", "gram"],
     "mv_lasso_120x60x4": ["auto", "cg"],
     "mv_lasso_sparse_3000x300x5": ["auto", "cg"],
+    # nnz >= 2^18: packed as stream-SELL without being asked to
+    "lasso_sparse_120000x4000": ["auto", "cg"],
+    "logreg_l1_sparse_60000x2000": ["auto", "cg"],
+    "hinge_l2_sparse_80000x3000": ["auto", "cg"],
 }
+
+# Sparse cases below the 2^18-nnz threshold are run a second time with EPS_SPARSE_FORMAT=sell, so that
+# the kernels every headline number comes from (SellStreamKernel + SellReduceKernel, and in CG mode on
+# the lasso the fused CgFusedTailKernel) are held to the REFERENCE's traces, not only to each other.
+SELL_FORCED = ["lasso_sparse_4000x400", "lasso_sparse_30000x3000", "hinge_l2_sparse_5000x300",
+               "logreg_l1_2000x200", "mv_lasso_sparse_3000x300x5"]
+SELL_NATURAL = ["lasso_sparse_120000x4000", "logreg_l1_sparse_60000x2000", "hinge_l2_sparse_80000x3000"]
 
 
 def _cases():
     for name in sorted(INDEX["solve"]):
         for mode in MODES.get(name, ["auto"]):
-            yield name, mode
+            yield name, mode, "default"
+            if name in SELL_FORCED:
+                yield name, mode, "sell"
 
 
 _EXPECTED = {}
@@ -70,16 +83,24 @@ def _expected(name, prob, info, params):
     return gold
 
 
-@pytest.mark.parametrize("name,mode", list(_cases()))
-def test_admm_matches_reference_golden(ctx, name, mode):
+@pytest.mark.parametrize("name,mode,fmt", list(_cases()))
+def test_admm_matches_reference_golden(ctx, name, mode, fmt, monkeypatch):
     prob, info, params = make_golden.make_problem(name)
     gold = _expected(name, prob, info, params)
     p = dict(params, kkt_mode=mode)
+    if fmt != "default":
+        monkeypatch.setenv("EPS_SPARSE_FORMAT", fmt)   # read by eps_map_csc at every ingest
+    launches0 = ctx.kernel_launches
     with ProxADMMSolver(prob, p, ctx=ctx) as s:
         x = s.solve()
         st = s.status.as_dict()
         trace = list(s.trace)
         desc = s.describe()
+    assert ctx.kernel_launches > launches0
+    assert st["cg_unconverged"] == 0, desc     # every inner CG solve reached cg_tol (1e-12)
+    if (fmt == "sell" or name in SELL_NATURAL) and mode == "cg" and name.startswith("lasso_sparse"):
+        # the headline kernel trio: stream-SELL passes + the fused reduce / CG-update kernel
+        assert "fused-matvec" in desc and "fused-tail" in desc, desc
     assert [st["m"], st["n"], st["N"]] == gold["mnN"].tolist(), desc
     assert len(trace) == gold["trace"].shape[0], (len(trace), gold["trace"].shape, desc)
     rtol = 1e-9 if mode != "cg" else 1e-7
@@ -200,8 +221,15 @@ def test_unsupported_structure_is_an_error(ctx):
         eval_prox(f, 1.0, {"x": rng.standard_normal(5)}, ctx=ctx)
 
 
-@pytest.mark.parametrize("name", sorted(INDEX.get("two_block", {})))
-def test_two_block_matches_reference_golden(ctx, name):
+def _tb_cases():
+    for name in sorted(INDEX.get("two_block", {})):
+        yield name, "default"
+        if name in ("tb_lasso_sparse_4000x400", "tb_logreg_l1_2000x200"):
+            yield name, "sell"
+
+
+@pytest.mark.parametrize("name,fmt", list(_tb_cases()))
+def test_two_block_matches_reference_golden(ctx, name, fmt, monkeypatch):
     """ProxADMMTwoBlockSolver (SolverParams.solver = PROX_ADMM_TWO_BLOCK) on the device vs the
     stock reference solver: identical iteration counts, per-epoch residuals, solution."""
     prob, info, params = make_golden.make_problem(name)
@@ -213,6 +241,8 @@ def test_two_block_matches_reference_golden(ctx, name):
                 "status": np.array([o["status"][k] for k in TRACE_KEYS], dtype=np.float64),
                 "x": o["x"][INDEX["two_block"][name]["solution_var"]],
                 "objective": np.float64(info["objective"](o["x"]))}
+    if fmt != "default":
+        monkeypatch.setenv("EPS_SPARSE_FORMAT", fmt)
     with ProxADMMSolver(prob, dict(params, solver="PROX_ADMM_TWO_BLOCK"), ctx=ctx) as s:
         x = s.solve()
         st = s.status.as_dict()

@@ -131,3 +131,60 @@ def test_buffers_may_outlive_their_context():
     assert np.isfinite(lm2.apply(rng.standard_normal(3000))).all()
     lm2.close()
     c2.close()
+
+
+def _raw_csc(ctx, m, n, indptr, indices, data):
+    """eps_map_csc on raw arrays (no scipy canonicalisation in between)."""
+    import ctypes as C
+    from epsilon_b200 import capi
+    indptr = np.ascontiguousarray(indptr, dtype=np.int32)
+    indices = np.ascontiguousarray(indices, dtype=np.int32)
+    data = np.ascontiguousarray(data, dtype=np.float64)
+    h = C.c_void_p()
+    rc = ctx.lib.eps_map_csc(ctx.handle, m, n, len(data), capi.iptr(indptr), capi.iptr(indices),
+                             capi.dptr(data), C.byref(h))
+    return rc, h
+
+
+@pytest.mark.parametrize("defect", ["row_out_of_range", "negative_row", "colptr_not_monotone"])
+def test_malformed_csc_is_an_error_code_not_a_device_fault(ctx, defect):
+    """a malformed wire matrix must come back as EPS_ERR_INVALID; the context stays usable."""
+    rng = np.random.default_rng(5)
+    a = sp.random(300, 40, density=0.1, random_state=7, format="csc")
+    indptr, indices, data = a.indptr.copy(), a.indices.copy(), a.data.copy()
+    if defect == "row_out_of_range":
+        indices[len(indices) // 2] = 300
+    elif defect == "negative_row":
+        indices[3] = -1
+    else:
+        indptr[10], indptr[11] = indptr[11], indptr[10]
+        assert indptr[10] > indptr[11]
+    rc, h = _raw_csc(ctx, 300, 40, indptr, indices, data)
+    assert rc == -1 and not h.value
+    assert b"malformed CSC" in ctx.lib.eps_last_error()
+    # no sticky CUDA error: the same context still computes
+    lm = LinearMap(ctx, LinearMapSpec.Sparse(a))
+    x = rng.standard_normal(40)
+    assert np.abs(lm.apply(x) - a @ x).max() <= 1e-13
+
+
+@pytest.mark.parametrize("fmt", ["csr", "sell"])
+def test_unsorted_csc_columns_are_sorted_at_ingest(ctx, fmt, monkeypatch):
+    """Row indices in arbitrary order inside a column are legal CSC (Eigen accepts them); the device kernels
+    need them ascending, so ingest sorts them."""
+    monkeypatch.setenv("EPS_SPARSE_FORMAT", fmt)
+    rng = np.random.default_rng(6)
+    a = sp.random(5000, 700, density=0.02, random_state=8, format="csc")
+    a.sort_indices()
+    indptr, indices, data = a.indptr.copy(), a.indices.copy(), a.data.copy()
+    for j in range(700):
+        lo, hi = indptr[j], indptr[j + 1]
+        perm = rng.permutation(hi - lo)
+        indices[lo:hi] = indices[lo:hi][perm]
+        data[lo:hi] = data[lo:hi][perm]
+    rc, h = _raw_csc(ctx, 5000, 700, indptr, indices, data)
+    assert rc == 0
+    lm = LinearMap(ctx, _handle=h)
+    x, y = rng.standard_normal(700), rng.standard_normal(5000)
+    assert np.abs(lm.apply(x) - a @ x).max() <= 1e-13 * 10
+    assert np.abs(lm.transpose().apply(y) - a.T @ y).max() <= 1e-13 * 100
