@@ -43,11 +43,15 @@ def parse_args():
     ap.add_argument("--cg-tol", type=float, default=1e-12)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--ref-m", type=int, default=30_000)
-    ap.add_argument("--ref-n", type=int, default=3_000)
-    # --impl reference: a larger sample (Init = dense n x n inverse, ~35 s per repetition at n = 6000)
+    # The reference's CPU solver cannot complete 1M x 100k (dense 100k x 100k inverse); both the
+    # cpu_baseline of our arm and --impl reference run it on this sample of the same generator
+    # (Init = dense n x n inverse, 35-80 s on one core at n = 6000), and our arm times the GPU on the
+    # SAME sample as well ("vs_reference_same_config").
+    ap.add_argument("--ref-m", type=int, default=60_000)
+    ap.add_argument("--ref-n", type=int, default=6_000)
     ap.add_argument("--ref-arm-m", type=int, default=60_000)
     ap.add_argument("--ref-arm-n", type=int, default=6_000)
+    ap.add_argument("--no-parity-check", action="store_true")
     return ap.parse_args()
 
 
@@ -145,6 +149,8 @@ def run_reference_sample(ref_m: int, ref_n: int, density: float) -> dict:
         "init_s": r["init_s"], "loop_s": r["loop_s"], "iterations": iters,
         "num_iterations": r["status"]["num_iterations"], "state": r["status"]["state"],
         "wall_s": wall, "host_cpus": os.cpu_count(),
+        "e2e_value": iters / (r["loop_s"] + r["init_s"]),
+        "_trace": r["trace"], "_x": r["x"],
     }
 
 
@@ -162,7 +168,7 @@ def main_reference(args):
         init_total += last["init_s"]
     value = steps_total / loop_total
     e2e_value = steps_total / (loop_total + init_total)
-    cb = dict(last)
+    cb = {k: v for k, v in last.items() if not k.startswith("_")}
     cb["value"] = value
     line = {
         "impl": "reference", "metric": "prox-ADMM iterations/s", "value": value,
@@ -176,6 +182,48 @@ def main_reference(args):
         "gpu_launches": 0,
     }
     print(json.dumps(line))
+
+
+# ----------------------------------------------------------------------------------------
+# self-check of the timed solve (the checker, never the thing measured)
+# ----------------------------------------------------------------------------------------
+TRACE_KEYS = ("state", "num_iterations", "r_norm", "s_norm", "epsilon_primal", "epsilon_dual")
+
+
+def compare_traces(trace, gold_rows, rtol=1e-7):
+    """Per-epoch comparison of a device trace (list of status dicts) with rows of TRACE_KEYS values.
+    Returns (ok, max relative difference of r, s, eps_pri, eps_dual, first mismatch or None)."""
+    if len(trace) != len(gold_rows):
+        return False, None, "epochs %d vs %d" % (len(trace), len(gold_rows))
+    max_rel = 0.0
+    for t, g in zip(trace, gold_rows):
+        gd = dict(zip(TRACE_KEYS, g))
+        if t["num_iterations"] != int(gd["num_iterations"]) or t["state"] != int(gd["state"]):
+            return False, max_rel, "epoch %s: state/iteration %s vs %s" % (gd["num_iterations"], (t["state"], t["num_iterations"]),
+                                                                            (int(gd["state"]), int(gd["num_iterations"])))
+        for k in TRACE_KEYS[2:]:
+            rel = abs(t[k] - gd[k]) / max(abs(gd[k]), 1e-300)
+            max_rel = max(max_rel, rel)
+            if rel > rtol and abs(t[k] - gd[k]) > 1e-12:
+                return False, max_rel, "epoch %d %s: %.17g vs %.17g" % (int(gd["num_iterations"]), k, t[k], gd[k])
+    return True, max_rel, None
+
+
+def parity_check_fullsize(args, trace, x, objective):
+    """The e2e solve of the bench instance against tests/golden/lasso_sparse_1Mx100k.npz (the pinned CPU oracle
+    run matrix-free on this exact instance, tests/golden/make_fullsize.py)."""
+    path = os.path.join(ROOT, "tests", "golden", "lasso_sparse_1Mx100k.npz")
+    if (args.m, args.n, args.density) != (1_000_000, 100_000, 1e-3) or not os.path.exists(path):
+        return {"ok": None, "against": None, "note": "no fixture for this shape"}
+    gold = np.load(path)
+    ok, max_rel, why = compare_traces(trace, gold["trace"])
+    obj_rel = abs(objective - float(gold["objective"])) / abs(float(gold["objective"]))
+    x_abs = float(np.abs(x - gold["x"]).max())
+    ok = bool(ok and obj_rel <= 1e-7 and x_abs <= 1e-7 * max(1.0, float(np.abs(gold["x"]).max())))
+    return {"ok": ok, "max_rel": max_rel, "objective_rel": obj_rel, "x_max_abs": x_abs, "epochs": len(trace),
+            "rtol": 1e-7, "mismatch": why,
+            "against": "tests/golden/lasso_sparse_1Mx100k.npz (CPU oracle, matrix-free, same instance): "
+                       "per-epoch r, s, eps_pri, eps_dual, states, iteration count, objective, x"}
 
 
 # ----------------------------------------------------------------------------------------
@@ -240,6 +288,7 @@ def main_ours(args):
     pinned = [torch.from_numpy(v).pin_memory() for v in (a.data, a.indices, a.indptr)]
     a.data, a.indices, a.indptr = (t.numpy() for t in pinned)
     e2e = None
+    parity = None
     h2d_bytes = 12 * nnz_local + 4 * (args.n + 1) + 8 * m_local
     if not args.no_e2e:
         # one untimed whole solve first: CUDA module loading, first-touch allocations and the
@@ -256,6 +305,13 @@ def main_ours(args):
         st = s.status.as_dict()
         iters = st["iterations_run"]
         obj = info["objective"](x)
+        if not args.no_parity_check:
+            parity = parity_check_fullsize(args, list(s.trace), x["x"], obj)
+            # every rank must have taken the same decisions
+            agree = allreduce(np.array([st["num_iterations"], st["r_norm"], st["s_norm"]], dtype=np.float64)) / world
+            parity["ranks_agree"] = bool(np.array_equal(agree, np.array([st["num_iterations"], st["r_norm"], st["s_norm"]])))
+            if parity["ok"] is not None:
+                parity["ok"] = bool(parity["ok"] and parity["ranks_agree"] and st["cg_unconverged"] == 0)
         e2e = {"value": iters / t_e2e, "unit": "iterations/s",
                "h2d_bytes_per_step": h2d_bytes / iters, "d2h_bytes_per_step": 8 * 2 * args.n / iters,
                "warmup_solves": 1, "host_buffers": "pinned (cudaHostAlloc)",
@@ -345,9 +401,41 @@ def main_ours(args):
     }
 
     cpu_baseline = None
+    same_config = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         try:
-            cpu_baseline = run_reference_sample(args.ref_m, args.ref_n, args.density)
+            ref = run_reference_sample(args.ref_m, args.ref_n, args.density)
+            cpu_baseline = {k: v for k, v in ref.items() if not k.startswith("_")}
+            # like-for-like pair: the GPU arm on the SAME instance the reference arm runs (the reference cannot
+            # run the 1M x 100k workload), steady state and end to end from host buffers, and held to the
+            # reference's own per-epoch trace of this run
+            sprob, sinfo = problems.lasso_sparse_panels(args.ref_m, args.ref_n, args.density, panels=PANELS, seed=0)
+            with ProxADMMSolver(sprob, {}, ctx=ctx) as s0:          # warm-up solve (module load of the dense kernels)
+                s0.solve()
+            ctx.synchronize()
+            t0 = time.time()
+            ss = ProxADMMSolver(sprob, {}, ctx=ctx)
+            sx = ss.solve()
+            ctx.synchronize()
+            t_s = time.time() - t0
+            sst, strace, sdesc = ss.status.as_dict(), list(ss.trace), ss.describe()
+            ss.close()
+            ss = ProxADMMSolver(sprob, {}, ctx=ctx)
+            ss.iterate(args.warmup)
+            s_ms = ss.iterate(args.steps)
+            ss.close()
+            rows = [[t[k] for k in TRACE_KEYS] for t in ref["_trace"]]
+            ok, max_rel, why = compare_traces(strace, rows)
+            x_abs = float(np.abs(sx["x"] - ref["_x"]["x"]).max())
+            same_config = {
+                "workload": "sparse lasso %dx%d density %g fp64 (the reference arm's instance)" % (args.ref_m, args.ref_n, args.density),
+                "gpu_it_s": args.steps / (s_ms / 1e3), "gpu_e2e_it_s": sst["iterations_run"] / t_s,
+                "gpu_time_to_tol_s": t_s, "gpu_solver": sdesc.strip().split("\n")[1:2],
+                "ref_it_s": ref["value"], "ref_e2e_it_s": ref["e2e_value"], "ref_time_to_tol_s": ref["init_s"] + ref["loop_s"],
+                "num_iterations": [sst["num_iterations"], ref["num_iterations"]],
+                "parity_vs_reference_run": {"ok": bool(ok and x_abs <= 1e-7), "max_rel": max_rel, "x_max_abs": x_abs,
+                                            "mismatch": why},
+            }
         except Exception as e:  # the oracle binary is test infrastructure; report its absence
             cpu_baseline = {"value": None, "unit": "iterations/s", "cores": 1, "kind": "reference",
                             "sample": "unavailable: %s" % e}
@@ -364,11 +452,18 @@ def main_ours(args):
                        "cg_iterations_per_step": cg_iters / max(args.steps, 1),
                        "l2": "inputs larger than L2 (matrix %.2f GB per GPU, streamed every CG step)"
                              % (24 * nnz_local / 1e9),
-                       "parallelism": "rows of A sharded over %d GPU(s); n-vectors replicated; "
-                                      "NCCL all-reduce of A'q per CG step" % world,
+                       "parallelism": ("rows of A sharded over %d GPU(s); n-vectors replicated; " % world) + (
+                           "single GPU, no exchange" if world == 1 else
+                           "sum of A_r'(A_r p) per CG step by the two-shot NVLink peer exchange fused into "
+                           "CgFusedTailKernel (CUDA-IPC buffers, flag-in-data packets)" if "peer-allreduce" in desc
+                           else "sum of A_r'(A_r p) per CG step by ncclAllReduce"),
+                       "cg_steps_per_s": cg_iters / (ms / 1e3),
+                       "note": "value covers iterations W..W+K of a cold solve (CG steps per iteration vary: "
+                               "cg_iterations_per_step); cg_steps_per_s is the steps-independent rate",
                        "solver": desc.strip().split("\n")},
             "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),
             "roofline": roofline, "cpu_baseline": cpu_baseline,
+            "parity_check": parity, "vs_reference_same_config": same_config,
             "data_generation_s": t_gen,
         }
         print(json.dumps(line))
@@ -376,6 +471,9 @@ def main_ours(args):
     ctx.close()
     if world > 1:
         dist.destroy_process_group()
+    if parity and parity.get("ok") is False:
+        sys.stderr.write("bench.py: PARITY CHECK FAILED: %s\n" % json.dumps(parity))
+        sys.exit(3)
 
 
 def _only_json_on_stdout():

@@ -90,6 +90,7 @@ SIGNATURES = {
     "eps_map_scalar": (C.c_int, [_P, C.c_int, C.c_double, C.POINTER(_P)]),
     "eps_map_kronecker": (C.c_int, [_P, _P, _P, C.POINTER(_P)]),
     "eps_map_transpose": (C.c_int, [_P, C.POINTER(_P)]),
+    "eps_map_inverse": (C.c_int, [_P, C.POINTER(_P)]),
     "eps_map_dims": (C.c_int, [_P, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "eps_map_apply": (C.c_int, [_P, _DP, _DP]),
     "eps_map_apply_dev": (C.c_int, [_P, _P, _P]),
@@ -111,6 +112,7 @@ SIGNATURES = {
     "eps_solver_create": (C.c_int, [_P, C.POINTER(Params), C.POINTER(_P)]),
     "eps_solver_destroy": (None, [_P]),
     "eps_solver_solve": (C.c_int, [_P, C.POINTER(Status), TRACE_FN, _P]),
+    "eps_solver_set_constant": (C.c_int, [_P, C.c_int, C.c_int, _DP]),
     "eps_solver_iterate": (C.c_int, [_P, C.c_int, C.POINTER(C.c_float)]),
     "eps_solver_residuals": (C.c_int, [_P, C.POINTER(Status)]),
     "eps_solver_get_variable": (C.c_int, [_P, C.c_char_p, _DP]),

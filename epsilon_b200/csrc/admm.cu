@@ -399,6 +399,14 @@ int eps_solver_residuals(eps_solver* s, eps_status* out) {
   EPS_API_END
 }
 
+int eps_solver_set_constant(eps_solver* s, int prox_index, int arg_or_constraint_index, const double* values) {
+  EPS_API_BEGIN
+  EPS_CHECK(s, "null solver");
+  CUDA_CHECK(cudaSetDevice(s->ctx->device));
+  s->SetConstant(prox_index, arg_or_constraint_index, values);
+  EPS_API_END
+}
+
 int eps_solver_get_variable(eps_solver* s, const char* var_id, double* out) {
   EPS_API_BEGIN
   EPS_CHECK(s && var_id && out, "eps_solver_get_variable arguments");

@@ -28,6 +28,12 @@ struct ProxOp {
   int64_t rows_h = 0;
   double vec_bg = 0, vec_cinv = 0;
   int64_t g_off = -1;           // g in the constant arena
+  // eps_solver_set_constant: rows of each argument inside the stacked g, the current g (host), and the
+  // per-part scaling the operator applies to g when it stores it (SECOND_ORDER_CONE divides by at / ax)
+  std::vector<int64_t> arg_off;
+  std::vector<double> g_host;
+  double g_div0 = 1.0, g_div1 = 1.0;
+  int64_t g_split = 0;
   VecOpDesc vdesc;
   VecOpWork vwork;
   DevBuf<double> vbuf, vtmp;    // stacked argument (rows_h), A'w (n)
@@ -65,6 +71,10 @@ struct eps_solver {
   double b_norm = 0;
   eps::DevBuf<double> u, b, x, consts, ybuf[2], tmp_m, diff_m, tmp_n, rhs_n, resid;
   double* h_resid = nullptr;  // pinned
+  std::vector<double> b_host;               // constant terms of the constraints (eps_solver_set_constant)
+  std::vector<double> consts_host;          // the constant arena as uploaded
+  std::vector<int64_t> constraint_off;      // first row of every constraint in u-space
+  std::vector<double> tb_hb_host;           // two-block: constants of the user's constraints
   int parity = 0;             // ybuf[parity] holds the current y
   int iter = 0;               // next iteration index (iter_ of the reference)
   bool started = false;
@@ -94,4 +104,8 @@ struct eps_solver {
   void RunIteration();       // graph replay when available
   void ComputeResiduals();
   void ResetVariables();
+  // Solver::SetParameterValue for constant vectors (solver.cc:109-116): a new constant term of
+  // constraint `index` (prox < 0) or of argument `index` of prox function `prox`
+  void SetConstant(int prox, int index, const double* values);
+  void InvalidateGraphs();
 };

@@ -145,7 +145,8 @@ void eps_solver::Init(const eps_problem& original) {
   std::vector<int64_t> coff(p.constraints.size() + 1, 0);
   for (size_t c = 0; c < p.constraints.size(); c++) coff[c + 1] = coff[c] + p.constraints[c].rows;
   m_total = coff.back();
-  std::vector<double> b_host(m_total, 0.0);
+  constraint_off = coff;
+  b_host.assign(m_total, 0.0);
   std::vector<char> var_in_constraint(vars.size(), 0);
   for (size_t c = 0; c < p.constraints.size(); c++) {
     std::vector<double> bc;
@@ -182,7 +183,6 @@ void eps_solver::Init(const eps_problem& original) {
   ops.resize(N);
   var_x_off.assign(vars.size(), -1);
   int64_t x_total = 0, y_total = 0, max_n = 1;
-  std::vector<double> consts_host;
   std::vector<std::vector<double>> g_hosts(N);
   std::vector<BlockOp> Hs(N);
   std::vector<int64_t> rows_h(N, 0);
@@ -216,6 +216,7 @@ void eps_solver::Init(const eps_problem& original) {
     bool any_g = false;
     int64_t hoff = 0;
     for (const AffineExpr& a : f.args) {
+      op.arg_off.push_back(hoff);
       std::vector<double> ga;
       any_g = EvalConstants(ctx, a, &ga) || any_g;
       g.insert(g.end(), ga.begin(), ga.end());
@@ -224,6 +225,8 @@ void eps_solver::Init(const eps_problem& original) {
       if (a.global_rows > 0 && ctx->n_ranks > 1) h_sharded[i] = 1;
       hoff += a.rows;
     }
+    op.arg_off.push_back(hoff);
+    op.g_host = g;                 // zeros when no argument carries a constant
     if (!any_g) g.clear();
     rows_h[i] = hoff;
     H.rows = hoff;
@@ -295,6 +298,7 @@ void eps_solver::Init(const eps_problem& original) {
         op.g_off = (int64_t)consts_host.size();
         for (int64_t j = 0; j < op.rows_h; j++) consts_host.push_back(g_hosts[i][j] / (j < m ? at : ax));
       }
+      op.g_div0 = at; op.g_div1 = ax; op.g_split = m;
       op.vbuf.alloc(ctx, op.rows_h);
       op.vtmp.alloc(ctx, op.n);
       VecOpInit(ctx, d, &op.vwork);
@@ -594,6 +598,8 @@ void eps_solver::InitTwoBlock(const eps_problem& p) {
   zbuf[0].alloc(ctx, na); zbuf[1].alloc(ctx, na); ub.alloc(ctx, na); zeros.alloc(ctx, na);
   v_tmp.alloc(ctx, na); hb.alloc(ctx, mc); r_m.alloc(ctx, mc); y_m.alloc(ctx, mc); cmask.alloc(ctx, na);
   zeros.zero();
+  constraint_off = coff;       // eps_solver_set_constant addresses the user's constraints
+  tb_hb_host = hb_host;
   hb.upload(hb_host.data(), m_c);
   cmask.upload(mask_host.data(), n_all);
   CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
@@ -639,6 +645,75 @@ void eps_solver::ResetVariables() {
   parity = 0;
   iter = 0;
   started = false;
+  CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+}
+
+void eps_solver::InvalidateGraphs() {
+  for (int i = 0; i < 2; i++) {
+    if (graph_exec[i]) cudaGraphExecDestroy(graph_exec[i]);
+    graph_exec[i] = nullptr;
+    eager_done[i] = 0;
+  }
+}
+
+// Solver::SetParameterValue (solver.cc:109-116) for constant vectors.  The reference rewrites the Constant
+// inside its Problem proto and re-runs InitConstraints / InitProxOperators on the next Solve()
+// (prox_admm.cc:110-120), i.e. it re-reads b_ and every g_i and refactorises although no matrix changed;
+// here only what depends on the constant is refreshed: b (and ||b||), the g of an elementwise / vector
+// operator, or c0 = -2a H'g - c of a KKT operator.  Factors, SELL streams and the iterate stay.
+void eps_solver::SetConstant(int prox, int index, const double* values) {
+  EPS_CHECK(values, "null constant");
+  CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+  if (prox < 0) {
+    EPS_CHECK(index >= 0 && index + 1 < (int)constraint_off.size(), "constraint %d of %d", index,
+              (int)constraint_off.size() - 1);
+    const int64_t lo = constraint_off[index], len = constraint_off[index + 1] - lo;
+    if (two_block) {
+      std::copy(values, values + len, tb_hb_host.begin() + lo);
+      if (len) UploadBytes(ctx, hb.p + lo, tb_hb_host.data() + lo, len * sizeof(double));
+    } else {
+      std::copy(values, values + len, b_host.begin() + lo);
+      if (len) UploadBytes(ctx, b.p + lo, b_host.data() + lo, len * sizeof(double));
+      if (!has_b) { has_b = true; InvalidateGraphs(); }   // the captured iteration skipped "u -= b"
+      b_norm = 0;
+      for (double v : b_host) b_norm += v * v;
+      b_norm = std::sqrt(b_norm);
+    }
+    CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+    return;
+  }
+  EPS_CHECK(prox < N, "prox function %d of %d", prox, N);
+  ProxOp& op = ops[prox];
+  EPS_CHECK(index >= 0 && index + 1 < (int)op.arg_off.size(), "argument %d of prox function %d", index, prox);
+  const int64_t lo = op.arg_off[index], len = op.arg_off[index + 1] - lo;
+  std::copy(values, values + len, op.g_host.begin() + lo);
+  if (op.kkt) {
+    // AFFINE / CONSTANT: only the linear part of the argument enters (affine.cc:26-28)
+    if (op.type == EPS_PROX_SUM_SQUARE) op.kkt->SetConstant(op.g_host);
+    return;
+  }
+  const bool vec = op.rows_h > 0;   // ST_VEC keeps its offset in the operator, the others in the segment
+  int64_t& goff = vec ? op.g_off : op.seg.g_off;
+  const int64_t rows = (int64_t)op.g_host.size();
+  if (goff < 0) {
+    // the operator was built without a constant: give it a slot in the arena
+    goff = (int64_t)consts_host.size();
+    consts_host.resize(consts_host.size() + rows, 0.0);
+    consts.alloc(ctx, consts_host.size());
+    consts.upload(consts_host.data(), consts_host.size());
+    InvalidateGraphs();
+    for (auto& stp : stages) {
+      Stage& st = *stp;
+      for (size_t k = 0; k < st.members.size(); k++)
+        if (st.members[k] == prox && st.segs.n > k)
+          UploadBytes(ctx, st.segs.p + k, &op.seg, sizeof(ElemSeg));
+    }
+  }
+  for (int64_t j = 0; j < rows; j++) {
+    const double div = op.type == EPS_PROX_SECOND_ORDER_CONE ? (j < op.g_split ? op.g_div0 : op.g_div1) : 1.0;
+    consts_host[goff + j] = op.g_host[j] / div;
+  }
+  UploadBytes(ctx, consts.p + goff, consts_host.data() + goff, rows * sizeof(double));
   CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
 }
 

@@ -388,6 +388,30 @@ KktSolver::~KktSolver() {
   if (ring) cudaFreeHost(ring);
 }
 
+// c0 = -2a H'g - c
+void KktSolver::ComputeC0(const std::vector<double>& g_host) {
+  if (!c0.p) c0.alloc(ctx, n);
+  c0.zero();
+  if (alpha2 != 0.0 && !g_host.empty() && rows_h > 0) {
+    EPS_CHECK((int64_t)g_host.size() == rows_h, "constant of the argument has %zu entries, expected %lld", g_host.size(),
+              (long long)rows_h);
+    DevBuf<double> g(ctx, rows_h);
+    g.upload(g_host.data(), rows_h);
+    H.ApplyT(g.p, c0.p);
+    if (h_sharded) AllReduceSum(ctx, c0.p, n);
+    VecScale(ctx, n, -alpha2, c0.p, c0.p);
+    CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+  }
+  if (!c_host_.empty()) {
+    DevBuf<double> c(ctx, n);
+    c.upload(c_host_.data(), n);
+    VecAxpby(ctx, n, 1.0, c0.p, -1.0, c.p, c0.p);
+    CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+  }
+}
+
+void KktSolver::SetConstant(const std::vector<double>& g_host) { ComputeC0(g_host); }
+
 void KktSolver::Init(const std::vector<double>& g_host, const std::vector<double>& c_host) {
   EPS_CHECK(n > 0, "KKT prox without variables");
   H.Compile();
@@ -401,24 +425,8 @@ void KktSolver::Init(const std::vector<double>& g_host, const std::vector<double
   scal.zero();
   CUDA_CHECK(cudaMallocHost(&h_scal, 8 * sizeof(double)));
 
-  // c0 = -2a H'g - c
-  c0.alloc(ctx, n);
-  c0.zero();
-  if (alpha2 != 0.0 && !g_host.empty() && rows_h > 0) {
-    DevBuf<double> g(ctx, rows_h);
-    g.upload(g_host.data(), rows_h);
-    H.ApplyT(g.p, c0.p);
-    if (h_sharded) AllReduceSum(ctx, c0.p, n);
-    VecScale(ctx, n, -alpha2, c0.p, c0.p);
-    CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
-  }
-  if (!c_host.empty()) {
-    DevBuf<double> c(ctx, n);
-    c.upload(c_host.data(), n);
-    VecAxpby(ctx, n, 1.0, c0.p, -1.0, c.p, c0.p);
-    CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
-  }
-
+  c_host_ = c_host;
+  ComputeC0(g_host);
   // ---- Kronecker structure: k identical diagonal blocks ----
   if (alpha2 != 0.0 && H.blks.size() == 1 && H.blks[0].map->kind == MK_KRONECKER && !H.blks[0].trans &&
       H.blks[0].map->ka->kind == MK_SCALAR && !h_sharded && H.blks[0].row_off == 0 && H.blks[0].col_off == 0 &&

@@ -58,6 +58,10 @@ struct KktSolver {
   ~KktSolver();
   // g: rows_h constants of the argument (may be empty = 0); c: n linear term (may be null)
   void Init(const std::vector<double>& g_host, const std::vector<double>& c_host);
+  // c0 = -2a H'g - c for a new constant g of the argument (eps_solver_set_constant); the factors stay
+  void SetConstant(const std::vector<double>& g_host);
+  void ComputeC0(const std::vector<double>& g_host);
+  std::vector<double> c_host_;   // linear term kept for SetConstant
   // x <- solution for rhs (both device, n).  x holds the warm start on entry (CG).
   void Solve(const double* rhs, double* x);
   void MatVec(const double* p, double* w, const int* skip = nullptr);  // w = (2a H'H + A'A) p

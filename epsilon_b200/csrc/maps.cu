@@ -613,6 +613,110 @@ int eps_map_transpose(eps_map* map, eps_map** out) {
   EPS_API_END
 }
 
+// LinearMapImpl::Inverse() (linear_map.h:49).  What the reference does per type:
+//   scalar    1/alpha                                    scalar_matrix_impl.h:29-31
+//   diagonal  1/d_i, 0 where d_i == 0                    diagonal_matrix_impl.cc:15-23
+//   Kronecker inv(A) (x) inv(B)                          kronecker_product_impl.h:37-39
+//   dense     Eigen::LDLT of the (assumed symmetric) matrix, solve(Identity)   dense_matrix_impl.cc:21-30
+//   sparse    scalar matrix -> scalar inverse, else densify and as dense       sparse_matrix_impl.cc:60-78
+// Every dense matrix the solver inverts (BlockCholesky pivots, block_cholesky.cc:125) is symmetric
+// definite (+ or -), so the device factorises M or -M by Cholesky, inv = W'W with W = inv(chol)
+// (DMMA Gram kernel); an indefinite matrix is refused with EPS_ERR_NUMERIC.
+static std::shared_ptr<MapData> InverseOf(Ctx* ctx, const MapData& A, bool trans) {
+  EPS_CHECK(A.m == A.n || A.kind == MK_KRONECKER, "inverse of a %d x %d map", A.m, A.n);
+  auto d = std::make_shared<MapData>();
+  d->ctx = ctx; d->m = A.n; d->n = A.m;
+  switch (A.kind) {
+    case MK_SCALAR:
+      d->kind = MK_SCALAR;
+      d->alpha = 1 / A.alpha;
+      return d;
+    case MK_DIAGONAL: {
+      d->kind = MK_DIAGONAL;
+      d->h_diag.resize(A.n);
+      for (int i = 0; i < A.n; i++) d->h_diag[i] = A.h_diag[i] != 0.0 ? 1 / A.h_diag[i] : 0.0;
+      d->diag.alloc(ctx, A.n);
+      d->diag.upload(d->h_diag.data(), A.n);
+      CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+      return d;
+    }
+    case MK_KRONECKER:
+      d->kind = MK_KRONECKER;
+      d->ka = InverseOf(ctx, *A.ka, A.ka_trans != trans);
+      d->kb = InverseOf(ctx, *A.kb, A.kb_trans != trans);
+      d->m = d->ka->m * d->kb->m;
+      d->n = d->ka->n * d->kb->n;
+      return d;
+    case MK_SPARSE:
+      if (A.has_host) {  // IsScalarMatrix (sparse_matrix_impl.cc:66-71)
+        bool scalar = A.h_colptr[A.n] == A.n && A.n > 0;
+        for (int j = 0; scalar && j < A.n; j++)
+          scalar = A.h_colptr[j] == j && A.h_rowidx[j] == j && A.h_vals[j] == A.h_vals[0];
+        if (scalar) {
+          d->kind = MK_SCALAR;
+          d->alpha = 1 / A.h_vals[0];
+          return d;
+        }
+      }
+      // fall through: densify
+    case MK_DENSE: {
+      const int n = A.n;
+      EPS_CHECK(n <= 60000, "dense inverse of a %d x %d map does not fit", n, n);
+      DevBuf<double> M(ctx, (size_t)n * n), W(ctx, (size_t)n * n);
+      auto load = [&](double sign) {
+        if (A.kind == MK_DENSE) {
+          VecScale(ctx, (int64_t)n * n, sign, A.dense.p, M.p);
+        } else {
+          M.zero();
+          CsrDensify(ctx, A.csr, sign, M.p, n, 0, 0, trans);
+        }
+      };
+      double sign = 1.0;
+      load(1.0);
+      try {
+        DenseCholInverseFactor(ctx, M.p, n, n, W.p);
+      } catch (const Error& e) {
+        if (e.code != EPS_ERR_NUMERIC) throw;
+        sign = -1.0;
+        load(-1.0);
+        try {
+          DenseCholInverseFactor(ctx, M.p, n, n, W.p);
+        } catch (const Error& e2) {
+          if (e2.code != EPS_ERR_NUMERIC) throw;
+          throw Error(EPS_ERR_NUMERIC, Format("eps_map_inverse: the %d x %d matrix is neither positive nor negative "
+                                              "definite (the reference's LDLT would accept it; the device path "
+                                              "factorises by Cholesky)", n, n));
+        }
+      }
+      d->kind = MK_DENSE;
+      d->dense.alloc(ctx, (size_t)n * n);
+      DenseGramTN(ctx, W.p, n, n, n, sign, d->dense.p, n, false);   // inv(M) = sign * W'W
+      CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+      return d;
+    }
+    default:
+      throw Error(EPS_ERR_INVALID, "unknown map kind");
+  }
+}
+
+int eps_map_inverse(eps_map* map, eps_map** out) {
+  EPS_API_BEGIN
+  EPS_CHECK(map && out, "eps_map_inverse arguments");
+  Ctx* ctx = map->d->ctx;
+  CUDA_CHECK(cudaSetDevice(ctx->device));
+  auto* h = new eps_map();
+  try {
+    h->d = InverseOf(ctx, *map->d, map->trans);
+  } catch (...) {
+    delete h;
+    throw;
+  }
+  // the inverse of a symmetric matrix is symmetric; a Kronecker inverse was built for op(map) already
+  h->trans = false;
+  *out = h;
+  EPS_API_END
+}
+
 int eps_map_dims(const eps_map* map, int* m, int* n) {
   EPS_API_BEGIN
   EPS_CHECK(map, "null map");

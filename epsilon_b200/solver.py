@@ -125,6 +125,14 @@ class LinearMap:
         t._keep = [self]
         return t
 
+    def inverse(self) -> "LinearMap":
+        """LinearMapImpl::Inverse() (linear_map.h:49)."""
+        h = C.c_void_p()
+        capi.check(self.lib.eps_map_inverse(self.handle, C.byref(h)))
+        t = LinearMap(self.ctx, _handle=h)
+        t._keep = [self]
+        return t
+
     def apply(self, x: np.ndarray) -> np.ndarray:
         m, n = self.shape
         x = np.ascontiguousarray(x, dtype=np.float64).ravel()
@@ -280,6 +288,12 @@ class ProxADMMSolver:
         cb = capi.TRACE_FN(_cb)
         capi.check(self.lib.eps_solver_solve(self.handle, C.byref(self.status), cb, None))
         return self.solution()
+
+    def set_constant(self, prox_index: int, index: int, values: np.ndarray) -> None:
+        """Solver::SetParameterValue for a constant vector (solver.cc:109-116): the constant term of
+        constraint `index` (prox_index < 0) or of argument `index` of prox function `prox_index`."""
+        v = np.ascontiguousarray(values, dtype=np.float64).ravel()
+        capi.check(self.lib.eps_solver_set_constant(self.handle, prox_index, index, capi.dptr(v)))
 
     def iterate(self, iterations: int) -> float:
         """Exactly `iterations` more ADMM iterations, no stop test; CUDA-event milliseconds."""

@@ -131,6 +131,12 @@ int eps_map_scalar(eps_ctx* ctx, int n, double alpha, eps_map** out);
 int eps_map_kronecker(eps_ctx* ctx, eps_map* a, eps_map* b, eps_map** out);
 /* LinearMapImpl::Transpose(): a new map sharing storage (dense_matrix_impl.h:41-43). */
 int eps_map_transpose(eps_map* map, eps_map** out);
+/* LinearMapImpl::Inverse() (linear_map.h:49): scalar 1/alpha (scalar_matrix_impl.h:29-31), diagonal with
+ * 0 kept 0 (diagonal_matrix_impl.cc:15-23), Kronecker inv(A) (x) inv(B) (kronecker_product_impl.h:37-39),
+ * dense symmetric matrix as an explicit dense inverse (dense_matrix_impl.cc:21-30), sparse by way of
+ * dense (sparse_matrix_impl.cc:60-78).  The dense factorisation is a Cholesky of M or -M on the device:
+ * EPS_ERR_NUMERIC for an indefinite matrix. */
+int eps_map_inverse(eps_map* map, eps_map** out);
 int eps_map_dims(const eps_map* map, int* m, int* n);
 /* LinearMapImpl::Apply(x) (linear_map.h:52): y = map * x; x has n, y has m entries. */
 int eps_map_apply(eps_map* map, const double* x, double* y);
@@ -228,6 +234,16 @@ void eps_solver_destroy(eps_solver* s);
 /* ProxADMMSolver::Solve() loop (prox_admm.cc:131-169) incl. ComputeResiduals
  * (:178-217) every epoch_iterations; fills `status`. */
 int eps_solver_solve(eps_solver* s, eps_status* status, eps_trace_fn trace, void* user);
+/* Solver::SetParameterValue (src/epsilon/algorithms/solver.cc:38-61,109-116; called for every
+ * parameter on every solve, python/epopt/solvemodule.cc:89-106,156) for constant VECTORS: replaces the
+ * constant term of constraint `arg_or_constraint_index` (prox_index < 0; that many rows) or of argument
+ * `arg_or_constraint_index` of prox function `prox_index` (the sum of the CONSTANT nodes of that affine
+ * expression, as affine::BuildAffineOperator leaves it in b(row_key), affine.cc:51-69).  With
+ * params.warm_start the next eps_solver_solve continues from the current iterate, which is the
+ * warm-start path of solvemodule.cc:142-151 / prox_admm.cc:115-120 without the reference's
+ * refactorisation.  A parameter inside a MATRIX needs a new solver (eps_solver_create). */
+int eps_solver_set_constant(eps_solver* s, int prox_index, int arg_or_constraint_index,
+                            const double* values);
 /* Run exactly `iterations` more ADMM iterations without stop test (benchmarking);
  * `elapsed_ms` = CUDA-event time on the context stream. */
 int eps_solver_iterate(eps_solver* s, int iterations, float* elapsed_ms);
