@@ -131,6 +131,9 @@ class Term:
     operand: Union[Variable, np.ndarray]
     map: Optional[LinearMapSpec] = None
     name: str = ""  # data_location stem when operand is a constant
+    # Constant.parameter_id (proto/epsilon/expression.proto:22): a cvxpy Parameter, replaceable on a live
+    # solver through Solver::SetParameterValue (solver.cc:109-116) / eps_solver_set_constant
+    parameter_id: str = ""
 
 
 @dataclass

@@ -35,13 +35,18 @@ class _RefWriter:
     def size(self, m: int, n: int = 1) -> str:
         return "size { dim: %d dim: %d }" % (m, n)
 
-    def dense_constant(self, a: np.ndarray, stem: str) -> str:
+    def dense_constant_body(self, a: np.ndarray, stem: str, parameter_id: str = "") -> str:
         a = np.asarray(a, dtype=np.float64)
         if a.ndim == 1:
             a = a.reshape(-1, 1)
         loc = self.store(stem, a.tobytes(order="F"))
-        return 'constant { constant_type: DENSE_MATRIX m: %d n: %d data_location: "%s" }' % (
-            a.shape[0], a.shape[1], loc)
+        body = 'constant_type: DENSE_MATRIX m: %d n: %d data_location: "%s"' % (a.shape[0], a.shape[1], loc)
+        if parameter_id:
+            body += ' parameter_id: "%s"' % parameter_id
+        return body
+
+    def dense_constant(self, a: np.ndarray, stem: str, parameter_id: str = "") -> str:
+        return "constant { %s }" % self.dense_constant_body(a, stem, parameter_id)
 
     def sparse_constant(self, a: sp.csc_matrix, stem: str) -> str:
         payload = (a.indptr.astype(np.int32).tobytes() + a.indices.astype(np.int32).tobytes()
@@ -74,7 +79,7 @@ class _RefWriter:
         else:
             c = np.asarray(t.operand, dtype=np.float64).ravel()
             leaf = "expression_type: CONSTANT %s %s" % (
-                self.size(c.size), self.dense_constant(c, t.name or "const"))
+                self.size(c.size), self.dense_constant(c, t.name or "const", getattr(t, "parameter_id", "")))
         if t.map is None:
             return leaf
         return "expression_type: LINEAR_MAP %s linear_map { %s } arg { %s }" % (
@@ -113,10 +118,18 @@ class _RefWriter:
 
 
 def write_reference_problem(problem: ProxAffineProblem, out_dir: str,
-                            params: Optional[dict] = None) -> None:
-    """Write <out_dir>/problem.pbtxt, params.pbtxt and data/ for oracle/_ref/epsilon_ref."""
+                            params: Optional[dict] = None,
+                            reparam: Optional[Dict[str, np.ndarray]] = None) -> None:
+    """Write <out_dir>/problem.pbtxt, params.pbtxt and data/ for oracle/_ref/epsilon_ref.
+    `reparam`: {parameter_id: new constant vector} applied by the harness' resolve modes through
+    Solver::SetParameterValue between two Solve() calls."""
     os.makedirs(out_dir, exist_ok=True)
     w = _RefWriter(os.path.join(out_dir, "data"))
+    if reparam:
+        os.makedirs(os.path.join(out_dir, "reparam"), exist_ok=True)
+        for pid, val in reparam.items():
+            with open(os.path.join(out_dir, "reparam", pid), "w") as f:
+                f.write(w.dense_constant_body(np.asarray(val, dtype=np.float64).ravel(), "param_" + pid, pid) + "\n")
     obj = "expression_type: ADD %s %s" % (
         w.size(1), " ".join("arg { %s }" % w.prox_function(f) for f in problem.prox))
     parts = ["objective { %s }" % obj]

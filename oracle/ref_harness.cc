@@ -13,9 +13,17 @@
 //           (prox_admm.h:66) and replays the statement sequence of
 //           prox_admm.cc:134-154 on the reference's own members; the harness
 //           cross-checks that the stepped run ends in the same status as
-//           `solve` (tests/test_oracle_ref.py).
+//           `solve` (tests/golden/make_golden.py: solve_case).
 //   prox  : single operator, the statement sequence of EvalProx
 //           (python/epopt/solvemodule.cc:189-242).
+//   resolve     : Solve(), then Solver::SetParameterValue (solver.cc:109-116) for every
+//                 <dir>/reparam/<parameter_id> (a text-format Constant) and Solve() again on the
+//                 same solver object -- the warm-start path of solvemodule.cc:142-156.
+//   gpu-solve, gpu-resolve : the same two flows through ProxADMMGpuSolver
+//                 (adapter/prox_admm_gpu.cc: the reference-side binding of libepsgpu.so), only in
+//                 the binary built with -DEPS_GPU_ADAPTER (oracle/_ref/epsilon_ref_gpu).  The DataMap
+//                 strings it uploads from are ordinary pageable std::string buffers, as in
+//                 solvemodule.cc:58-72.
 //
 // Directory protocol (all numbers little-endian, doubles as raw f64):
 //   <dir>/problem.pbtxt   Problem            (solve/trace)
@@ -46,6 +54,10 @@
 #include "epsilon/solver.pb.h"
 #include "epsilon/solver_params.pb.h"
 #include "epsilon/vector/vector_util.h"
+
+#ifdef EPS_GPU_ADAPTER
+#include "prox_admm_gpu.h"
+#endif
 
 namespace {
 
@@ -212,6 +224,76 @@ int RunSolve(const std::string& dir, bool trace, int dump_iter) {
   return 0;
 }
 
+void WriteTrace(const std::string& path, const std::vector<SolverStatus>& epochs) {
+  std::ofstream trace(path);
+  for (const SolverStatus& e : epochs) trace << StatusLine(e) << "\n";
+}
+
+// solve / resolve through the Solver interface only (solver.h:42-102), CPU or device class.
+int RunSolver(const std::string& dir, const std::string& mode) {
+  const bool gpu = mode.compare(0, 4, "gpu-") == 0;
+  const bool resolve = mode.find("resolve") != std::string::npos;
+  Problem problem;
+  CHECK(google::protobuf::TextFormat::ParseFromString(
+      ReadFile(dir + "/problem.pbtxt"), &problem));
+  SolverParams params;
+  std::string params_txt = ReadFile(dir + "/params.pbtxt", false);
+  if (!params_txt.empty())
+    CHECK(google::protobuf::TextFormat::ParseFromString(params_txt, &params));
+  if (resolve) params.set_warm_start(true);
+  double t0 = Now();
+  DataMap data = LoadData(dir);            // pageable std::string buffers (solvemodule.cc:58-72)
+  double t_load = Now() - t0;
+  std::string out = dir + "/out_" + mode;
+  MakeDir(out);
+
+  std::unique_ptr<Solver> solver;
+#ifdef EPS_GPU_ADAPTER
+  ProxADMMGpuSolver* dev = nullptr;
+  if (gpu) {
+    dev = new ProxADMMGpuSolver(problem, data, params);
+    solver.reset(dev);
+  }
+#else
+  CHECK(!gpu) << "this binary was built without the device adapter (make -C oracle gpu)";
+#endif
+  if (!solver) solver.reset(new ProxADMMSolver(problem, data, params));
+
+  t0 = Now();
+  BlockVector x = solver->Solve();
+  double t_first = Now() - t0;
+  std::string first = StatusLine(solver->status());
+#ifdef EPS_GPU_ADAPTER
+  if (dev) WriteTrace(out + "/trace_first.txt", dev->epochs());
+#endif
+  double t_second = 0;
+  if (resolve) {
+    MakeDir(out + "/x_first");
+    for (const std::string& key : x.keys()) WriteVector(out + "/x_first/" + key, x(key));
+    for (const std::string& id : ListDir(dir + "/reparam")) {
+      Constant c;
+      CHECK(google::protobuf::TextFormat::ParseFromString(ReadFile(dir + "/reparam/" + id), &c));
+      solver->SetParameterValue(id, c);
+    }
+    t0 = Now();
+    x = solver->Solve();
+    t_second = Now() - t0;
+  }
+#ifdef EPS_GPU_ADAPTER
+  if (dev) {
+    WriteTrace(out + "/trace.txt", dev->epochs());
+    WriteFile(out + "/describe.txt", dev->describe());
+  }
+#endif
+  char buf[1024];
+  snprintf(buf, sizeof(buf), "%s\nload_s %.6f\ntotal_s %.6f\nsecond_s %.6f\n",
+           StatusLine(solver->status()).c_str(), t_load, t_first, t_second);
+  WriteFile(out + "/status.txt", buf);
+  WriteFile(out + "/status_first.txt", first + "\n");
+  WriteSolution(out, x);
+  return 0;
+}
+
 // Statement sequence of EvalProx, python/epopt/solvemodule.cc:205-236.
 int RunProx(const std::string& dir) {
   Expression f_expr;
@@ -259,7 +341,7 @@ int RunProx(const std::string& dir) {
 int main(int argc, char** argv) {
   google::InitGoogleLogging(argv[0]);
   if (argc < 3) {
-    fprintf(stderr, "usage: %s solve|trace|prox <dir> [dump_iter]\n", argv[0]);
+    fprintf(stderr, "usage: %s solve|trace|prox|resolve|gpu-solve|gpu-resolve <dir> [dump_iter]\n", argv[0]);
     return 2;
   }
   std::string mode = argv[1];
@@ -268,6 +350,7 @@ int main(int argc, char** argv) {
   if (mode == "solve") return RunSolve(dir, false, -1);
   if (mode == "trace") return RunSolve(dir, true, dump_iter);
   if (mode == "prox") return RunProx(dir);
+  if (mode == "resolve" || mode == "gpu-solve" || mode == "gpu-resolve") return RunSolver(dir, mode);
   fprintf(stderr, "unknown mode %s\n", mode.c_str());
   return 2;
 }

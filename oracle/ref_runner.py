@@ -16,6 +16,8 @@ import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 BINARY = os.path.join(HERE, "_ref", "epsilon_ref")
+# the same harness with adapter/prox_admm_gpu.cc (the reference-side binding of libepsgpu.so) linked in
+BINARY_GPU = os.path.join(HERE, "_ref", "epsilon_ref_gpu")
 
 STATE_NAMES = {0: "NOT_STARTED", 1: "INITIALIZING", 2: "RUNNING", 3: "OPTIMAL",
                4: "MAX_ITERATIONS_REACHED", 5: "ERROR"}
@@ -23,6 +25,10 @@ STATE_NAMES = {0: "NOT_STARTED", 1: "INITIALIZING", 2: "RUNNING", 3: "OPTIMAL",
 
 def available() -> bool:
     return os.path.isfile(BINARY) and os.access(BINARY, os.X_OK)
+
+
+def gpu_adapter_available() -> bool:
+    return os.path.isfile(BINARY_GPU) and os.access(BINARY_GPU, os.X_OK)
 
 
 def _parse_status_line(line: str) -> dict:
@@ -40,15 +46,21 @@ def _read_vectors(path: str) -> Dict[str, np.ndarray]:
 
 
 def run(problem, params: Optional[dict] = None, mode: str = "trace", dump_iter: int = -1,
-        workdir: Optional[str] = None, timeout: float = 3600.0) -> dict:
-    """mode 'solve' = stock ProxADMMSolver::Solve(); 'trace' = stepped, per-epoch residuals."""
+        workdir: Optional[str] = None, timeout: float = 3600.0, reparam: Optional[dict] = None,
+        env_extra: Optional[dict] = None) -> dict:
+    """mode 'solve' = stock ProxADMMSolver::Solve(); 'trace' = stepped, per-epoch residuals;
+    'resolve' = Solve, SetParameterValue(reparam), Solve again (warm start); 'gpu-solve' / 'gpu-resolve' =
+    the same flows through ProxADMMGpuSolver (adapter/prox_admm_gpu.cc over libepsgpu.so)."""
     from oracle.ref_format import write_reference_problem
-    assert available(), "oracle/_ref/epsilon_ref missing: run `make -C oracle`"
+    gpu = mode.startswith("gpu-")
+    binary = BINARY_GPU if gpu else BINARY
+    assert os.path.isfile(binary), "%s missing: run `make -C oracle%s`" % (binary, " gpu" if gpu else "")
     tmp = workdir or tempfile.mkdtemp(prefix="epsref_")
     try:
-        write_reference_problem(problem, tmp, params)
-        cmd = [BINARY, mode, tmp] + ([str(dump_iter)] if mode == "trace" else [])
+        write_reference_problem(problem, tmp, params, reparam)
+        cmd = [binary, mode, tmp] + ([str(dump_iter)] if mode == "trace" else [])
         env = dict(os.environ, OMP_NUM_THREADS="1")
+        env.update(env_extra or {})
         subprocess.run(cmd, check=True, timeout=timeout, env=env)
         out = os.path.join(tmp, "out_" + mode)
         lines = open(os.path.join(out, "status.txt")).read().splitlines()
@@ -60,6 +72,17 @@ def run(problem, params: Optional[dict] = None, mode: str = "trace", dump_iter: 
         if os.path.exists(tr):
             res["trace"] = [_parse_status_line(l) for l in open(tr).read().splitlines() if l.strip()]
         res["x"] = _read_vectors(os.path.join(out, "x"))
+        for extra in ("trace_first", ):
+            trf = os.path.join(out, extra + ".txt")
+            if os.path.exists(trf):
+                res[extra] = [_parse_status_line(l) for l in open(trf).read().splitlines() if l.strip()]
+        sf = os.path.join(out, "status_first.txt")
+        if os.path.exists(sf):
+            res["status_first"] = _parse_status_line(open(sf).read().splitlines()[0])
+            res["x_first"] = _read_vectors(os.path.join(out, "x_first"))
+        df = os.path.join(out, "describe.txt")
+        if os.path.exists(df):
+            res["describe"] = open(df).read()
         if dump_iter >= 0:
             res["apply"] = {}
             for name in sorted(os.listdir(out)):

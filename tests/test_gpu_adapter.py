@@ -1,0 +1,110 @@
+"""The drop-in boundary through the REFERENCE's own C++ classes: adapter/prox_admm_gpu.cc (a `Solver` subclass,
+src/epsilon/algorithms/solver.h:42-102, that walks the reference's AffineOperators and calls the C ABI of
+include/epsgpu.h) compiled against /root/reference and linked with libepsgpu.so into
+oracle/_ref/epsilon_ref_gpu.  One harness (oracle/ref_harness.cc) runs the same problem.pbtxt + DataMap bytes
+through the stock ProxADMMSolver and through ProxADMMGpuSolver; uploads start from ordinary pageable
+std::string buffers, as in python/epopt/solvemodule.cc:58-72.
+
+Checked: per-epoch traces, iteration counts and solutions equal the reference fixtures (tests/golden) and the
+stock solver run live; Solver::SetParameterValue + warm start (solver.cc:109-116, solvemodule.cc:142-156)
+gives the same second solve as the stock solver."""
+import json
+import os
+import sys
+
+import numpy as np
+import pytest
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+GOLDEN = os.path.join(HERE, "golden")
+sys.path.insert(0, GOLDEN)
+
+import make_golden  # noqa: E402
+from epsilon_b200 import problems  # noqa: E402
+from oracle import ref_runner  # noqa: E402
+
+pytestmark = pytest.mark.gpu
+
+INDEX = json.load(open(os.path.join(GOLDEN, "index.json")))
+TRACE_KEYS = make_golden.TRACE_KEYS
+RES = TRACE_KEYS[2:]
+
+
+@pytest.fixture(scope="module")
+def adapter():
+    if not ref_runner.gpu_adapter_available():
+        pytest.skip("oracle/_ref/epsilon_ref_gpu not built (make -C oracle gpu; needs /root/reference)")
+    return ref_runner
+
+
+CASES = ["lasso_dense_100x500", "lasso_sparse_4000x400", "lasso_sparse_120000x4000", "logreg_l1_2000x200",
+         "hinge_l2_sparse_5000x300", "group_lasso_400x10x12", "tv_1d_5000", "mv_lasso_40x100x3",
+         "l1_epigraph_denoise_300", "covsel_12"]
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_adapter_matches_reference_golden(adapter, name):
+    prob, info, params = make_golden.make_problem(name)
+    if make_golden.problem_digest(prob) != INDEX["solve"][name]["digest"]:
+        pytest.skip("generator drift on this host: fixture inputs differ")
+    gold = np.load(os.path.join(GOLDEN, name + ".npz"))
+    r = adapter.run(prob, params=params, mode="gpu-solve")
+    assert "ProxADMM" in r["describe"]
+    trace = r["trace"]
+    assert len(trace) == gold["trace"].shape[0], r["describe"]
+    for t, g in zip(trace, gold["trace"]):
+        gd = dict(zip(TRACE_KEYS, g))
+        assert t["num_iterations"] == int(gd["num_iterations"]) and t["state"] == int(gd["state"]), (t, gd)
+        for k in RES:
+            assert t[k] == pytest.approx(gd[k], rel=1e-7, abs=1e-12), (k, t, gd, r["describe"])
+    gst = dict(zip(TRACE_KEYS, gold["status"]))
+    assert r["status"]["num_iterations"] == int(gst["num_iterations"])
+    assert r["status"]["state"] == int(gst["state"])
+    v = INDEX["solve"][name]["solution_var"]
+    assert np.abs(r["x"][v] - gold["x"]).max() <= 1e-7 * max(1.0, np.abs(gold["x"]).max())
+    assert info["objective"](r["x"]) == pytest.approx(float(gold["objective"]), rel=1e-6)
+    # GetSolution returns every variable of the compiled problem (solvemodule.cc:166-176)
+    assert sorted(r["x"]) == sorted(prob.variables())
+
+
+def _with_parameter(prob, prox, arg, term, pid):
+    prob.prox[prox].args[arg].terms[term].parameter_id = pid
+    return prob
+
+
+@pytest.mark.parametrize("kind", ["lasso_dense", "lasso_sparse_cg", "tv_1d", "hinge_constraint"])
+def test_set_parameter_value_and_warm_start_match_the_stock_solver(adapter, ref, kind):
+    """Solve, SetParameterValue, Solve again with warm_start -- through Solver's own interface, on the
+    stock ProxADMMSolver (CPU) and on ProxADMMGpuSolver (device); first and second solves must agree."""
+    rng = np.random.default_rng(11)
+    env = {}
+    if kind == "lasso_dense":
+        prob, info = problems.lasso(100, 500)
+        _with_parameter(prob, 0, 0, 1, "b")
+        new = {"b": info["b"] + 0.2 * rng.standard_normal(100)}
+    elif kind == "lasso_sparse_cg":
+        prob, info = problems.lasso(4000, 400, density=0.02, seed=3)
+        _with_parameter(prob, 0, 0, 1, "b")
+        new = {"b": info["b"] + 0.2 * rng.standard_normal(4000)}
+        env = {"EPSILON_GPU_KKT_MODE": "4", "EPS_SPARSE_FORMAT": "sell"}   # matrix-free, the headline kernels
+    elif kind == "tv_1d":
+        prob, info = problems.tv_1d(5000, seed=7)
+        _with_parameter(prob, 0, 0, 1, "b")
+        new = {"b": info["b"] + 0.5 * rng.standard_normal(5000)}
+    else:
+        prob, info = problems.hinge_l2(1500, 100, seed=5)
+        prob.constraints[0].terms[0].parameter_id = "margin"      # the constant 1 of  1 - DA x - t = 0
+        new = {"margin": 1.0 + 0.3 * rng.random(1500)}
+    params = {"max_iterations": 300}
+    cpu = ref.run(prob, params=params, mode="resolve", reparam=new)
+    dev = adapter.run(prob, params=params, mode="gpu-resolve", reparam=new, env_extra=env)
+    for which in ("status_first", "status"):
+        a, b = dev[which], cpu[which]
+        assert a["num_iterations"] == b["num_iterations"] and a["state"] == b["state"], (which, a, b)
+        for k in RES:
+            assert a[k] == pytest.approx(b[k], rel=1e-7, abs=1e-12), (which, k, a, b)
+    v = info["solution_var"]
+    for xa, xb in ((dev["x_first"][v], cpu["x_first"][v]), (dev["x"][v], cpu["x"][v])):
+        assert np.abs(xa - xb).max() <= 1e-7 * max(1.0, np.abs(xb).max())
+    # the parameter did change the answer (the test would be vacuous otherwise)
+    assert np.abs(cpu["x"][v] - cpu["x_first"][v]).max() > 1e-3 * max(1.0, np.abs(cpu["x"][v]).max())

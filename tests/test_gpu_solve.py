@@ -87,3 +87,33 @@ def test_group_lasso(ctx, ref):
 def test_tv_1d(ctx, ref):
     prob, info = problems.tv_1d(5000, seed=7)
     compare(ctx, ref, prob, info, res_rtol=1e-8, max_iterations=300)
+
+
+def test_set_constant_on_an_operator_built_without_one(ctx):
+    """eps_solver_set_constant (Solver::SetParameterValue, solver.cc:109-116) gives an elementwise operator
+    that was built with g = 0 a constant later: NORM_1(x) -> NORM_1(x + c).  Must equal a solver built
+    with c from the start, and the pinned CPU oracle on that problem."""
+    from epsilon_b200.problem import Term
+    from oracle import prox_admm_np as onp
+    rng = np.random.default_rng(31)
+    prob, info = problems.lasso(300, 120, seed=9)
+    c = 0.05 * rng.standard_normal(120)
+    with ProxADMMSolver(prob, {}, ctx=ctx) as s:
+        s.solve()
+        s.set_constant(1, 0, c)              # argument 0 of prox function 1 (NORM_1)
+        s.set_constant(0, 0, -info["b"])     # unchanged value of the SUM_SQUARE constant: c0 recomputed
+        x1 = s.solve()                       # warm_start = 0: a cold solve of the new problem
+        st1, tr1 = s.status.as_dict(), list(s.trace)
+    prob2, _ = problems.lasso(300, 120, seed=9)
+    prob2.prox[1].args[0].terms.append(Term(c, name="c"))
+    with ProxADMMSolver(prob2, {}, ctx=ctx) as s:
+        x2 = s.solve()
+        st2, tr2 = s.status.as_dict(), list(s.trace)
+    assert st1["num_iterations"] == st2["num_iterations"] and len(tr1) == len(tr2)
+    for a, b in zip(tr1, tr2):
+        for k in RES_KEYS:
+            assert a[k] == b[k]
+    assert np.array_equal(x1["x"], x2["x"])
+    o = onp.ProxADMM(prob2).solve()
+    assert o["status"]["num_iterations"] == st2["num_iterations"]
+    assert np.abs(o["x"]["x"] - x2["x"]).max() <= 1e-9
