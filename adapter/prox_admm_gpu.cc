@@ -41,6 +41,26 @@ eps_ctx* Context() {
 
 bool IsMatrixFunction(ProxFunction::Type t) { return t >= ProxFunction::LAMBDA_MAX; }
 
+// LinearMapImpl::operator== is unimplemented for sparse matrices (sparse_matrix_impl.cc:80-90 returns
+// false), so the compressed arrays are compared here; everything else defers to the reference.
+bool SameMap(const linear_map::LinearMapImpl& a, const linear_map::LinearMapImpl& b) {
+  if (a.type() != b.type() || a.m() != b.m() || a.n() != b.n()) return false;
+  if (a.type() == linear_map::SPARSE_MATRIX) {
+    const auto& A = static_cast<const linear_map::SparseMatrixImpl&>(a).sparse();
+    const auto& B = static_cast<const linear_map::SparseMatrixImpl&>(b).sparse();
+    if (A.nonZeros() != B.nonZeros()) return false;
+    return memcmp(A.outerIndexPtr(), B.outerIndexPtr(), sizeof(int) * (A.cols() + 1)) == 0 &&
+           memcmp(A.innerIndexPtr(), B.innerIndexPtr(), sizeof(int) * A.nonZeros()) == 0 &&
+           memcmp(A.valuePtr(), B.valuePtr(), sizeof(double) * A.nonZeros()) == 0;
+  }
+  if (a.type() == linear_map::KRONECKER_PRODUCT) {
+    const auto& A = static_cast<const linear_map::KroneckerProductImpl&>(a);
+    const auto& B = static_cast<const linear_map::KroneckerProductImpl&>(b);
+    return SameMap(A.A().impl(), B.A().impl()) && SameMap(A.B().impl(), B.B().impl());
+  }
+  return a == b;
+}
+
 }  // namespace
 
 ProxADMMGpuSolver::ProxADMMGpuSolver(
@@ -159,7 +179,13 @@ std::vector<ProxADMMGpuSolver::Affine> ProxADMMGpuSolver::Walk() {
 }
 
 void ProxADMMGpuSolver::Build(const std::vector<Affine>& exprs) {
-  Release();
+  // a live solver whose matrices changed (SetParameterValue on a LinearMap constant): the reference keeps
+  // x_, y_, u_ across the re-run of Init (prox_admm.cc:110-120); the old device solver hands its iterate on
+  eps_solver* old_solver = solver_;
+  eps_problem* old_prob = prob_;
+  solver_ = nullptr;
+  prob_ = nullptr;
+  var_index_.clear();
   eps_ctx* ctx = Context();
   EPS_OK_OR_FATAL(eps_problem_create(ctx, &prob_));
   for (const Expression* var : GetVariables(problem())) {
@@ -223,6 +249,9 @@ void ProxADMMGpuSolver::Build(const std::vector<Affine>& exprs) {
   p.solver = EPS_SOLVER_PROX_ADMM;
   if (const char* mode = getenv("EPSILON_GPU_KKT_MODE")) p.kkt_mode = atoi(mode);
   EPS_OK_OR_FATAL(eps_solver_create(prob_, &p, &solver_));
+  if (old_solver && params_.warm_start()) EPS_OK_OR_FATAL(eps_solver_copy_state(solver_, old_solver));
+  if (old_solver) eps_solver_destroy(old_solver);
+  if (old_prob) eps_problem_destroy(old_prob);
   built_ = exprs;
 }
 
@@ -238,7 +267,9 @@ bool ProxADMMGpuSolver::SameMaps(const std::vector<Affine>& exprs) const {
     if (a.A.col_keys() != b.A.col_keys()) return false;
     for (const std::string& var_id : a.A.col_keys()) {
       if (a.A.has_key(a.row_key, var_id) != b.A.has_key(b.row_key, var_id)) return false;
-      if (a.A.has_key(a.row_key, var_id) && !(a.A(a.row_key, var_id) == b.A(b.row_key, var_id))) return false;
+      if (a.A.has_key(a.row_key, var_id) &&
+          !SameMap(a.A(a.row_key, var_id).impl(), b.A(b.row_key, var_id).impl()))
+        return false;
     }
   }
   return true;

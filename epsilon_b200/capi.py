@@ -113,6 +113,7 @@ SIGNATURES = {
     "eps_solver_destroy": (None, [_P]),
     "eps_solver_solve": (C.c_int, [_P, C.POINTER(Status), TRACE_FN, _P]),
     "eps_solver_set_constant": (C.c_int, [_P, C.c_int, C.c_int, _DP]),
+    "eps_solver_copy_state": (C.c_int, [_P, _P]),
     "eps_solver_iterate": (C.c_int, [_P, C.c_int, C.POINTER(C.c_float)]),
     "eps_solver_residuals": (C.c_int, [_P, C.POINTER(Status)]),
     "eps_solver_get_variable": (C.c_int, [_P, C.c_char_p, _DP]),

@@ -407,6 +407,34 @@ int eps_solver_set_constant(eps_solver* s, int prox_index, int arg_or_constraint
   EPS_API_END
 }
 
+int eps_solver_copy_state(eps_solver* dst, eps_solver* src) {
+  EPS_API_BEGIN
+  EPS_CHECK(dst && src && dst != src, "eps_solver_copy_state arguments");
+  EPS_CHECK(dst->ctx == src->ctx, "solvers live on different contexts");
+  EPS_CHECK(dst->two_block == src->two_block && dst->u.n == src->u.n && dst->x.n == src->x.n &&
+                dst->ybuf[0].n == src->ybuf[0].n && dst->zbuf[0].n == src->zbuf[0].n && dst->ub.n == src->ub.n &&
+                dst->y_m.n == src->y_m.n,
+            "the two solvers do not share a variable / constraint layout");
+  Ctx* ctx = dst->ctx;
+  CUDA_CHECK(cudaSetDevice(ctx->device));
+  auto copy = [&](eps::DevBuf<double>& d, const eps::DevBuf<double>& s_) {
+    if (d.n) CUDA_CHECK(cudaMemcpyAsync(d.p, s_.p, d.n * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream));
+  };
+  copy(dst->u, src->u);
+  copy(dst->x, src->x);
+  copy(dst->ybuf[0], src->ybuf[0]);
+  copy(dst->ybuf[1], src->ybuf[1]);
+  copy(dst->zbuf[0], src->zbuf[0]);
+  copy(dst->zbuf[1], src->zbuf[1]);
+  copy(dst->ub, src->ub);
+  copy(dst->y_m, src->y_m);
+  dst->parity = src->parity;
+  dst->zpar = src->zpar;
+  dst->started = src->started;
+  CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+  EPS_API_END
+}
+
 int eps_solver_get_variable(eps_solver* s, const char* var_id, double* out) {
   EPS_API_BEGIN
   EPS_CHECK(s && var_id && out, "eps_solver_get_variable arguments");

@@ -69,6 +69,7 @@ class LinearMapSpec:
     kron: Optional[Sequence["LinearMapSpec"]] = None  # (A, B) for A (x) B
     trans: bool = False  # DENSE only: stored data is the transpose's (shares storage)
     name: str = ""  # data_location stem for the reference
+    parameter_id: str = ""  # DENSE only: Constant.parameter_id of the matrix data (a cvxpy Parameter)
 
     @staticmethod
     def Dense(a: np.ndarray, name: str = "") -> "LinearMapSpec":

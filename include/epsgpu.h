@@ -244,6 +244,11 @@ int eps_solver_solve(eps_solver* s, eps_status* status, eps_trace_fn trace, void
  * refactorisation.  A parameter inside a MATRIX needs a new solver (eps_solver_create). */
 int eps_solver_set_constant(eps_solver* s, int prox_index, int arg_or_constraint_index,
                             const double* values);
+/* Carries the iterate (u, x_i, y_i, y_prev; z, u of the two-block form) of `src` over to `dst`, a solver
+ * created from a problem with the same variables and constraint rows (e.g. after a parameter inside a
+ * matrix changed): with params.warm_start the next eps_solver_solve(dst) continues from it, as the
+ * reference does when Init() re-runs on a live solver (prox_admm.cc:110-120 keeps x_, y_, u_). */
+int eps_solver_copy_state(eps_solver* dst, eps_solver* src);
 /* Run exactly `iterations` more ADMM iterations without stop test (benchmarking);
  * `elapsed_ms` = CUDA-event time on the context stream. */
 int eps_solver_iterate(eps_solver* s, int iterations, float* elapsed_ms);

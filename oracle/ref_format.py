@@ -58,7 +58,7 @@ class _RefWriter:
     def linear_map(self, lm: LinearMapSpec) -> str:
         if lm.kind == MAP_DENSE:
             return "linear_map_type: DENSE_MATRIX m: %d n: %d %s" % (
-                lm.m, lm.n, self.dense_constant(lm.dense, lm.name or "dense"))
+                lm.m, lm.n, self.dense_constant(lm.dense, lm.name or "dense", getattr(lm, "parameter_id", "")))
         if lm.kind == MAP_SPARSE:
             return "linear_map_type: SPARSE_MATRIX m: %d n: %d %s" % (
                 lm.m, lm.n, self.sparse_constant(lm.sparse, lm.name or "sparse"))
@@ -129,7 +129,8 @@ def write_reference_problem(problem: ProxAffineProblem, out_dir: str,
         os.makedirs(os.path.join(out_dir, "reparam"), exist_ok=True)
         for pid, val in reparam.items():
             with open(os.path.join(out_dir, "reparam", pid), "w") as f:
-                f.write(w.dense_constant_body(np.asarray(val, dtype=np.float64).ravel(), "param_" + pid, pid) + "\n")
+                val = np.asarray(val, dtype=np.float64)
+                f.write(w.dense_constant_body(val if val.ndim == 2 else val.ravel(), "param_" + pid, pid) + "\n")
     obj = "expression_type: ADD %s %s" % (
         w.size(1), " ".join("arg { %s }" % w.prox_function(f) for f in problem.prox))
     parts = ["objective { %s }" % obj]

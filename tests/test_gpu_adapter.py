@@ -72,7 +72,7 @@ def _with_parameter(prob, prox, arg, term, pid):
     return prob
 
 
-@pytest.mark.parametrize("kind", ["lasso_dense", "lasso_sparse_cg", "tv_1d", "hinge_constraint"])
+@pytest.mark.parametrize("kind", ["lasso_dense", "lasso_sparse_cg", "tv_1d", "hinge_constraint", "lasso_matrix"])
 def test_set_parameter_value_and_warm_start_match_the_stock_solver(adapter, ref, kind):
     """Solve, SetParameterValue, Solve again with warm_start -- through Solver's own interface, on the
     stock ProxADMMSolver (CPU) and on ProxADMMGpuSolver (device); first and second solves must agree."""
@@ -91,10 +91,16 @@ def test_set_parameter_value_and_warm_start_match_the_stock_solver(adapter, ref,
         prob, info = problems.tv_1d(5000, seed=7)
         _with_parameter(prob, 0, 0, 1, "b")
         new = {"b": info["b"] + 0.5 * rng.standard_normal(5000)}
+    elif kind == "lasso_matrix":
+        # a parameter inside a linear map: the device solver is rebuilt and inherits the iterate
+        # (eps_solver_copy_state), the reference refactorises and keeps x_, y_, u_
+        prob, info = problems.lasso(80, 120, seed=12)
+        prob.prox[0].args[0].terms[0].map.parameter_id = "A"
+        new = {"A": np.asfortranarray(info["A"] * (1.0 + 0.1 * rng.standard_normal((80, 120))))}
     else:
         prob, info = problems.hinge_l2(1500, 100, seed=5)
         prob.constraints[0].terms[0].parameter_id = "margin"      # the constant 1 of  1 - DA x - t = 0
-        new = {"margin": 1.0 + 0.3 * rng.random(1500)}
+        new = {"margin": 0.2 + 3.0 * rng.random(1500)}
     params = {"max_iterations": 300}
     cpu = ref.run(prob, params=params, mode="resolve", reparam=new)
     dev = adapter.run(prob, params=params, mode="gpu-resolve", reparam=new, env_extra=env)
@@ -107,4 +113,4 @@ def test_set_parameter_value_and_warm_start_match_the_stock_solver(adapter, ref,
     for xa, xb in ((dev["x_first"][v], cpu["x_first"][v]), (dev["x"][v], cpu["x"][v])):
         assert np.abs(xa - xb).max() <= 1e-7 * max(1.0, np.abs(xb).max())
     # the parameter did change the answer (the test would be vacuous otherwise)
-    assert np.abs(cpu["x"][v] - cpu["x_first"][v]).max() > 1e-3 * max(1.0, np.abs(cpu["x"][v]).max())
+    assert np.abs(cpu["x"][v] - cpu["x_first"][v]).max() > 1e-4 * max(1.0, np.abs(cpu["x"][v]).max())

@@ -188,3 +188,44 @@ def test_unsorted_csc_columns_are_sorted_at_ingest(ctx, fmt, monkeypatch):
     x, y = rng.standard_normal(700), rng.standard_normal(5000)
     assert np.abs(lm.apply(x) - a @ x).max() <= 1e-13 * 10
     assert np.abs(lm.transpose().apply(y) - a.T @ y).max() <= 1e-13 * 100
+
+
+def test_inverse_per_map_type(ctx):
+    """LinearMapImpl::Inverse (linear_map.h:49; block_matrix_test.cc:78-93 checks block-diagonal inverses
+    against Eigen::LLT at 1e-8)."""
+    from epsilon_b200.capi import EpsError
+    rng = np.random.default_rng(12)
+    n = 150
+    x = rng.standard_normal(n)
+    # scalar, diagonal with a zero entry (kept zero, diagonal_matrix_impl.cc:15-23)
+    assert np.allclose(LinearMap(ctx, LinearMapSpec.Scalar(-4.0, n)).inverse().apply(x), x / -4.0, rtol=1e-15)
+    d = rng.standard_normal(n)
+    d[7] = 0.0
+    ref = np.where(d != 0, x / np.where(d != 0, d, 1.0), 0.0)
+    assert np.allclose(LinearMap(ctx, LinearMapSpec.Diagonal(d)).inverse().apply(x), ref, rtol=1e-15)
+    # dense symmetric positive definite, and negative definite (the -I - 2a AA' pivots of BlockCholesky)
+    b = rng.standard_normal((n, 40))
+    spd = b @ b.T + np.eye(n)
+    for mat in (spd, -spd):
+        inv = LinearMap(ctx, LinearMapSpec.Dense(mat)).inverse()
+        assert inv.shape == (n, n)
+        assert np.abs(inv.apply(x) - np.linalg.solve(mat, x)).max() <= 1e-10 * np.abs(x).max()
+    # sparse: scalar matrix -> scalar inverse; general -> dense inverse (sparse_matrix_impl.cc:60-78)
+    assert np.allclose(LinearMap(ctx, LinearMapSpec.Sparse(2.5 * sp.identity(n, format="csc"))).inverse().apply(x), x / 2.5)
+    s = sp.random(n, n, density=0.05, random_state=3, format="csc")
+    ssp = (s @ s.T + sp.identity(n)).tocsc()
+    got = LinearMap(ctx, LinearMapSpec.Sparse(ssp)).inverse().apply(x)
+    assert np.abs(got - np.linalg.solve(ssp.toarray(), x)).max() <= 1e-10 * np.abs(x).max()
+    # Kronecker: inv(A) (x) inv(B)
+    a2 = rng.standard_normal((4, 6))
+    a2 = a2 @ a2.T + np.eye(4)
+    k = LinearMapSpec.Kronecker(LinearMapSpec.Dense(a2), LinearMapSpec.Scalar(0.5, 10))
+    xk = rng.standard_normal(40)
+    got = LinearMap(ctx, k).inverse().apply(xk)
+    assert np.abs(got - np.linalg.solve(np.kron(a2, 0.5 * np.eye(10)), xk)).max() <= 1e-11
+    # indefinite: refused, not approximated
+    ind = np.diag(np.concatenate([np.ones(5), -np.ones(5)]))
+    with pytest.raises(EpsError):
+        LinearMap(ctx, LinearMapSpec.Dense(ind)).inverse()
+    # the context survives the refused factorisation
+    assert np.allclose(LinearMap(ctx, LinearMapSpec.Scalar(2.0, 10)).inverse().apply(np.ones(10)), 0.5)
