@@ -262,6 +262,13 @@ def main_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t[0])
 
+    def max_over_ranks_vec(a):
+        if world == 1:
+            return a
+        t = torch.from_numpy(np.ascontiguousarray(a, dtype=np.float64).copy())
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return t.numpy()
+
     assert PANELS % world == 0
     per = PANELS // world
     t_gen = time.time()
@@ -308,8 +315,9 @@ def main_ours(args):
         if not args.no_parity_check:
             parity = parity_check_fullsize(args, list(s.trace), x["x"], obj)
             # every rank must have taken the same decisions
-            agree = allreduce(np.array([st["num_iterations"], st["r_norm"], st["s_norm"]], dtype=np.float64)) / world
-            parity["ranks_agree"] = bool(np.array_equal(agree, np.array([st["num_iterations"], st["r_norm"], st["s_norm"]])))
+            mine = np.array([st["num_iterations"], st["r_norm"], st["s_norm"], obj], dtype=np.float64)
+            parity["ranks_agree"] = bool(np.array_equal(max_over_ranks_vec(mine), mine)
+                                         and np.array_equal(-max_over_ranks_vec(-mine), mine))
             if parity["ok"] is not None:
                 parity["ok"] = bool(parity["ok"] and parity["ranks_agree"] and st["cg_unconverged"] == 0)
         e2e = {"value": iters / t_e2e, "unit": "iterations/s",

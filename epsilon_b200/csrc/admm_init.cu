@@ -637,6 +637,10 @@ void eps_solver::ResetVariables() {
     zbuf[0].zero(); zbuf[1].zero(); ub.zero(); y_m.zero();
     zpar = 0;
   }
+  // x is about to change under the CG solvers: the residual they carry between solves is void
+  for (auto& op : ops)
+    if (op.kkt) { op.kkt->carry_valid = false; if (op.kkt->inner) op.kkt->inner->carry_valid = false; }
+  if (proj) proj->carry_valid = false;
   u.zero();
   x.zero();
   ybuf[0].zero();

@@ -58,6 +58,7 @@ Ctx::~Ctx() {
   split_scratch.release();
   seg_scratch.release();
   sell_scratch.release();
+  sell_scratch2.release();
   red_partials.release();
   red_counter.release();
   if (h_flag) cudaFreeHost(h_flag);
@@ -211,6 +212,85 @@ void UploadBytes(Ctx* ctx, void* dst, const void* src, size_t bytes) {
 int* PinnedFlag(Ctx* ctx) {
   if (!ctx->h_flag) CUDA_CHECK(cudaMallocHost(&ctx->h_flag, 64));
   return ctx->h_flag;
+}
+
+namespace {
+struct StepTrace {
+  int from = -2;           // -2: not read yet, -1: off
+  int sell_launches = 0;
+  static constexpr int kSlots = 9, kStride = 256 * 8;
+  DevBuf<unsigned long long> buf;
+  int used = 0;
+  bool dumped = false;
+  struct Rec { int kind, ctas; char label[48]; } recs[kSlots];
+};
+StepTrace g_step_trace;
+}  // namespace
+
+static void StepTracePreset(Ctx* ctx, StepTrace& t) {
+  // slot s is a stream pass unless s % 3 == 2 (pass, pass 2, tail, pass, ...): the stream layout wants its
+  // "first warp done" word preset for atomicMin; nothing is written between the traced launches
+  std::vector<unsigned long long> init((size_t)StepTrace::kSlots * StepTrace::kStride, 0ull);
+  for (int s = 0; s < StepTrace::kSlots; s++)
+    if (s % 3 != 2)
+      for (size_t i = 0; i < StepTrace::kStride; i += 4) init[(size_t)s * StepTrace::kStride + i + 2] = ~0ull;
+  t.buf.upload(init.data(), init.size());
+  CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+}
+
+unsigned long long* StepTraceSlot(Ctx* ctx, int kind, int ctas, const char* label) {
+  StepTrace& t = g_step_trace;
+  if (t.from == -2) t.from = getenv("EPS_STEP_TRACE") ? atoi(getenv("EPS_STEP_TRACE")) : -1;
+  if (t.from < 0 || t.dumped || ctas > 256) return nullptr;
+  if (kind == 0) t.sell_launches++;
+  if (t.sell_launches < t.from) return nullptr;
+  if (!t.buf.p) {
+    t.buf.alloc(ctx, (size_t)StepTrace::kSlots * StepTrace::kStride);
+    StepTracePreset(ctx, t);
+    return nullptr;     // this launch ran behind a synchronisation: start with a later one
+  }
+  const bool pass1 = kind == 0 && strstr(label, "pre-phase") == nullptr;
+  if (t.used == 0 && !pass1) return nullptr;            // the window opens at a first pass of the CG step
+  if (t.used == StepTrace::kSlots) {
+    t.dumped = true;
+    std::vector<unsigned long long> h((size_t)StepTrace::kSlots * StepTrace::kStride);
+    t.buf.download(h.data(), h.size());
+    unsigned long long t0 = ~0ull;
+    for (int s = 0; s < t.used; s++)
+      for (int c = 0; c < t.recs[s].ctas; c++) {
+        const unsigned long long v = h[(size_t)s * StepTrace::kStride + (size_t)c * (t.recs[s].kind ? 8 : 4)];
+        if (v) t0 = std::min(t0, v);
+      }
+    std::string out = Format("[step trace] rank %d: us since the first stamp; per stamp min/median/max over the CTAs\n", ctx->rank);
+    for (int s = 0; s < t.used; s++) {
+      const int per = t.recs[s].kind ? 8 : 4;
+      std::string line = Format("[step trace] rank %d %-28s", ctx->rank, t.recs[s].label);
+      for (int k = 0; k < per; k++) {
+        std::vector<double> v;
+        for (int c = 0; c < t.recs[s].ctas; c++) {
+          const unsigned long long x = h[(size_t)s * StepTrace::kStride + (size_t)c * per + k];
+          if (x && x != ~0ull) v.push_back((double)(x - t0) * 1e-3);
+        }
+        if (v.empty()) { line += " | -"; continue; }
+        std::sort(v.begin(), v.end());
+        line += Format(" | %.1f/%.1f/%.1f", v.front(), v[v.size() / 2], v.back());
+      }
+      out += line + "\n";
+    }
+    fputs(out.c_str(), stderr);
+    return nullptr;
+  }
+  const bool expect_tail = t.used % 3 == 2, expect_pass2 = t.used % 3 == 1;
+  if ((kind == 1) != expect_tail || (kind == 0 && pass1 == expect_pass2)) {
+    // not the pass / pass 2 / tail rhythm (a solve started in between): start over at the next first pass
+    t.used = 0;
+    StepTracePreset(ctx, t);
+    return nullptr;
+  }
+  StepTrace::Rec& r = t.recs[t.used];
+  r.kind = kind; r.ctas = ctas;
+  snprintf(r.label, sizeof(r.label), "%s", label);
+  return t.buf.p + (size_t)(t.used++) * StepTrace::kStride;
 }
 
 double* GrowScratch(Ctx* ctx, DevBuf<double>* buf, size_t count) {

@@ -161,6 +161,29 @@ __device__ __forceinline__ void StReleaseSys(unsigned long long* p, unsigned lon
   asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 
+// Grid-wide barrier for kernels whose CTAs are all co-resident (grid <= number of SMs, one CTA per SM
+// fits next to whatever the programmatic launch overlaps with): bar[0] counts arrivals, bar[1] is the
+// generation.  Unlike cooperative_groups::grid_group::sync() it does not need a cooperative launch, so
+// the kernel can be launched with programmatic stream serialization (its prologue overlaps the drain
+// of its predecessor).  Both words start at zero; the barrier leaves bar[0] at zero again.
+__device__ __forceinline__ void GridBarrier(unsigned* bar) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    volatile unsigned* gen = bar + 1;
+    const unsigned g = *gen;
+    __threadfence();
+    if (atomicAdd(bar, 1u) == gridDim.x - 1) {
+      bar[0] = 0;
+      __threadfence();
+      atomicAdd(bar + 1, 1u);
+    } else {
+      while (*gen == g) {}
+    }
+    __threadfence();
+  }
+  __syncthreads();
+}
+
 inline int GridFor(int64_t n, int block, int per_thread, int sm_count, int max_waves = 8) {
   int64_t g = (n + (int64_t)block * per_thread - 1) / ((int64_t)block * per_thread);
   int64_t cap = (int64_t)sm_count * max_waves;

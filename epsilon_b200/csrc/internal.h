@@ -118,7 +118,7 @@ struct Ctx {
   Prof prof[KC_COUNT];
   cudaEvent_t prof_ev[2] = {nullptr, nullptr};
   // scratch owned by the context (grown on demand, never during graph capture)
-  DevBuf<double> split_scratch, seg_scratch, red_partials, sell_scratch;
+  DevBuf<double> split_scratch, seg_scratch, red_partials, sell_scratch, sell_scratch2;
   DevBuf<unsigned int> red_counter;
   int64_t scratch_generation = 0;
   int* h_flag = nullptr;
@@ -267,6 +267,10 @@ void SellApply(Ctx* ctx, const Sell& S, double alpha, const double* x, double be
 // The stream kernel alone: returns the T x R partial planes (context scratch, valid until the
 // next sparse apply); y = alpha * sum_t planes[t] is left to the caller's consumer kernel.
 const double* SellApplyPlanes(Ctx* ctx, const Sell& S, const double* x, int kclass, const int* skip);
+// Second pass of a matvec pair: x = alpha * sum_t prevP[t] is formed INSIDE the kernel (every CTA a slice,
+// then a grid barrier on `bar`) before the x tiles are staged; returns this pass's planes (second buffer).
+const double* SellApplyPlanesAfter(Ctx* ctx, const Sell& S, double* x, const double* prevP, int prevT, double alpha,
+                                   unsigned* bar, int kclass, const int* skip);
 void DenseGemv(Ctx* ctx, const double* A, int lda, int m, int n, bool trans, double alpha,
                const double* x, double beta, double* y, int tri = 0);
 
@@ -285,6 +289,12 @@ struct ReduceScratch {
 };
 ReduceScratch GetReduceScratch(Ctx* ctx);
 double* GrowScratch(Ctx* ctx, DevBuf<double>* buf, size_t count);
+// EPS_STEP_TRACE=<k>: from the k-th sparse stream launch on, the next 9 kernels of the fused CG step (stream
+// passes and tails) record per-CTA globaltimer stamps into one buffer WITHOUT any synchronisation in
+// between; the table (us since the first stamp, min / median / max over the CTAs) goes to stderr afterwards.
+// kind 0 = stream pass (4 stamps per CTA: start, x staged, first warp done, last warp done),
+// kind 1 = fused tail (8 stamps per CTA).  Returns nullptr when not tracing this launch.
+unsigned long long* StepTraceSlot(Ctx* ctx, int kind, int ctas, const char* label);
 int* PinnedFlag(Ctx* ctx);  // one pinned host int for device->host round trips
 
 // ---- composite block operator (BlockMatrix, vector/block_matrix.h) --------------------

@@ -288,6 +288,194 @@ CgFusedTailKernel(int64_t n, int T, const double* __restrict__ planes, double al
 #undef EPS_TT
 }
 
+// r0 without a matvec: the previous solve left r_prev = rhs_prev - M x_prev for the x that is the warm
+// start of this one, so r0 = rhs - M x_prev = r_prev + (rhs - rhs_prev).  (One product with M = two passes over
+// the matrix saved per ADMM iteration; the true residual is recomputed every few solves to bound the drift
+// of the recurrence.)  Otherwise as CgStartKernel; also leaves rhs in rhs_prev for the next solve.
+__global__ void __launch_bounds__(kBlock)
+CgCarryStartKernel(int64_t n, const double* __restrict__ rhs, double* __restrict__ rhs_prev,
+                   double* __restrict__ r, double* __restrict__ p, double tol, double* scal, double* partials,
+                   unsigned* counter, int* done, KktSolver::CgResult* ring, long long seq) {
+  __shared__ double smem[64];
+  double acc[2] = {0.0, 0.0};
+  const int64_t stride = (int64_t)gridDim.x * kBlock;
+  for (int64_t i = (int64_t)blockIdx.x * kBlock + threadIdx.x; i < n; i += stride) {
+    const double b = rhs[i];
+    const double t = r[i] + (b - rhs_prev[i]);
+    rhs_prev[i] = b;
+    r[i] = t;
+    p[i] = t;
+    acc[0] += t * t;
+    acc[1] += b * b;
+  }
+  if (GridSumLast<2>(acc, smem, partials, counter)) {
+    const double thresh = tol * sqrt(acc[1] > 0.0 ? acc[1] : acc[0]);
+    const int conv = sqrt(acc[0]) <= thresh ? 1 : 0;
+    scal[0] = acc[0];
+    scal[1] = thresh;
+    *done = conv;
+    KktSolver::CgResult* e = &ring[seq % kCgRing];
+    e->rr = acc[0];
+    e->converged = conv;
+    __threadfence_system();
+    *reinterpret_cast<volatile long long*>(&e->seq) = seq;
+  }
+}
+
+// CgFusedTailKernel with ONE grid-wide synchronisation and no cooperative launch.
+//   The four sums p.w, r.w, w.w, r.r are formed in the same pass that builds w; after the barrier every CTA knows
+//       a = rr / p.w,   rr' = ||r - a w||^2 = rr - 2a r.w + a^2 w.w,   b = rr' / rr
+//   and updates x += a p, r -= a w, p = r + b p in one sweep (the classical recurrence needs r.r of the UPDATED
+//   r, i.e. a second synchronisation).  rr is recomputed from r every step, so the expansion never feeds on
+//   itself: its error is a few ulp of rr, far below the 1e-2..1e-1 by which a CG step shrinks rr here.
+//   The barrier is GridBarrier (device.cuh): the launch is an ordinary one with programmatic stream
+//   serialization, so the kernel's launch latency hides behind the drain of the second SpMV pass.
+__global__ void __launch_bounds__(kTailBlock)
+CgFusedTail2Kernel(int64_t n, int T, const double* __restrict__ planes, double alpha,
+                   double* __restrict__ w, double* __restrict__ p, double* __restrict__ x,
+                   double* __restrict__ r, double* scal, double* partials, int* done,
+                   KktSolver::CgResult* ring, long long seq, PeerXchg px, unsigned long long xseq,
+                   const double* __restrict__ dg, unsigned* bar, unsigned long long* __restrict__ trace) {
+  __shared__ double smem[128];
+  const int G = gridDim.x;
+  const int c = blockIdx.x;
+#define EPS_TT(k) if (trace && threadIdx.x == 0) trace[c * 8 + (k)] = GlobalTimerNs()
+  EPS_TT(0);
+  GridDepLaunch();
+  GridDepWait();
+  const int parity = (int)(xseq & 1ull);
+  const bool finished = *done != 0;  // uniform: written only by the last phase of an earlier launch
+  int64_t per = (n + G - 1) / G;
+  per = (per + 1) & ~(int64_t)1;
+  const int64_t lo = min(n, (int64_t)c * per), hi = min(n, lo + per);
+  const bool ll = px.G > 1 && px.ll1[0] != nullptr;
+  const unsigned seq32 = (unsigned)xseq;
+  if (ll) {
+    // two-shot exchange with flag-in-data packets.  Ownership is by 64-element chunk, chunk k belongs to rank
+    // k % G, so EVERY CTA of every rank owns ~1/G of its own slice: all 148 CTAs take part in the owner step
+    // (with whole slices owned by rank c % G, 7 of 8 CTAs idled while the owners walked their slice twice).
+    if (!finished) {
+      for (int64_t i = lo + threadIdx.x; i < hi; i += 2 * kTailBlock) {
+        const int64_t j = i + kTailBlock;
+        double s0 = 0.0, s1 = 0.0;
+#pragma unroll 8
+        for (int t = 0; t < T; t++) {
+          s0 += __ldcg(planes + (size_t)t * n + i);
+          if (j < hi) s1 += __ldcg(planes + (size_t)t * n + j);
+        }
+        LlStore(px.ll1[(int)((i >> 6) % px.G)] + ((size_t)parity * px.G + px.rank) * px.n + i, alpha * s0, seq32);
+        if (j < hi) LlStore(px.ll1[(int)((j >> 6) % px.G)] + ((size_t)parity * px.G + px.rank) * px.n + j, alpha * s1, seq32);
+      }
+      EPS_TT(1);
+      // owner step: the chunks of this slice that belong to this rank
+      const int64_t ch_lo = lo >> 6, ch_hi = (hi + 63) >> 6;
+      int64_t first = ch_lo + ((px.rank - ch_lo % px.G) + px.G) % px.G;
+      for (int64_t k = threadIdx.x;; k += kTailBlock) {
+        const int64_t ch = first + (k >> 6) * px.G;
+        if (ch >= ch_hi) break;
+        const int64_t i = (ch << 6) + (k & 63);
+        if (i < lo || i >= hi) continue;
+        const double sum = LlSumRanks(px.ll1[px.rank] + (size_t)parity * px.G * px.n + i, (size_t)px.n, px.G, seq32);
+        for (int q = 0; q < px.G; q++)
+          LlStore(px.ll2[(px.rank + q) % px.G] + (size_t)parity * px.n + i, sum, seq32);
+      }
+      EPS_TT(2);
+    }
+  } else if (px.G > 1) {
+    if (!finished) {
+      for (int64_t i = lo + threadIdx.x; i < hi; i += kTailBlock) {
+        double s = 0.0;
+#pragma unroll 8
+        for (int t = 0; t < T; t++) s += __ldcg(planes + (size_t)t * n + i);
+        const double out = alpha * s;
+        const size_t slot = ((size_t)parity * px.G + px.rank) * px.n + i;
+        for (int k = 0; k < px.G; k++) px.recv[(px.rank + k) % px.G][slot] = out;
+      }
+    }
+    __syncthreads();
+    EPS_TT(1);
+    if (threadIdx.x == 0) __threadfence_system();
+    __syncthreads();
+    EPS_TT(2);
+    if (threadIdx.x < px.G)
+      StReleaseSys(px.cflag[threadIdx.x] + ((size_t)parity * px.G + px.rank) * kPeerMaxCtas + c, xseq);
+    if (threadIdx.x < px.G) {
+      const unsigned long long* f = px.cflag[px.rank] + ((size_t)parity * px.G + threadIdx.x) * kPeerMaxCtas + c;
+      while (LdAcquireSys(f) < xseq) {}
+    }
+    __syncthreads();
+  }
+  if (finished) return;
+  const double thresh = scal[1];
+  double v[4] = {0.0, 0.0, 0.0, 0.0};
+  for (int64_t i = lo + threadIdx.x; i < hi; i += kTailBlock) {
+    const double pi = p[i], ri = r[i];
+    double wi;
+    if (ll) {
+      // (the packets of a thread's later elements are already on their way while it spins on this one)
+      wi = LlLoad(px.ll2[px.rank] + (size_t)parity * px.n + i, seq32) + dg[i] * pi;
+    } else if (px.G > 1) {
+      wi = PeerSum(px, xseq, i) + dg[i] * pi;
+    } else {
+      double s = 0.0;
+#pragma unroll 8
+      for (int t = 0; t < T; t++) s += __ldcg(planes + (size_t)t * n + i);
+      wi = alpha * s + dg[i] * pi;
+    }
+    w[i] = wi;
+    v[0] += pi * wi;
+    v[1] += ri * wi;
+    v[2] += wi * wi;
+    v[3] += ri * ri;
+  }
+  EPS_TT(3);
+  BlockSum<4>(v, smem);
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int k = 0; k < 4; k++) partials[k * G + c] = v[k];
+  }
+  EPS_TT(4);
+  GridBarrier(bar);
+  EPS_TT(5);
+  // every CTA adds the G partials of the four sums in the same order: identical a, b everywhere
+  double t4[4] = {0.0, 0.0, 0.0, 0.0};
+  for (int i = threadIdx.x; i < G; i += kTailBlock) {
+#pragma unroll
+    for (int k = 0; k < 4; k++) t4[k] += __ldcg(&partials[k * G + i]);
+  }
+  BlockSum<4>(t4, smem);
+  __shared__ double tot_[4];
+  __syncthreads();
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int k = 0; k < 4; k++) tot_[k] = t4[k];
+  }
+  __syncthreads();
+  const double pw = tot_[0], rw = tot_[1], ww = tot_[2], rr = tot_[3];
+  const double a = pw != 0.0 ? rr / pw : 0.0;
+  const double rr_new = fmax(rr - 2.0 * a * rw + a * a * ww, 0.0);
+  const double b = rr != 0.0 ? rr_new / rr : 0.0;
+  for (int64_t i = lo + threadIdx.x; i < hi; i += kTailBlock) {
+    const double pi = p[i];
+    x[i] += a * pi;
+    const double t = r[i] - a * w[i];
+    r[i] = t;
+    p[i] = t + b * pi;
+  }
+  EPS_TT(6);
+  if (c == 0 && threadIdx.x == 0) {
+    const int conv = sqrt(rr_new) <= thresh ? 1 : 0;
+    scal[0] = rr_new;
+    if (conv) *done = 1;
+    KktSolver::CgResult* e = &ring[seq % kCgRing];
+    e->rr = rr_new;
+    e->converged = conv;
+    __threadfence_system();
+    *reinterpret_cast<volatile long long*>(&e->seq) = seq;
+  }
+#undef EPS_TT
+}
+
 __global__ void InvertKernel(int64_t n, const double* __restrict__ d, double* __restrict__ out, int* bad) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
@@ -468,6 +656,7 @@ void KktSolver::Init(const std::vector<double>& g_host, const std::vector<double
       ab.map = dm; ab.trans = false; ab.scale = 1.0; ab.row_off = 0; ab.col_off = 0;
       inner->A.ctx = ctx; inner->A.rows = nb; inner->A.cols = nb;
       inner->A.blks.push_back(ab);
+      inner->carry_enabled = k == 1;
       inner->Init(std::vector<double>(), std::vector<double>());
       kron_k = k;
       mode = inner->mode;
@@ -563,7 +752,7 @@ void KktSolver::Init(const std::vector<double>& g_host, const std::vector<double
       const int64_t want = (n + kTailBlock - 1) / kTailBlock;
       tail_grid = (int)std::max<int64_t>(1, std::min<int64_t>(want, (int64_t)ctx->sm_count * per_sm));
       tail_grid = std::min(tail_grid, ctx->sm_count);
-      cg_partials.alloc(ctx, 2 * (size_t)tail_grid);
+      cg_partials.alloc(ctx, 4 * (size_t)tail_grid);
     }
     // fused matvec: H is one SELL-packed sparse block over all of x and A'A is diagonal
     fast_h = a_diag && alpha2 != 0.0 && H.blks.size() == 1 && H.blks[0].map->kind == MK_SPARSE &&
@@ -575,12 +764,19 @@ void KktSolver::Init(const std::vector<double>& g_host, const std::vector<double
       int per_sm = 0;
       CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, CgFusedTailKernel, kTailBlock, 0));
       EPS_CHECK(per_sm >= 1, "CgFusedTailKernel does not fit an SM");
+      tail_v2 = !getenv("EPS_TAIL_V1") && H.blks[0].map->sell.n_cta <= ctx->sm_count &&
+                H.blks[0].map->sell_t.n_cta <= ctx->sm_count;
+      if (tail_v2) {
+        rhs_prev.alloc(ctx, n);
+        cg_bar.alloc(ctx, 4);
+        cg_bar.zero();
+      }
     }
     CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
     description = Format("kkt=CG n=%lld rows_h=%lld tol=%.1e%s%s%s", (long long)n, (long long)rows_h, cg_tol,
                          h_sharded ? " sharded" : "", fast_h ? " fused-matvec" : "",
                          peer ? " peer-allreduce" : "");
-    if (fused_tail) description += " fused-tail";
+    if (fused_tail) description += tail_v2 ? " fused-tail(one-barrier, pre-phase, residual-carry)" : " fused-tail";
   } else {
     throw Error(EPS_ERR_INVALID, Format("unknown kkt mode %d", mode));
   }
@@ -710,11 +906,23 @@ void KktSolver::Solve(const double* rhs, double* x) {
         }
         return *const_cast<const CgResult*>(e);
       };
-      MatVec(x, cg_w.p, nullptr);
-      CgStartKernel<<<grid, kBlock, 0, ctx->stream>>>(n, rhs, cg_w.p, cg_r.p, cg_p.p, cg_tol, scal.p,
-                                                       rs.partials, rs.counter, cg_done.p, ring, base,
-                                                       peer ? peer->x : PeerXchg(), pending_seq, ddiag.p, x);
-      ctx->count_launch();
+      static const bool no_carry = getenv("EPS_NO_CARRY") != nullptr;
+      // every 8th solve recomputes the true residual (bounds the drift of the carried recurrence)
+      const bool carry = tail_v2 && carry_enabled && carry_valid && !no_carry && (carry_count % 8) != 0;
+      if (carry) {
+        ProfScope ps(ctx, KC_VEC, 48.0 * n);
+        CgCarryStartKernel<<<grid, kBlock, 0, ctx->stream>>>(n, rhs, rhs_prev.p, cg_r.p, cg_p.p, cg_tol, scal.p,
+                                                             rs.partials, rs.counter, cg_done.p, ring, base);
+        ctx->count_launch();
+      } else {
+        MatVec(x, cg_w.p, nullptr);
+        CgStartKernel<<<grid, kBlock, 0, ctx->stream>>>(n, rhs, cg_w.p, cg_r.p, cg_p.p, cg_tol, scal.p,
+                                                         rs.partials, rs.counter, cg_done.p, ring, base,
+                                                         peer ? peer->x : PeerXchg(), pending_seq, ddiag.p, x);
+        ctx->count_launch();
+        if (tail_v2) VecCopy(ctx, n, rhs, rhs_prev.p);
+      }
+      if (tail_v2) carry_count++;
       int it = 0;
       bool converged = false;
       for (; it < cg_max_iter; it++) {
@@ -728,10 +936,18 @@ void KktSolver::Solve(const double* rhs, double* x) {
           const MapData& M = *b.map;
           const Sell& S1 = b.trans ? M.sell_t : M.sell;
           const Sell& S2 = b.trans ? M.sell : M.sell_t;
-          SpmvExtra e1;
-          e1.skip = cg_done.p;
-          SellApply(ctx, S1, b.scale, cg_p.p, 0.0, th1.p, b.trans ? KC_SPMV_T : KC_SPMV_N, &e1);
-          const double* planes = SellApplyPlanes(ctx, S2, th1.p, b.trans ? KC_SPMV_N : KC_SPMV_T, cg_done.p);
+          const double* planes = nullptr;
+          if (tail_v2) {
+            // first pass as planes; their reduction rides in the second pass (pre-phase + grid barrier)
+            const double* p1 = SellApplyPlanes(ctx, S1, cg_p.p, b.trans ? KC_SPMV_T : KC_SPMV_N, cg_done.p);
+            planes = SellApplyPlanesAfter(ctx, S2, th1.p, p1, S1.T, b.scale, cg_bar.p + 2,
+                                          b.trans ? KC_SPMV_N : KC_SPMV_T, cg_done.p);
+          } else {
+            SpmvExtra e1;
+            e1.skip = cg_done.p;
+            SellApply(ctx, S1, b.scale, cg_p.p, 0.0, th1.p, b.trans ? KC_SPMV_T : KC_SPMV_N, &e1);
+            planes = SellApplyPlanes(ctx, S2, th1.p, b.trans ? KC_SPMV_N : KC_SPMV_T, cg_done.p);
+          }
           {
           ProfScope ps(ctx, peer ? KC_ALLREDUCE : KC_VEC, 8.0 * S2.T * n + 72.0 * n);
           int64_t nn = n;
@@ -757,6 +973,30 @@ void KktSolver::Solve(const double* rhs, double* x) {
             }
             if (launch_no++ == trace_at) trace = tbuf.p;
           }
+          bool step_trace = false;
+          if (tail_v2) {
+            if (unsigned long long* st = StepTraceSlot(ctx, 1, tail_grid, "tail")) {
+              trace = st;
+              step_trace = true;
+            }
+            // ordinary launch with programmatic stream serialization; one GridBarrier inside
+            if (cg_partials.n < 4 * (size_t)tail_grid) cg_partials.alloc(ctx, 4 * (size_t)tail_grid);
+            part = cg_partials.p;
+            cudaLaunchConfig_t cfg = {};
+            cfg.gridDim = dim3(tail_grid);
+            cfg.blockDim = dim3(kTailBlock);
+            cfg.stream = ctx->stream;
+            cudaLaunchAttribute attr[1];
+            attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+            attr[0].val.programmaticStreamSerializationAllowed = 1;
+            cfg.attrs = attr;
+            static const bool pdl = getenv("EPS_NO_PDL") == nullptr;
+            cfg.numAttrs = pdl ? 1 : 0;
+            unsigned* barp = cg_bar.p;
+            CUDA_CHECK(cudaLaunchKernelEx(&cfg, CgFusedTail2Kernel, nn, T, planes, alpha, wp, pp, xp, rp, sp, part, dp,
+                                          rg, seq, pxv, xs, dgp, barp, trace));
+            ctx->count_launch();
+          } else {
           void* args[] = {&nn, &T, &planes, &alpha, &wp, &pp, &xp, &rp, &sp, &part, &dp, &rg, &seq, &pxv, &xs, &dgp, &trace};
           // EPS_TAIL_PDL=1: cooperative + programmatic serialization (set-up overlaps the SpMV drain)
           static int tail_pdl = getenv("EPS_TAIL_PDL") ? atoi(getenv("EPS_TAIL_PDL")) : 0;
@@ -787,7 +1027,8 @@ void KktSolver::Solve(const double* rhs, double* x) {
             CUDA_CHECK(cudaLaunchCooperativeKernel((const void*)CgFusedTailKernel, dim3(tail_grid),
                                                    dim3(kTailBlock), args, 0, ctx->stream));
           ctx->count_launch();
-          if (trace) {
+          }
+          if (trace && !step_trace) {
             std::vector<unsigned long long> h((size_t)tail_grid * 8);
             tbuf.download(h.data(), h.size());
             unsigned long long t0 = ~0ull;
@@ -833,6 +1074,7 @@ void KktSolver::Solve(const double* rhs, double* x) {
       }
       cg_seq = base + cg_max_iter + 2;
       cg_iters_total += it;
+      carry_valid = tail_v2;   // cg_r is the residual of the x just returned
       break;
     }
     default:

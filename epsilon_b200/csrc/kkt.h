@@ -42,6 +42,15 @@ struct KktSolver {
   int tail_grid = 0;
   bool fast_h = false;           // H = one SELL block, A'A diagonal: fused matvec
   bool fused_tail = false;       // plane reduction + exchange + CG update in one kernel (CgFusedTailKernel)
+  // fused_tail, second generation (EPS_TAIL_V1=1 restores the first): the first-pass plane reduction rides in
+  // the second SpMV pass (pre-phase + GridBarrier), the tail has one grid-wide synchronisation and an ordinary
+  // (programmatic) launch, and the initial residual of a solve is carried over from the previous one
+  bool tail_v2 = false;
+  bool carry_enabled = true;     // false where one object serves several right-hand sides (Kronecker columns)
+  bool carry_valid = false;      // cg_r / rhs_prev belong to the x the next Solve() is warm-started from
+  int64_t carry_count = 0;
+  DevBuf<double> rhs_prev;
+  DevBuf<unsigned> cg_bar;       // GridBarrier state: [0,1] tail, [2,3] pre-phase of the second pass
   PeerBuf* peer = nullptr;       // row-sharded: the context's one-shot NVLink all-reduce buffers (not owned)
   unsigned long long pending_seq = 0;  // exchange the next consumer kernel has to complete (0: none)
   // H = (s I_k) (x) B with A'A repeating over the k blocks (matrix variables, A*X): the system

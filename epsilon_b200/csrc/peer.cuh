@@ -62,4 +62,35 @@ __device__ __forceinline__ double LlLoad(const uint4* p, unsigned seq) {
   return __longlong_as_double((long long)(((unsigned long long)b << 32) | a));
 }
 
+__device__ __forceinline__ uint4 LlPeek(const uint4* p) {
+  uint4 v;
+  asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ double LlValue(const uint4& v) {
+  return __longlong_as_double((long long)(((unsigned long long)v.z << 32) | v.x));
+}
+
+// Sum, in rank order, of the G packets base[q * stride], q < G: all G loads are issued before any of them is
+// tested, so a poll costs one L2 round trip instead of G (one packet at a time the owner step of the exchange
+// took 8 dependent round trips per element: ~6 us at G = 8).
+__device__ __forceinline__ double LlSumRanks(const uint4* base, size_t stride, int G, unsigned seq) {
+  uint4 v[kMaxRanks];
+  bool ok;
+  do {
+    ok = true;
+#pragma unroll
+    for (int q = 0; q < kMaxRanks; q++)
+      if (q < G) v[q] = LlPeek(base + (size_t)q * stride);
+#pragma unroll
+    for (int q = 0; q < kMaxRanks; q++)
+      if (q < G) ok = ok && v[q].y == seq && v[q].w == seq;
+  } while (!ok);
+  double s = 0.0;
+#pragma unroll
+  for (int q = 0; q < kMaxRanks; q++)
+    if (q < G) s += LlValue(v[q]);
+  return s;
+}
+
 }  // namespace eps

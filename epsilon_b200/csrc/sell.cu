@@ -318,7 +318,13 @@ SellStreamKernel(int R, int Cn, int TW, const int32_t* __restrict__ cta_visit,
                  const int32_t* __restrict__ sl_len, const double* __restrict__ val,
                  const uint16_t* __restrict__ idx, const int32_t* __restrict__ rowid,
                  const double* __restrict__ x, double* __restrict__ P, int use_tma,
-                 const int* __restrict__ skip, unsigned long long* __restrict__ trace) {
+                 const int* __restrict__ skip, unsigned long long* __restrict__ trace,
+                 const double* __restrict__ preP, int preT, double preAlpha, double* __restrict__ preY,
+                 unsigned* __restrict__ gbar) {
+  // Optional pre-phase (preP != nullptr): x itself is not in memory yet -- it is alpha * the sum of the preT
+  // partial planes preP[t][0..Cn) the PREVIOUS pass of the CG matvec left behind.  Every CTA adds a fixed
+  // slice of the planes into preY (== x), the grid meets at a barrier, and only then are the x tiles staged.
+  // This replaces the separate plane-reduction launch between the two passes (SellReduceKernel).
   constexpr int kBatch = KB;
   extern __shared__ __align__(128) double xs[];
   __shared__ __align__(8) unsigned long long bar;
@@ -328,7 +334,43 @@ SellStreamKernel(int R, int Cn, int TW, const int32_t* __restrict__ cta_visit,
   if (TRACE && threadIdx.x == 0) trace[blockIdx.x * 4 + 0] = GlobalTimer();
   GridDepLaunch();  // the plane reduction behind this pass is set up while the streams drain
   const int v_lo = cta_visit[blockIdx.x], v_hi = cta_visit[blockIdx.x + 1];
-  if (v_lo >= v_hi) return;
+  auto pre_phase = [&]() {
+    int per = (Cn + (int)gridDim.x - 1) / (int)gridDim.x;
+    const int lo = min(Cn, (int)blockIdx.x * per), hi = min(Cn, lo + per);
+    // four rows per thread and round: the 4 x preT plane loads are independent, so a thread keeps
+    // 16 of them in flight (one row at a time this phase was latency-bound: 24 us for 1M rows)
+    constexpr int kStep = NW * 32;
+    for (int i = lo + (int)threadIdx.x; i < hi; i += 4 * kStep) {
+      const int i1 = i + kStep, i2 = i + 2 * kStep, i3 = i + 3 * kStep;
+      double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+#pragma unroll 4
+      for (int t = 0; t < preT; t++) {
+        const double* row = preP + (size_t)t * Cn;
+        const double a0 = __ldcg(row + i);
+        const double a1 = i1 < hi ? __ldcg(row + i1) : 0.0;
+        const double a2 = i2 < hi ? __ldcg(row + i2) : 0.0;
+        const double a3 = i3 < hi ? __ldcg(row + i3) : 0.0;
+        s0 += a0; s1 += a1; s2 += a2; s3 += a3;
+      }
+      preY[i] = preAlpha * s0;
+      if (i1 < hi) preY[i1] = preAlpha * s1;
+      if (i2 < hi) preY[i2] = preAlpha * s2;
+      if (i3 < hi) preY[i3] = preAlpha * s3;
+    }
+    // the tiles of preY are read by bulk copies (async proxy) on other SMs: order the generic-proxy stores
+    // before them on both sides of the barrier
+    asm volatile("fence.proxy.async.global;" ::: "memory");
+    GridBarrier(gbar);
+    asm volatile("fence.proxy.async.global;" ::: "memory");
+  };
+  if (v_lo >= v_hi) {
+    // a CTA without visits still owes its slice of the pre-phase and its arrival at the barrier
+    if (preP) {
+      GridDepWait();
+      if (!(skip && *skip)) pre_phase();
+    }
+    return;
+  }
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const uint32_t bar_a = SmemAddr(&bar);
   if (use_tma && threadIdx.x == 0) {
@@ -376,6 +418,7 @@ SellStreamKernel(int R, int Cn, int TW, const int32_t* __restrict__ cta_visit,
       // first visit: the loads above are in flight; now order behind the producer of x
       GridDepWait();
       if (skip && *skip) return;  // speculative launch after the CG loop converged (kkt.cu)
+      if (preP) pre_phase();
       if (use_tma && threadIdx.x == 0) {
         const uint32_t bytes = (uint32_t)cw * 8u;
         asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_a), "r"(bytes) : "memory");
@@ -395,7 +438,7 @@ SellStreamKernel(int R, int Cn, int TW, const int32_t* __restrict__ cta_visit,
         }
         phase ^= 1u;
       } else {
-        for (int i = threadIdx.x; i < cw; i += NW * 32) xs[i] = x[c0 + i];
+        for (int i = threadIdx.x; i < cw; i += NW * 32) xs[i] = __ldcg(x + c0 + i);  // may be written in-kernel (pre-phase)
         __syncthreads();
       }
       cur_t = t;
@@ -572,8 +615,17 @@ static void BuildSellStream(Ctx* ctx, const Csr& A, Sell* S) {
 
 void BuildSell(Ctx* ctx, const Csr& A, Sell* S) { BuildSellStream(ctx, A, S); }
 
-static double* SellLaunch(Ctx* ctx, const Sell& S, const double* x, int kclass, const int* skip) {
-  double* P = GrowScratch(ctx, &ctx->sell_scratch, (size_t)S.T * S.R);
+struct SellPre {
+  const double* P = nullptr;  // planes of the previous pass, T x Cn of THIS pass
+  int T = 0;
+  double alpha = 1.0;
+  double* y = nullptr;        // receives alpha * sum_t P[t]; must be the x of this pass
+  unsigned* bar = nullptr;    // two zero-initialised words (GridBarrier)
+};
+
+static double* SellLaunch(Ctx* ctx, const Sell& S, const double* x, int kclass, const int* skip,
+                          const SellPre* pre = nullptr, bool second_buffer = false) {
+  double* P = GrowScratch(ctx, second_buffer ? &ctx->sell_scratch2 : &ctx->sell_scratch, (size_t)S.T * S.R);
   {
     ProfScope ps(ctx, kclass, 12.0 * S.nnz + 4.0 * (S.R + 1) + 8.0 * S.Cn + 8.0 * S.R);
     // bulk copies need 16-byte aligned addresses and sizes: TW is even, so only the base
@@ -586,7 +638,11 @@ static double* SellLaunch(Ctx* ctx, const Sell& S, const double* x, int kclass, 
     static int launch_no = 0;
     static DevBuf<unsigned long long> tbuf;
     unsigned long long* trace = nullptr;
-    if (trace_at >= 0 && launch_no++ == trace_at) {
+    bool step_trace = false;
+    if (unsigned long long* st = StepTraceSlot(ctx, 0, S.n_cta, pre ? "pass 2 (+pre-phase)" : "pass 1")) {
+      trace = st;
+      step_trace = true;
+    } else if (trace_at >= 0 && launch_no++ == trace_at) {
       tbuf.alloc(ctx, (size_t)S.n_cta * 4);
       std::vector<unsigned long long> init((size_t)S.n_cta * 4, 0ull);
       for (int g = 0; g < S.n_cta; g++) init[g * 4 + 2] = ~0ull;
@@ -596,7 +652,7 @@ static double* SellLaunch(Ctx* ctx, const Sell& S, const double* x, int kclass, 
     }
     using KernT = void (*)(int, int, int, const int32_t*, const int32_t*, const SellStream*, const int32_t*,
                            const double*, const uint16_t*, const int32_t*, const double*, double*, int, const int*,
-                           unsigned long long*);
+                           unsigned long long*, const double*, int, double, double*, unsigned*);
     KernT kern = nullptr;
     switch (S.nw) {
       case 16: kern = trace ? SellStreamKernel<16, 8, true> : SellStreamKernel<16, 8, false>; break;
@@ -621,9 +677,15 @@ static double* SellLaunch(Ctx* ctx, const Sell& S, const double* x, int kclass, 
     const SellStream* a_st = S.streams.p;
     const double* a_val = S.val.p;
     const uint16_t* a_idx = S.idx.p;
+    const double* pre_P = pre ? pre->P : nullptr;
+    const int pre_T = pre ? pre->T : 0;
+    const double pre_alpha = pre ? pre->alpha : 1.0;
+    double* pre_y = pre ? pre->y : nullptr;
+    unsigned* pre_bar = pre ? pre->bar : nullptr;
+    if (pre) EPS_CHECK(pre->y == x && pre->bar && S.n_cta <= ctx->sm_count, "pre-phase of the stream kernel: bad arguments");
     CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, S.R, S.Cn, S.TW, a_cv, a_vt, a_st, a_sl, a_val, a_idx, a_ri, x, P,
-                                  use_tma, skip, trace));
-    if (trace) {
+                                  use_tma, skip, trace, pre_P, pre_T, pre_alpha, pre_y, pre_bar));
+    if (trace && !step_trace) {
       std::vector<unsigned long long> h((size_t)S.n_cta * 4);
       tbuf.download(h.data(), h.size());
       unsigned long long t0 = ~0ull;
@@ -651,6 +713,14 @@ static double* SellLaunch(Ctx* ctx, const Sell& S, const double* x, int kclass, 
 const double* SellApplyPlanes(Ctx* ctx, const Sell& S, const double* x, int kclass, const int* skip) {
   EPS_CHECK(S.R > 0, "empty sparse map");
   return SellLaunch(ctx, S, x, kclass, skip);
+}
+
+const double* SellApplyPlanesAfter(Ctx* ctx, const Sell& S, double* x, const double* prevP, int prevT, double alpha,
+                                   unsigned* bar, int kclass, const int* skip) {
+  EPS_CHECK(S.R > 0, "empty sparse map");
+  SellPre pre;
+  pre.P = prevP; pre.T = prevT; pre.alpha = alpha; pre.y = x; pre.bar = bar;
+  return SellLaunch(ctx, S, x, kclass, skip, &pre, true);
 }
 
 void SellApply(Ctx* ctx, const Sell& S, double alpha, const double* x, double beta, double* y, int kclass,
