@@ -114,10 +114,21 @@ static void PeerSetup(Ctx* ctx, int64_t n, PeerBuf* out) {
   const size_t recv_bytes = sizeof(double) * 2 * (size_t)G * n;
   const size_t ll1_bytes = sizeof(uint4) * 2 * (size_t)G * n, ll2_bytes = sizeof(uint4) * 2 * (size_t)n;
   const bool use_ll = !getenv("EPS_PEER_LL") || atoi(getenv("EPS_PEER_LL")) != 0;
-  const size_t bytes = head + recv_bytes + (use_ll ? ll1_bytes + ll2_bytes : 0);
+  const bool use_sn = use_ll && (!getenv("EPS_PEER_SENTINEL") || atoi(getenv("EPS_PEER_SENTINEL")) != 0);
+  const size_t sn1_bytes = sizeof(double) * 2 * (size_t)G * n, sn2_bytes = sizeof(double) * 2 * (size_t)n;
+  const size_t sn_off = head + recv_bytes + (use_ll ? ll1_bytes + ll2_bytes : 0);
+  const size_t bytes = sn_off + (use_sn ? sn1_bytes + sn2_bytes : 0);
   CUDA_CHECK(cudaMalloc(&out->block, bytes));
   ctx->bytes_allocated += bytes;
   CUDA_CHECK(cudaMemsetAsync(out->block, 0, bytes, ctx->stream));
+  if (use_sn) {
+    // 64-bit pattern fill of the sentinel inboxes (cudaMemset only knows bytes / 32-bit words: two D2D copies
+    // from a host vector would do as well; the driver's 32-bit 2D memset writes the two halves)
+    std::vector<unsigned long long> fill((sn1_bytes + sn2_bytes) / 8, kPeerSentinel);
+    CUDA_CHECK(cudaMemcpyAsync(static_cast<char*>(out->block) + sn_off, fill.data(), sn1_bytes + sn2_bytes,
+                               cudaMemcpyHostToDevice, ctx->stream));
+    CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+  }
   cudaIpcMemHandle_t mine;
   int ok = cudaIpcGetMemHandle(&mine, out->block) == cudaSuccess ? 1 : 0;
   if (!ok) cudaGetLastError();
@@ -159,6 +170,8 @@ static void PeerSetup(Ctx* ctx, int64_t n, PeerBuf* out) {
     out->x.recv[r] = reinterpret_cast<double*>(base + head);
     out->x.ll1[r] = use_ll ? reinterpret_cast<uint4*>(base + head + recv_bytes) : nullptr;
     out->x.ll2[r] = use_ll ? reinterpret_cast<uint4*>(base + head + recv_bytes + ll1_bytes) : nullptr;
+    out->x.sn1[r] = use_sn ? reinterpret_cast<double*>(base + sn_off) : nullptr;
+    out->x.sn2[r] = use_sn ? reinterpret_cast<double*>(base + sn_off + sn1_bytes) : nullptr;
   }
   out->counter = reinterpret_cast<unsigned*>(static_cast<char*>(out->block) + 2048);
   out->seq = 0;

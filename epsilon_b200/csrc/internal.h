@@ -229,6 +229,9 @@ void BuildSell(Ctx* ctx, const Csr& A, Sell* S);
 // all ranks obtain bit-identical sums.  Passed to kernels by value.
 constexpr int kMaxRanks = 8;
 constexpr int kPeerMaxCtas = 256;  // CTAs of the fused exchange kernel (one per SM)
+// "nothing has arrived yet": a signalling-NaN bit pattern no arithmetic produces (operations return the
+// canonical quiet NaN), so a partial sum that is itself NaN still reads as "arrived"
+constexpr unsigned long long kPeerSentinel = 0xFFF4DEADBEEFCAFEull;
 struct PeerXchg {
   double* recv[kMaxRanks] = {};              // recv[r]: rank r's buffer [2][G][n], mapped here
   unsigned long long* flag[kMaxRanks] = {};  // flag[r]: rank r's flags [2][G]
@@ -237,6 +240,10 @@ struct PeerXchg {
   // own sequence number, so a packet needs no fence and no separate flag)
   uint4* ll1[kMaxRanks] = {};                // ll1[r]: rank r's reduce-scatter inbox [2][G][n]
   uint4* ll2[kMaxRanks] = {};                // ll2[r]: rank r's all-gather inbox [2][n]
+  // sentinel inboxes: plain 8-byte doubles, a slot holds kPeerSentinel until its value lands and is put back
+  // to the sentinel by the reader (half the NVLink bytes of the 16-byte packets)
+  double* sn1[kMaxRanks] = {};               // sn1[r]: rank r's reduce-scatter inbox [2][G][n]
+  double* sn2[kMaxRanks] = {};               // sn2[r]: rank r's all-gather inbox [2][n]
   int G = 0, rank = 0;
   int64_t n = 0;   // slot stride (capacity); vectors of up to n entries fit
 };

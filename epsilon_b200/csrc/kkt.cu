@@ -349,8 +349,36 @@ CgFusedTail2Kernel(int64_t n, int T, const double* __restrict__ planes, double a
   per = (per + 1) & ~(int64_t)1;
   const int64_t lo = min(n, (int64_t)c * per), hi = min(n, lo + per);
   const bool ll = px.G > 1 && px.ll1[0] != nullptr;
+  const bool sn = ll && px.sn1[0] != nullptr;   // same two-shot exchange, 8-byte sentinel slots instead of 16-byte packets
   const unsigned seq32 = (unsigned)xseq;
-  if (ll) {
+  if (sn) {
+    if (!finished) {
+      for (int64_t i = lo + threadIdx.x; i < hi; i += 2 * kTailBlock) {
+        const int64_t j = i + kTailBlock;
+        double s0 = 0.0, s1 = 0.0;
+#pragma unroll 8
+        for (int t = 0; t < T; t++) {
+          s0 += __ldcg(planes + (size_t)t * n + i);
+          if (j < hi) s1 += __ldcg(planes + (size_t)t * n + j);
+        }
+        SnStore(px.sn1[(int)((i >> 6) % px.G)] + ((size_t)parity * px.G + px.rank) * px.n + i, alpha * s0);
+        if (j < hi) SnStore(px.sn1[(int)((j >> 6) % px.G)] + ((size_t)parity * px.G + px.rank) * px.n + j, alpha * s1);
+      }
+      EPS_TT(1);
+      const int64_t ch_lo = lo >> 6, ch_hi = (hi + 63) >> 6;
+      int64_t first = ch_lo + ((px.rank - ch_lo % px.G) + px.G) % px.G;
+      for (int64_t k = threadIdx.x;; k += kTailBlock) {
+        const int64_t ch = first + (k >> 6) * px.G;
+        if (ch >= ch_hi) break;
+        const int64_t i = (ch << 6) + (k & 63);
+        if (i < lo || i >= hi) continue;
+        const double sum = SnTakeRanks(px.sn1[px.rank] + (size_t)parity * px.G * px.n + i, (size_t)px.n, px.G);
+        for (int q = 0; q < px.G; q++)
+          SnStore(px.sn2[(px.rank + q) % px.G] + (size_t)parity * px.n + i, sum);
+      }
+      EPS_TT(2);
+    }
+  } else if (ll) {
     // two-shot exchange with flag-in-data packets.  Ownership is by 64-element chunk, chunk k belongs to rank
     // k % G, so EVERY CTA of every rank owns ~1/G of its own slice: all 148 CTAs take part in the owner step
     // (with whole slices owned by rank c % G, 7 of 8 CTAs idled while the owners walked their slice twice).
@@ -407,28 +435,74 @@ CgFusedTail2Kernel(int64_t n, int T, const double* __restrict__ planes, double a
   }
   if (finished) return;
   const double thresh = scal[1];
+  // A thread owns elements i0 = lo + tid and i1 = i0 + kTailBlock (slices of up to 2 * kTailBlock elements, i.e.
+  // n <= 1024 * gridDim: everything of both elements is loaded up front -- one L2 round trip instead of one per
+  // operand -- and p, r, w stay in registers across the barrier); longer slices take the generic loop below.
+  const bool two = hi - lo <= 2 * kTailBlock;
   double v[4] = {0.0, 0.0, 0.0, 0.0};
-  for (int64_t i = lo + threadIdx.x; i < hi; i += kTailBlock) {
-    const double pi = p[i], ri = r[i];
-    double wi;
-    if (ll) {
-      // (the packets of a thread's later elements are already on their way while it spins on this one)
-      wi = LlLoad(px.ll2[px.rank] + (size_t)parity * px.n + i, seq32) + dg[i] * pi;
+  double pk[2] = {0.0, 0.0}, rk[2] = {0.0, 0.0}, wk[2] = {0.0, 0.0};
+  if (two) {
+    const int64_t i0 = lo + threadIdx.x, i1 = i0 + kTailBlock;
+    const bool h0 = i0 < hi, h1 = i1 < hi;
+    double dk[2] = {0.0, 0.0}, sk[2] = {0.0, 0.0};
+    if (h0) { pk[0] = p[i0]; rk[0] = r[i0]; dk[0] = dg[i0]; }
+    if (h1) { pk[1] = p[i1]; rk[1] = r[i1]; dk[1] = dg[i1]; }
+    if (sn) {
+      if (h0) sk[0] = SnTake(px.sn2[px.rank] + (size_t)parity * px.n + i0);
+      if (h1) sk[1] = SnTake(px.sn2[px.rank] + (size_t)parity * px.n + i1);
+    } else if (ll) {
+      if (h0) sk[0] = LlLoad(px.ll2[px.rank] + (size_t)parity * px.n + i0, seq32);
+      if (h1) sk[1] = LlLoad(px.ll2[px.rank] + (size_t)parity * px.n + i1, seq32);
     } else if (px.G > 1) {
-      wi = PeerSum(px, xseq, i) + dg[i] * pi;
+      if (h0) sk[0] = PeerSum(px, xseq, i0);
+      if (h1) sk[1] = PeerSum(px, xseq, i1);
     } else {
-      double s = 0.0;
 #pragma unroll 8
-      for (int t = 0; t < T; t++) s += __ldcg(planes + (size_t)t * n + i);
-      wi = alpha * s + dg[i] * pi;
+      for (int t = 0; t < T; t++) {
+        if (h0) sk[0] += __ldcg(planes + (size_t)t * n + i0);
+        if (h1) sk[1] += __ldcg(planes + (size_t)t * n + i1);
+      }
+      sk[0] *= alpha; sk[1] *= alpha;
     }
-    w[i] = wi;
-    v[0] += pi * wi;
-    v[1] += ri * wi;
-    v[2] += wi * wi;
-    v[3] += ri * ri;
+#pragma unroll
+    for (int k = 0; k < 2; k++) {
+      wk[k] = sk[k] + dk[k] * pk[k];
+      v[0] += pk[k] * wk[k];
+      v[1] += rk[k] * wk[k];
+      v[2] += wk[k] * wk[k];
+      v[3] += rk[k] * rk[k];
+    }
+  } else {
+    for (int64_t i = lo + threadIdx.x; i < hi; i += kTailBlock) {
+      const double pi = p[i], ri = r[i];
+      double wi;
+      if (sn) {
+        wi = SnTake(px.sn2[px.rank] + (size_t)parity * px.n + i) + dg[i] * pi;
+      } else if (ll) {
+        wi = LlLoad(px.ll2[px.rank] + (size_t)parity * px.n + i, seq32) + dg[i] * pi;
+      } else if (px.G > 1) {
+        wi = PeerSum(px, xseq, i) + dg[i] * pi;
+      } else {
+        double s = 0.0;
+#pragma unroll 8
+        for (int t = 0; t < T; t++) s += __ldcg(planes + (size_t)t * n + i);
+        wi = alpha * s + dg[i] * pi;
+      }
+      w[i] = wi;
+      v[0] += pi * wi;
+      v[1] += ri * wi;
+      v[2] += wi * wi;
+      v[3] += ri * ri;
+    }
   }
   EPS_TT(3);
+  // x of both elements: requested now, needed after the barrier
+  double xk[2] = {0.0, 0.0};
+  if (two) {
+    const int64_t i0 = lo + threadIdx.x, i1 = i0 + kTailBlock;
+    if (i0 < hi) xk[0] = x[i0];
+    if (i1 < hi) xk[1] = x[i1];
+  }
   BlockSum<4>(v, smem);
   if (threadIdx.x == 0) {
 #pragma unroll
@@ -455,12 +529,26 @@ CgFusedTail2Kernel(int64_t n, int T, const double* __restrict__ planes, double a
   const double a = pw != 0.0 ? rr / pw : 0.0;
   const double rr_new = fmax(rr - 2.0 * a * rw + a * a * ww, 0.0);
   const double b = rr != 0.0 ? rr_new / rr : 0.0;
-  for (int64_t i = lo + threadIdx.x; i < hi; i += kTailBlock) {
-    const double pi = p[i];
-    x[i] += a * pi;
-    const double t = r[i] - a * w[i];
-    r[i] = t;
-    p[i] = t + b * pi;
+  if (two) {
+    const int64_t i0 = lo + threadIdx.x, i1 = i0 + kTailBlock;
+#pragma unroll
+    for (int k = 0; k < 2; k++) {
+      const int64_t i = k ? i1 : i0;
+      if (i < hi) {
+        x[i] = xk[k] + a * pk[k];
+        const double t = rk[k] - a * wk[k];
+        r[i] = t;
+        p[i] = t + b * pk[k];
+      }
+    }
+  } else {
+    for (int64_t i = lo + threadIdx.x; i < hi; i += kTailBlock) {
+      const double pi = p[i];
+      x[i] += a * pi;
+      const double t = r[i] - a * w[i];
+      r[i] = t;
+      p[i] = t + b * pi;
+    }
   }
   EPS_TT(6);
   if (c == 0 && threadIdx.x == 0) {

@@ -62,6 +62,48 @@ __device__ __forceinline__ double LlLoad(const uint4* p, unsigned seq) {
   return __longlong_as_double((long long)(((unsigned long long)b << 32) | a));
 }
 
+// ---- sentinel slots ------------------------------------------------------------------------------
+__device__ __forceinline__ void SnStore(double* p, double v) {
+  asm volatile("st.volatile.global.f64 [%0], %1;" ::"l"(p), "d"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long SnPeek(const double* p) {
+  unsigned long long v;
+  asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void SnReset(double* p) {
+  asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(p), "l"(kPeerSentinel) : "memory");
+}
+// Waits for the slot, returns its value and hands the slot back (sentinel) for the exchange after next.
+__device__ __forceinline__ double SnTake(double* p) {
+  unsigned long long v;
+  do { v = SnPeek(p); } while (v == kPeerSentinel);
+  SnReset(p);
+  return __longlong_as_double((long long)v);
+}
+// Sum in rank order of the G slots base[q * stride]; all loads of a poll are in flight together.
+__device__ __forceinline__ double SnTakeRanks(double* base, size_t stride, int G) {
+  unsigned long long v[kMaxRanks];
+  bool ok;
+  do {
+    ok = true;
+#pragma unroll
+    for (int q = 0; q < kMaxRanks; q++)
+      if (q < G) v[q] = SnPeek(base + (size_t)q * stride);
+#pragma unroll
+    for (int q = 0; q < kMaxRanks; q++)
+      if (q < G) ok = ok && v[q] != kPeerSentinel;
+  } while (!ok);
+  double s = 0.0;
+#pragma unroll
+  for (int q = 0; q < kMaxRanks; q++)
+    if (q < G) {
+      s += __longlong_as_double((long long)v[q]);
+      SnReset(base + (size_t)q * stride);
+    }
+  return s;
+}
+
 __device__ __forceinline__ uint4 LlPeek(const uint4* p) {
   uint4 v;
   asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");

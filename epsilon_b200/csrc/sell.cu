@@ -225,6 +225,23 @@ __global__ void StreamFillKernel(int R, int TW, int n_slices, int NW, VisitTab v
   }
 }
 
+// The x tile as several bulk copies in flight at once (all completing on the same mbarrier): one 200 KB request
+// is walked by the copy engine front to back, several smaller ones overlap their L2 round trips.
+// (experiment knob EPS_SELL_TMA_CHUNK: bytes per request, 0 = one request)
+__device__ __forceinline__ void StageTile(uint32_t dst, const double* src, uint32_t bytes, uint32_t bar_a, uint32_t chunk) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_a), "r"(bytes) : "memory");
+  if (chunk == 0 || chunk >= bytes) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar_a) : "memory");
+    return;
+  }
+  for (uint32_t off = 0; off < bytes; off += chunk) {
+    const uint32_t len = min(chunk, bytes - off);
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst + off), "l"(reinterpret_cast<const char*>(src) + off), "r"(len), "r"(bar_a) : "memory");
+  }
+}
+
 __device__ __forceinline__ unsigned long long GlobalTimer() {
   unsigned long long t;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
@@ -390,11 +407,7 @@ SellStreamKernel(int R, int Cn, int TW, const int32_t* __restrict__ cta_visit,
       if (vi != v_lo && use_tma && threadIdx.x == 0) {
         // one TMA bulk copy of the x tile (cp.async.bulk, completion on an mbarrier), issued
         // before anything else so that it overlaps the first loads of the streams
-        const uint32_t bytes = (uint32_t)cw * 8u;
-        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_a), "r"(bytes) : "memory");
-        asm volatile(
-            "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-            ::"r"(SmemAddr(xs)), "l"(x + c0), "r"(bytes), "r"(bar_a) : "memory");
+        StageTile(SmemAddr(xs), x + c0, (uint32_t)cw * 8u, bar_a, (uint32_t)(use_tma >> 1) << 4);
       }
     }
     // this warp's stream: two batches of loads in flight before the x tile is needed
@@ -420,11 +433,7 @@ SellStreamKernel(int R, int Cn, int TW, const int32_t* __restrict__ cta_visit,
       if (skip && *skip) return;  // speculative launch after the CG loop converged (kkt.cu)
       if (preP) pre_phase();
       if (use_tma && threadIdx.x == 0) {
-        const uint32_t bytes = (uint32_t)cw * 8u;
-        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_a), "r"(bytes) : "memory");
-        asm volatile(
-            "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-            ::"r"(SmemAddr(xs)), "l"(x + c0), "r"(bytes), "r"(bar_a) : "memory");
+        StageTile(SmemAddr(xs), x + c0, (uint32_t)cw * 8u, bar_a, (uint32_t)(use_tma >> 1) << 4);
       }
     }
     if (restage) {
@@ -484,7 +493,14 @@ static void BuildSellStream(Ctx* ctx, const Csr& A, Sell* S) {
   EPS_CHECK(NW == 16 || NW == 20 || NW == 24 || NW == 32, "EPS_SELL_WARPS must be 16, 20, 24 or 32");
   S->nw = NW;
   S->R = R; S->Cn = Cn; S->nnz = A.nnz;
-  const int T = (Cn + kMaxTile - 1) / kMaxTile;
+  // Tile width.  200 KB tiles (25 600 doubles) leave the SM 27 KB of L1 for the slice descriptors and the
+  // partial-sum stores; 160 KB tiles measured 5.7 % faster on the 1M x 100k matrix (184.4 vs 174.4 it/s) although
+  // they add a plane.  On small matrices the 8*TW bytes every CTA stages before it can start weigh more: the
+  // 125k x 100k shard of an 8-GPU run is fastest at 100 KB (473.7 vs 454.4 it/s at 160 KB).  So: staging at most
+  // ~10 % of the bytes a CTA streams, between 12 800 and 20 000 doubles.  EPS_SELL_TILE overrides.
+  int max_tile = (int)std::min<double>(20000.0, std::max<double>(12800.0, 0.1 * 10.0 * (double)A.nnz / ctx->sm_count / 8.0));
+  if (getenv("EPS_SELL_TILE")) max_tile = std::min(kMaxTile, std::max(256, atoi(getenv("EPS_SELL_TILE"))));
+  const int T = (Cn + max_tile - 1) / max_tile;
   int TW = (Cn + T - 1) / T;
   TW = (TW + 1) / 2 * 2;  // keep tile starts 16-byte aligned for the bulk copy
   S->T = T; S->TW = TW;
@@ -631,7 +647,9 @@ static double* SellLaunch(Ctx* ctx, const Sell& S, const double* x, int kclass, 
     // bulk copies need 16-byte aligned addresses and sizes: TW is even, so only the base
     // pointer and the width of the last tile can break that
     const int last = S.Cn - (S.T - 1) * S.TW;
-    const int use_tma = ((reinterpret_cast<uintptr_t>(x) & 15) == 0 && last % 2 == 0) ? 1 : 0;
+    static const int tma_chunk = getenv("EPS_SELL_TMA_CHUNK") ? atoi(getenv("EPS_SELL_TMA_CHUNK")) : 0;
+    // bit 0: stage by bulk copies; bits 1..: bytes per request / 16 (0 = the whole tile in one request)
+    const int use_tma = ((reinterpret_cast<uintptr_t>(x) & 15) == 0 && last % 2 == 0) ? (1 | ((tma_chunk / 16) << 1)) : 0;
     {
     // EPS_SELL_TRACE=<launch number>: per-CTA timeline of that launch on stderr (diagnostics)
     static const int trace_at = getenv("EPS_SELL_TRACE") ? atoi(getenv("EPS_SELL_TRACE")) : -1;
