@@ -300,15 +300,22 @@ def main_ours(args):
     if not args.no_e2e:
         # one untimed whole solve first: CUDA module loading, first-touch allocations and the
         # cuda/cub kernels of the ingest path are a per-process cost, not a per-solve one
-        with ProxADMMSolver(prob, params, ctx=ctx, sharded_args=sharded) as s0:
-            s0.solve()
-        ctx.synchronize()
+        # (two of them: the first construction after a tear-down re-shapes the stream-ordered memory pool once --
+        # 14-23 ms of the transposition phase on multi-GPU boxes, EPS_TIMING=1 -- and a long-lived process pays
+        # that once, not per solve)
+        for _ in range(2):
+            with ProxADMMSolver(prob, params, ctx=ctx, sharded_args=sharded) as s0:
+                s0.solve()
+            ctx.synchronize()
         barrier()
         t0 = time.time()
         s = ProxADMMSolver(prob, params, ctx=ctx, sharded_args=sharded)
+        t_built = time.time()
         x = s.solve()
         ctx.synchronize()
-        t_e2e = max_over_ranks(time.time() - t0)
+        t_done = time.time()
+        t_e2e = max_over_ranks(t_done - t0)
+        t_construct, t_solve = max_over_ranks(t_built - t0), max_over_ranks(t_done - t_built)
         st = s.status.as_dict()
         iters = st["iterations_run"]
         obj = info["objective"](x)
@@ -322,8 +329,10 @@ def main_ours(args):
                 parity["ok"] = bool(parity["ok"] and parity["ranks_agree"] and st["cg_unconverged"] == 0)
         e2e = {"value": iters / t_e2e, "unit": "iterations/s",
                "h2d_bytes_per_step": h2d_bytes / iters, "d2h_bytes_per_step": 8 * 2 * args.n / iters,
-               "warmup_solves": 1, "host_buffers": "pinned (cudaHostAlloc)",
+               "warmup_solves": 2, "host_buffers": "pinned (cudaHostAlloc)",
                "time_to_tol_s": t_e2e, "init_s": st["init_ms"] / 1e3, "loop_s": st["loop_ms"] / 1e3,
+               # max over ranks: upload + on-device transposition + SELL build + Init | iterations + download of x
+               "construct_s": t_construct, "solve_s": t_solve,
                "iterations": iters, "num_iterations": st["num_iterations"], "state": st["state"],
                "cg_iterations": st["cg_iterations"], "objective": obj,
                "r_norm": st["r_norm"], "s_norm": st["s_norm"]}

@@ -154,6 +154,22 @@ __global__ void CutKernel(int64_t TR, int G, const int64_t* __restrict__ csum, i
   cut[g] = (int32_t)lo;
 }
 
+// Cut positions for explicit cost targets (no-span assignment of CTAs to tiles): cut[g] = first index whose
+// running cost reaches target[g], or forced[g] when that is >= 0 (tile boundaries).
+__global__ void CutTargetsKernel(int64_t TR, int G, const int64_t* __restrict__ csum, const int64_t* __restrict__ target,
+                                 const int64_t* __restrict__ forced, int32_t* __restrict__ cut) {
+  const int g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g > G) return;
+  if (forced[g] >= 0) { cut[g] = (int32_t)forced[g]; return; }
+  const int64_t t = target[g];
+  int64_t lo = 0, hi = TR;
+  while (lo < hi) {
+    const int64_t mid = (lo + hi) >> 1;
+    if (csum[mid] < t) lo = mid + 1; else hi = mid;
+  }
+  cut[g] = (int32_t)lo;
+}
+
 // Rows are sorted by length inside windows of kSortWindow consecutive rows of a visit, not
 // over the whole visit: a warp's slices then walk the visit's rows window by window, so the
 // 8-byte partial sums a CTA scatters into P fall into a few 32 KB windows at a time and complete
@@ -522,8 +538,50 @@ static void BuildSellStream(Ctx* ctx, const Csr& A, Sell* S) {
     DevBuf<char> tmp(ctx, bytes);
     CUDA_CHECK(cub::DeviceScan::InclusiveSum(tmp.p, bytes, cost, csum.p, (int)TR, ctx->stream));
     DevBuf<int32_t> dcut(ctx, G + 1);
-    CutKernel<<<(G + 1 + 255) / 256, 256, 0, ctx->stream>>>(TR, G, csum.p, dcut.p);
+    // With few tiles every CTA gets rows of ONE tile (whole CTAs per tile, largest-remainder rounding): a range
+    // that spills a handful of rows into the next tile pays a full restaging of x for them and finishes last
+    // (8-GPU shard: the slowest CTA ended 4 us after the median one, and every rank waits for the slowest CTA of
+    // the slowest rank).  With many tiles (T > G/8) whole CTAs per tile would cost more balance than restaging.
+    const bool no_span = T > 1 && T <= G / 8 && !getenv("EPS_SELL_SPAN");
+    if (no_span) {
+      std::vector<int64_t> tile_end(T);
+      for (int t = 0; t < T; t++)
+        CUDA_CHECK(cudaMemcpyAsync(&tile_end[t], csum.p + ((int64_t)(t + 1) * R - 1), sizeof(int64_t),
+                                   cudaMemcpyDeviceToHost, ctx->stream));
+      CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+      std::vector<double> cost_t(T);
+      double total = 0;
+      for (int t = 0; t < T; t++) { cost_t[t] = (double)(tile_end[t] - (t ? tile_end[t - 1] : 0)); total += cost_t[t]; }
+      std::vector<int> share(T, 1);
+      int left = G - T;
+      std::vector<std::pair<double, int>> frac;
+      for (int t = 0; t < T; t++) {
+        const double want = total > 0 ? cost_t[t] / total * G : (double)G / T;
+        const int extra = std::max(0, (int)std::floor(want) - 1);
+        share[t] += std::min(extra, left);
+        left -= std::min(extra, left);
+        frac.push_back({want - std::floor(want), t});
+      }
+      std::sort(frac.begin(), frac.end(), [](const auto& a, const auto& b) { return a.first > b.first || (a.first == b.first && a.second < b.second); });
+      for (size_t k = 0; left > 0; k = (k + 1) % frac.size()) { share[frac[k].second]++; left--; }
+      std::vector<int64_t> target(G + 1, 0), forced(G + 1, -1);
+      int g = 0;
+      for (int t = 0; t < T; t++) {
+        const int64_t base = t ? tile_end[t - 1] : 0;
+        forced[g] = (int64_t)t * R;
+        for (int j = 1; j < share[t]; j++) target[g + j] = base + (int64_t)(cost_t[t] * j / share[t]);
+        g += share[t];
+      }
+      forced[G] = TR;
+      DevBuf<int64_t> dt(ctx, G + 1), df(ctx, G + 1);
+      dt.upload(target.data(), G + 1);
+      df.upload(forced.data(), G + 1);
+      CutTargetsKernel<<<(G + 1 + 255) / 256, 256, 0, ctx->stream>>>(TR, G, csum.p, dt.p, df.p, dcut.p);
+    } else {
+      CutKernel<<<(G + 1 + 255) / 256, 256, 0, ctx->stream>>>(TR, G, csum.p, dcut.p);
+    }
     dcut.download(cut.data(), G + 1);
+    for (int g = 1; g <= G; g++) cut[g] = std::max(cut[g], cut[g - 1]);   // monotone whatever the rounding did
   }
   // visits: the part of each CTA's range inside one tile
   std::vector<int32_t> lin0, slice_base, vtile, cta_visit(G + 1);

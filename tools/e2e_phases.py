@@ -16,7 +16,8 @@ from epsilon_b200.solver import Context, ProxADMMSolver  # noqa: E402
 
 
 def main():
-    m, n, density = 1_000_000, 100_000, 1e-3
+    m = int(sys.argv[1]) if len(sys.argv) > 1 else 1_000_000
+    n, density = 100_000, 1e-3
     prob, info = problems.lasso_sparse_panels(m, n, density, panels=8, my_panels=range(8), seed=0,
                                               allreduce=lambda a: a)
     a = info["A"]
@@ -25,7 +26,7 @@ def main():
     a.data, a.indices, a.indptr = (t.numpy() for t in pinned)
     ctx = Context(0)
     out = []
-    for rep in range(4):
+    for rep in range(int(sys.argv[2]) if len(sys.argv) > 2 else 4):
         ctx.synchronize()
         t0 = time.time()
         s = ProxADMMSolver(prob, {"cg_tol": 1e-12}, ctx=ctx)
