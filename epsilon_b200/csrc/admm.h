@@ -52,6 +52,7 @@ struct Stage {
   int64_t total = 0;
   int max_len = 0;
   DevBuf<double> tv_work;
+  unsigned tv_tag = 0;          // last round tag of the TV solver's slot maxima (tv1d_par.cu)
 };
 
 }  // namespace eps

@@ -645,7 +645,7 @@ void eps_solver::ResetVariables() {
   x.zero();
   ybuf[0].zero();
   ybuf[1].zero();
-  for (auto& stp : stages) stp->tv_work.zero();  // cold active set for the TV solver
+  for (auto& stp : stages) { stp->tv_work.zero(); stp->tv_tag = 0; }  // cold active set for the TV solver
   parity = 0;
   iter = 0;
   started = false;

@@ -39,7 +39,8 @@ void Norm2ProxStep(Ctx* ctx, const ElemSeg* segs_dev, int nseg, int max_len, con
                    double* u, const double* y_old, double* y_new, double* x);
 // TOTAL_VARIATION_1D for one segment (host copy of the segment passed by value).
 void Tv1dProxStep(Ctx* ctx, const ElemSeg& seg, const double* consts, double* u, const double* y_old,
-                  double* y_new, double* x, double* work /* 9*len doubles */);
+                  double* y_new, double* x, double* work /* Tv1dWorkDoubles(len) */,
+                  unsigned* tag_state /* host word kept with `work`: round tags of the slot maxima */);
 size_t Tv1dWorkDoubles(int64_t len);
 
 // dst[a_off + j] += c1*src1[b_off + j] + c2*src2[b_off + j]   (src2 may be null)

@@ -20,7 +20,7 @@
 // rounding: the prefix sums are carried in double-double, so group sums are exact to ~1e-30).
 // Cold starts take O(log(#groups)) rounds (splits only), warm starts (the active set of the
 // previous ADMM iteration is kept) 1-3.  If the loop has not settled after kMaxRounds the
-// caller falls back to the sequential dynamic program (tv1d.cu); nothing is approximated.
+// caller reports EPS_ERR_NUMERIC (tv1d.cu); nothing is approximated and there is no second algorithm.
 #include <cub/cub.cuh>
 #include <thrust/iterator/reverse_iterator.h>
 
@@ -32,7 +32,15 @@ namespace eps {
 namespace {
 
 constexpr int kTvpBlock = 256;
-constexpr int kMaxRounds = 120;
+constexpr int kMaxRounds = 400;
+
+// Per-group maxima live in slots that are never cleared: a slot holds (round tag << 40 | top 39 bits of the
+// positive double), so an entry of an earlier round loses against any entry of the current one.  (Clearing two
+// slot arrays cost 16n bytes per round.)  Violations that agree in their top 39 bits tie and are both activated,
+// which the algorithm allows: every boundary with z_k > lam may be pinned, the merge step releases wrong pins.
+__device__ __forceinline__ unsigned long long PackSlot(unsigned tag, double v) {
+  return ((unsigned long long)tag << 40) | ((unsigned long long)__double_as_longlong(v) >> 24);
+}
 
 struct DD { double hi, lo; };
 
@@ -104,7 +112,7 @@ __device__ __forceinline__ double GroupValue(const Group& g, const DD* __restric
 __global__ void __launch_bounds__(kTvpBlock)
 TvpViolationKernel(int n, double lam, const DD* __restrict__ R, const int8_t* __restrict__ act,
                    const int* __restrict__ lastb, const int* __restrict__ nextr, double* __restrict__ z,
-                   unsigned long long* __restrict__ slot_pos, unsigned long long* __restrict__ slot_neg) {
+                   unsigned long long* __restrict__ slot_pos, unsigned long long* __restrict__ slot_neg, unsigned tag) {
   const int m = n - 1;
   const int k = blockIdx.x * kTvpBlock + threadIdx.x;
   const int lane = threadIdx.x & 31;
@@ -135,23 +143,20 @@ TvpViolationKernel(int n, double lam, const DD* __restrict__ R, const int8_t* __
   const int pg = __shfl_up_sync(kFull, gid, 1);
   const bool head = lane == 0 || pg != gid;
   if (head && gid >= 0) {
-    if (vp > 0.0) atomicMax(&slot_pos[gid], (unsigned long long)__double_as_longlong(vp));
-    if (vn > 0.0) atomicMax(&slot_neg[gid], (unsigned long long)__double_as_longlong(vn));
+    if (vp > 0.0) atomicMax(&slot_pos[gid], PackSlot(tag, vp));
+    if (vn > 0.0) atomicMax(&slot_neg[gid], PackSlot(tag, vn));
   }
 }
 
-// Round, part 2: the new active set (double-buffered) and the number of changes.  Also clears
-// the slots the next round will use.
+// Round, part 2: the new active set (double-buffered) and the number of changes.
 __global__ void __launch_bounds__(kTvpBlock)
 TvpUpdateKernel(int n, double lam, const DD* __restrict__ R, const int8_t* __restrict__ act,
                 int8_t* __restrict__ act_out, const int* __restrict__ lastb, const int* __restrict__ nextr,
                 const double* __restrict__ z, const unsigned long long* __restrict__ slot_pos,
-                const unsigned long long* __restrict__ slot_neg, unsigned long long* __restrict__ clr_pos,
-                unsigned long long* __restrict__ clr_neg, int* __restrict__ changed) {
+                const unsigned long long* __restrict__ slot_neg, unsigned tag, int* __restrict__ changed) {
   const int m = n - 1;
   const int k = blockIdx.x * kTvpBlock + threadIdx.x;
   bool diff = false;
-  if (k < n) { clr_pos[k] = 0ull; clr_neg[k] = 0ull; }
   if (k < m) {
     const int8_t a = act[k];
     int8_t out = a;
@@ -166,8 +171,8 @@ TvpUpdateKernel(int n, double lam, const DD* __restrict__ R, const int8_t* __res
       const int s = lb + 1;
       const double zk = z[k];
       const double vp = zk - lam, vn = -lam - zk;
-      if (vp > 0.0 && (unsigned long long)__double_as_longlong(vp) == slot_pos[s]) out = 1;
-      else if (vn > 0.0 && (unsigned long long)__double_as_longlong(vn) == slot_neg[s]) out = -1;
+      if (vp > 0.0 && PackSlot(tag, vp) == slot_pos[s]) out = 1;
+      else if (vn > 0.0 && PackSlot(tag, vn) == slot_neg[s]) out = -1;
     }
     act_out[k] = out;
     diff = out != a;
@@ -198,7 +203,7 @@ size_t Tv1dParallelBytes(int64_t n) {
   b += 2 * Align256(sizeof(int) * n);                  // lastb, nextr
   b += 2 * Align256(n);                                // act (double-buffered; [0] persists)
   b += Align256(sizeof(double) * n);                   // z
-  b += 4 * Align256(sizeof(unsigned long long) * n);   // two slot pairs
+  b += 2 * Align256(sizeof(unsigned long long) * n);   // slot pair (never cleared: entries carry a round tag)
   b += 256;                                            // changed counter
   b += Align256((size_t)(n / 64 + 4096) * 16);         // cub temp storage (scans)
   return b;
@@ -208,7 +213,7 @@ size_t Tv1dParallelBytes(int64_t n) {
 // the sequential dynamic program).  `scratch` keeps the active set between calls (warm start);
 // it must be zeroed to start cold.
 int Tv1dParallelSolve(Ctx* ctx, int n, const double* v, double lam, double* beta, char* scratch,
-                      int* h_changed /* pinned */) {
+                      int* h_changed /* pinned */, unsigned* tag_state /* host, per solver: last round tag used */) {
   const int m = n - 1;
   char* p = scratch;
   auto take = [&](size_t bytes) { char* q = p; p += Align256(bytes); return q; };
@@ -218,8 +223,8 @@ int Tv1dParallelSolve(Ctx* ctx, int n, const double* v, double lam, double* beta
   int8_t* act0 = reinterpret_cast<int8_t*>(take(n));
   int8_t* act1 = reinterpret_cast<int8_t*>(take(n));
   double* z = reinterpret_cast<double*>(take(sizeof(double) * n));
-  unsigned long long* slots[4];
-  for (int i = 0; i < 4; i++) slots[i] = reinterpret_cast<unsigned long long*>(take(sizeof(unsigned long long) * n));
+  unsigned long long* slots[2];
+  for (int i = 0; i < 2; i++) slots[i] = reinterpret_cast<unsigned long long*>(take(sizeof(unsigned long long) * n));
   int* changed = reinterpret_cast<int*>(take(256));
   void* cub_tmp = p;
   size_t cub_bytes = Align256((size_t)(n / 64 + 4096) * 16);
@@ -235,9 +240,12 @@ int Tv1dParallelSolve(Ctx* ctx, int n, const double* v, double lam, double* beta
     EPS_CHECK(need <= cub_bytes, "cub scan scratch %zu > %zu", need, cub_bytes);
     CUDA_CHECK(cub::DeviceScan::InclusiveScan(cub_tmp, need, in, R + 1, DDAdd(), n, st));
     TvpSetZeroDD<<<1, 1, 0, st>>>(R);
-    CUDA_CHECK(cudaMemsetAsync(slots[0], 0, sizeof(unsigned long long) * n, st));
-    CUDA_CHECK(cudaMemsetAsync(slots[1], 0, sizeof(unsigned long long) * n, st));
-    ctx->count_launch(3);
+    ctx->count_launch(2);
+    if (*tag_state + kMaxRounds + 2 >= (1u << 23)) {   // tag space used up: start over on cleared slots
+      CUDA_CHECK(cudaMemsetAsync(slots[0], 0, sizeof(unsigned long long) * n, st));
+      CUDA_CHECK(cudaMemsetAsync(slots[1], 0, sizeof(unsigned long long) * n, st));
+      *tag_state = 0;
+    }
   }
   int8_t* act = act0;
   int8_t* act_other = act1;
@@ -256,13 +264,12 @@ int Tv1dParallelSolve(Ctx* ctx, int n, const double* v, double lam, double* beta
   if (m > 0) {
     for (int r = 0; r < kMaxRounds; r++) {
       ProfScope ps(ctx, KC_TV, 90.0 * n);
-      unsigned long long* sp = slots[(r & 1) * 2], *sn = slots[(r & 1) * 2 + 1];
-      unsigned long long* cp = slots[((r + 1) & 1) * 2], *cn = slots[((r + 1) & 1) * 2 + 1];
+      unsigned long long* sp = slots[0], *sn = slots[1];
+      const unsigned tag = ++(*tag_state);
       scans(act);
       CUDA_CHECK(cudaMemsetAsync(changed, 0, sizeof(int), st));
-      TvpViolationKernel<<<grid_n, kTvpBlock, 0, st>>>(n, lam, R, act, lastb, nextr, z, sp, sn);
-      TvpUpdateKernel<<<grid_n, kTvpBlock, 0, st>>>(n, lam, R, act, act_other, lastb, nextr, z, sp, sn, cp, cn,
-                                                     changed);
+      TvpViolationKernel<<<grid_n, kTvpBlock, 0, st>>>(n, lam, R, act, lastb, nextr, z, sp, sn, tag);
+      TvpUpdateKernel<<<grid_n, kTvpBlock, 0, st>>>(n, lam, R, act, act_other, lastb, nextr, z, sp, sn, tag, changed);
       ctx->count_launch(2);
       CUDA_CHECK(cudaMemcpyAsync(h_changed, changed, sizeof(int), cudaMemcpyDeviceToHost, st));
       CUDA_CHECK(cudaStreamSynchronize(st));
