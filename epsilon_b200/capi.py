@@ -107,6 +107,7 @@ SIGNATURES = {
     "eps_problem_prox_zone": (C.c_int, [_P, C.c_int, C.c_double, _DP, _DP, C.c_int]),
     "eps_problem_prox_add_arg": (C.c_int, [_P, C.c_int, C.c_int, C.POINTER(C.c_int)]),
     "eps_problem_prox_arg_sharded": (C.c_int, [_P, C.c_int, C.c_int, C.c_int64]),
+    "eps_problem_constraint_sharded": (C.c_int, [_P, C.c_int, C.c_int64]),
     "eps_problem_add_term": (C.c_int, [_P, C.c_int, C.c_int, _P, C.c_int, _DP]),
     "eps_params_default": (None, [C.POINTER(Params)]),
     "eps_solver_create": (C.c_int, [_P, C.POINTER(Params), C.POINTER(_P)]),

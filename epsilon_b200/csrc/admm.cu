@@ -58,7 +58,19 @@ void eps_solver::RunStages(const double* yo, double* yn) {
           op.kkt->Solve(rhs_n.p, xi);
           KktScalarPost(ctx, op.n, op.a, xi, us, yn + op.y_off);
         } else {
-          if (op.span_len > 0) {
+          if (op.span_len > 0 && op.a_sharded) {
+            // rows of the sharded constraints: this rank's A_r'w, summed over the ranks; replicated rows as usual
+            VecAxpby(ctx, op.span_len, 1.0, us, 1.0, yo + op.y_off, us);
+            op.A_sh.ApplyT(us, tmp_n.p);
+            AllReduceSum(ctx, tmp_n.p, op.n);
+            if (!op.A_rep.blks.empty()) {
+              op.A_rep.ApplyT(us, rhs_n.p);
+              VecAxpby(ctx, op.n, 1.0, rhs_n.p, 1.0, tmp_n.p, rhs_n.p);
+              VecAxpby(ctx, op.n, 1.0, rhs_n.p, 1.0, op.kkt->c0.p, rhs_n.p);
+            } else {
+              VecAxpby(ctx, op.n, 1.0, tmp_n.p, 1.0, op.kkt->c0.p, rhs_n.p);
+            }
+          } else if (op.span_len > 0) {
             VecAxpby(ctx, op.span_len, 1.0, us, 1.0, yo + op.y_off, us);
             op.A.ApplyT(us, rhs_n.p);
             VecAxpby(ctx, op.n, 1.0, rhs_n.p, 1.0, op.kkt->c0.p, rhs_n.p);
@@ -164,7 +176,88 @@ void eps_solver::RunIteration() {
 }
 
 // prox_admm.cc:178-217.  On entry ybuf[parity] = y, ybuf[1-parity] = y_prev.
+// ComputeResiduals (prox_admm.cc:178-217) with row-sharded constraints: every sum over constraint rows splits
+// into the rows this rank holds a shard of (summed over the ranks) and the replicated rows (counted once);
+// products with A_i' of a replicated variable that enters sharded rows are all-reduced as n-vectors.  All scalar
+// partial sums travel in ONE all-reduce.  Layout of resid_sh: [sharded | replicated] x [r^2, s_i^2[N], |A_i'u|^2[N], |y_i|^2[N]].
+void eps_solver::ComputeResidualsSharded() {
+  const double* yn = ybuf[parity].p;
+  const double* yo = ybuf[1 - parity].p;
+  const int K = 1 + 3 * N;
+  double* SH = resid_sh.p;
+  double* RP = resid_sh.p + K;
+  resid_sh.zero();
+  const int nc = (int)c_sharded.size();
+  auto rows_dot = [&](const double* v, int64_t lo, int64_t len, int64_t base, int slot) {
+    // sum over rows [lo, lo+len) of u-space (v indexed from `base`), split by constraint
+    for (int c = 0; c < nc; c++) {
+      const int64_t a = std::max(lo, constraint_off[c]), b = std::min(lo + len, constraint_off[c + 1]);
+      if (b <= a) continue;
+      VecDot(ctx, b - a, v + (a - base), v + (a - base), (c_sharded[c] ? SH : RP) + slot, true);
+    }
+  };
+  // r = || b + sum_i A x_i ||
+  VecCopy(ctx, m_total, b.p, tmp_m.p);
+  for (auto& stp : stages) {
+    Stage& st = *stp;
+    SegAxpy(ctx, st.pairs.p, st.prefix.p, (int)st.members.size(), st.total, tmp_m.p, yn, 1.0, nullptr, 0.0);
+  }
+  rows_dot(tmp_m.p, 0, m_total, 0, 0);
+  // || A x_i ||^2 = || y_i ||^2
+  for (int i = 0; i < N; i++) {
+    ProxOp& op = ops[i];
+    if (op.span_len > 0) rows_dot(yn + op.y_off, op.span_lo, op.span_len, op.span_lo, 1 + 2 * N + i);
+  }
+  // A_i' d: scalar blocks give a^2 |d_rows|^2; a replicated variable in sharded rows needs the all-reduced n-vector
+  auto at_norm = [&](ProxOp& op, const double* d, int slot) {
+    if (op.span_len == 0) return;
+    if (op.a_sharded) {
+      op.A_sh.ApplyT(d + op.span_lo, tmp_n.p);
+      AllReduceSum(ctx, tmp_n.p, op.n);
+      if (!op.A_rep.blks.empty()) op.A_rep.ApplyT(d + op.span_lo, tmp_n.p, true);
+      VecDot(ctx, op.n, tmp_n.p, tmp_n.p, RP + slot, true);
+    } else if (op.simple_scalar) {
+      rows_dot(d, op.span_lo, op.span_len, 0, slot);   // times a^2 on the host
+    } else {
+      op.A.ApplyT(d + op.span_lo, tmp_n.p);
+      VecDot(ctx, op.n, tmp_n.p, tmp_n.p, (op.local ? SH : RP) + slot, true);
+    }
+  };
+  // s^2 = sum_{i<N-1} || A_i' sum_{j>i} (y_j - y_prev_j) ||^2
+  diff_m.zero();
+  for (int i = N - 1; i >= 0; i--) {
+    ProxOp& op = ops[i];
+    if (i < N - 1) at_norm(op, diff_m.p, 1 + i);
+    if (i > 0 && op.span_len > 0) {
+      VecAxpby(ctx, op.span_len, 1.0, diff_m.p + op.span_lo, 1.0, yn + op.y_off, diff_m.p + op.span_lo);
+      VecAxpby(ctx, op.span_len, 1.0, diff_m.p + op.span_lo, -1.0, yo + op.y_off, diff_m.p + op.span_lo);
+    }
+  }
+  // || A' u ||^2 over all variables
+  for (int i = 0; i < N; i++) at_norm(ops[i], u.p, 1 + N + i);
+  AllReduceSum(ctx, SH, K);
+  std::vector<double> h(2 * K);
+  resid_sh.download(h.data(), 2 * K);
+  auto tot = [&](int slot) { return h[slot] + h[K + slot]; };
+  double s2 = 0, atu2 = 0, max_ax2 = 0;
+  for (int i = 0; i < N; i++) {
+    const double coef = ops[i].simple_scalar && !ops[i].a_sharded ? ops[i].a * ops[i].a : 1.0;
+    s2 += coef * tot(1 + i);
+    atu2 += coef * tot(1 + N + i);
+    max_ax2 = std::fmax(max_ax2, tot(1 + 2 * N + i));
+  }
+  const double rho = params.rho;
+  status.r_norm = std::sqrt(tot(0));
+  status.s_norm = rho * std::sqrt(s2);
+  status.epsilon_primal = params.abs_tol * std::sqrt((double)m_global) +
+                          params.rel_tol * std::fmax(b_norm, std::sqrt(max_ax2));
+  status.epsilon_dual = params.abs_tol * std::sqrt((double)n_total) + params.rel_tol * rho * std::sqrt(atu2);
+  status.state = (status.r_norm <= status.epsilon_primal && status.s_norm <= status.epsilon_dual)
+                     ? EPS_OPTIMAL : EPS_RUNNING;
+}
+
 void eps_solver::ComputeResiduals() {
+  if (any_sharded) { ComputeResidualsSharded(); return; }
   if (two_block) {
     // prox_admm_two_block.cc:135-156; the five sums were left in `resid` by the last iteration
     CUDA_CHECK(cudaMemcpyAsync(h_resid, resid.p, 5 * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));

@@ -18,6 +18,10 @@ struct ProxOp {
   int64_t span_lo = 0, span_len = 0;  // rows of u this operator touches (contiguous cover)
   int64_t y_off = 0;            // into each y arena
   BlockOp A;                    // span_len x n, rows relative to span_lo
+  // row-sharded constraints: A = A_sh (rows this rank holds a shard of) + A_rep (replicated rows)
+  BlockOp A_sh, A_rep;
+  bool a_sharded = false;       // replicated variables entering sharded constraints (KKT operators only)
+  bool local = false;           // a sharded variable: the operator lives on this rank's rows alone
   bool simple_scalar = false;   // A = a*I on exactly the span
   double a = 0;
   std::unique_ptr<KktSolver> kkt;
@@ -75,6 +79,11 @@ struct eps_solver {
   std::vector<double> b_host;               // constant terms of the constraints (eps_solver_set_constant)
   std::vector<double> consts_host;          // the constant arena as uploaded
   std::vector<int64_t> constraint_off;      // first row of every constraint in u-space
+  // row-sharded constraints (eps_problem_constraint_sharded)
+  bool any_sharded = false;
+  std::vector<char> c_sharded;              // per constraint
+  int64_t m_global = 0;                     // A_.m() over all ranks
+  eps::DevBuf<double> resid_sh;             // partial sums of ComputeResidualsSharded
   std::vector<double> tb_hb_host;           // two-block: constants of the user's constraints
   int parity = 0;             // ybuf[parity] holds the current y
   int iter = 0;               // next iteration index (iter_ of the reference)
@@ -104,6 +113,7 @@ struct eps_solver {
   void Iteration();          // one ADMM iteration, eager launches
   void RunIteration();       // graph replay when available
   void ComputeResiduals();
+  void ComputeResidualsSharded();
   void ResetVariables();
   // Solver::SetParameterValue for constant vectors (solver.cc:109-116): a new constant term of
   // constraint `index` (prox < 0) or of argument `index` of prox function `prox`

@@ -157,12 +157,49 @@ void eps_solver::Init(const eps_problem& original) {
     for (const Term& t : p.constraints[c].terms)
       if (t.var >= 0) var_in_constraint[t.var] = 1;
   }
+  // ---- row-sharded constraints (eps_problem_constraint_sharded): which rows are this rank's shard, which
+  // variables live on those rows, the global A_.m() / A_.n() of the tolerances (prox_admm.cc:41-42,206-207)
+  c_sharded.assign(p.constraints.size(), 0);
+  m_global = 0;
+  std::vector<int64_t> var_global(vars.size(), -1);   // global size of a sharded variable
+  for (size_t c = 0; c < p.constraints.size(); c++) {
+    const bool sh = p.constraints[c].global_rows > 0 && ctx->n_ranks > 1;
+    c_sharded[c] = sh;
+    any_sharded = any_sharded || sh;
+    m_global += sh ? p.constraints[c].global_rows : p.constraints[c].rows;
+    if (!sh) continue;
+    for (const Term& t : p.constraints[c].terms) {
+      if (t.var < 0) continue;
+      const bool diag = !t.map || t.map->kind == MK_SCALAR || t.map->kind == MK_DIAGONAL;
+      if (diag) var_global[t.var] = p.constraints[c].global_rows;   // lives on the sharded rows
+    }
+  }
+  if (any_sharded) {
+    EPS_CHECK(!two_block, "row-sharded constraints are not supported by the two-block solver");
+    EPS_CHECK(N <= 64, "row-sharded constraints: at most 64 prox functions (got %d)", N);
+    for (size_t c = 0; c < p.constraints.size(); c++)
+      for (const Term& t : p.constraints[c].terms) {
+        if (t.var < 0 || var_global[t.var] < 0) continue;
+        const bool diag = !t.map || t.map->kind == MK_SCALAR || t.map->kind == MK_DIAGONAL;
+        EPS_CHECK(c_sharded[c] && diag, "variable %s lives on the rows of a sharded constraint but also enters "
+                  "constraint %zu%s", vars[t.var].id.c_str(), c, diag ? "" : " through a general map");
+      }
+  }
   n_total = 0;
   for (size_t v = 0; v < vars.size(); v++)
-    if (var_in_constraint[v]) n_total += vars[v].size;
-  b_norm = 0;
-  for (double v : b_host) b_norm += v * v;
-  b_norm = std::sqrt(b_norm);
+    if (var_in_constraint[v]) n_total += var_global[v] >= 0 ? var_global[v] : vars[v].size;
+  {
+    double sq_sh = 0, sq_rep = 0;
+    for (size_t c = 0; c < p.constraints.size(); c++)
+      for (int64_t i = coff[c]; i < coff[c + 1]; i++) (c_sharded[c] ? sq_sh : sq_rep) += b_host[i] * b_host[i];
+    if (any_sharded) {
+      DevBuf<double> tmp(ctx, 1);
+      tmp.upload(&sq_sh, 1);
+      AllReduceSum(ctx, tmp.p, 1);
+      tmp.download(&sq_sh, 1);
+    }
+    b_norm = std::sqrt(sq_sh + sq_rep);
+  }
 
   // ---- variable ownership ----
   var_owner.assign(vars.size(), -1);
@@ -255,6 +292,28 @@ void eps_solver::Init(const eps_problem& original) {
     op.A.Compile();
     op.simple_scalar = op.A.simple_scalar && op.A.simple_row_off == 0 && op.span_len == op.n;
     op.a = op.simple_scalar ? op.A.simple_alpha : 0.0;
+    if (any_sharded) {
+      // local: every variable of f_i lives on sharded rows; a_sharded: replicated variables that enter sharded rows
+      int n_local = 0;
+      for (int v : op.vars) n_local += var_global[v] >= 0;
+      EPS_CHECK(n_local == 0 || n_local == (int)op.vars.size(), "prox %d mixes sharded and replicated variables", i);
+      op.local = n_local > 0;
+      op.A_sh.ctx = op.A_rep.ctx = ctx;
+      op.A_sh.rows = op.A_rep.rows = op.A.rows;
+      op.A_sh.cols = op.A_rep.cols = op.A.cols;
+      for (size_t c = 0; c < p.constraints.size(); c++)
+        for (const Term& t : p.constraints[c].terms)
+          if (t.var >= 0 && var_owner[t.var] == i)
+            (c_sharded[c] ? op.A_sh : op.A_rep).blks.push_back(
+                TermBlk(ctx, t, p.constraints[c].rows, (int)(coff[c] - lo), (int)voff[t.var]));
+      op.a_sharded = !op.local && !op.A_sh.blks.empty();
+      if (op.a_sharded) {
+        EPS_CHECK(IsKktType(f.type), "prox %d (type %d): a replicated variable enters a row-sharded constraint; only "
+                  "the linear-equality operators (SUM_SQUARE, AFFINE, CONSTANT) can own it", i, f.type);
+        op.A_sh.Compile();
+        op.A_rep.Compile();
+      }
+    }
   }
 
   // ---- operators ----
@@ -382,6 +441,14 @@ void eps_solver::Init(const eps_problem& original) {
       k->gram_max_n = params.gram_max_n;
       k->rows_a = op.span_len;
       k->A.ctx = ctx; k->A.rows = op.A.rows; k->A.cols = op.A.cols; k->A.blks = op.A.blks;
+      if (op.a_sharded) {
+        k->a_sharded = true;
+        k->A_sh.ctx = k->A_rep.ctx = ctx;
+        k->A_sh.rows = k->A_rep.rows = op.A.rows;
+        k->A_sh.cols = k->A_rep.cols = op.A.cols;
+        k->A_sh.blks = op.A_sh.blks;
+        k->A_rep.blks = op.A_rep.blks;
+      }
       std::vector<double> c_host;
       if (f.type == EPS_PROX_SUM_SQUARE) {
         k->alpha2 = 2.0 * f.alpha;
@@ -547,10 +614,12 @@ void eps_solver::Init(const eps_problem& original) {
     if (op.kkt && op.kkt->mode == EPS_KKT_CG) graph_ok = false;  // host-checked inner loop
   for (auto& stp : stages)
     if (stp->kind == ST_TV || stp->kind == ST_VEC) graph_ok = false;  // host-checked rounds / library sorts
+  if (any_sharded) graph_ok = false;                                  // collectives inside the iteration
   memset(&status, 0, sizeof(status));
   status.state = EPS_NOT_STARTED;
-  status.m = (int32_t)m_total;
+  status.m = (int32_t)(any_sharded ? m_global : m_total);
   status.n = (int32_t)n_total;
+  if (any_sharded) resid_sh.alloc(ctx, 2 * (1 + 3 * (size_t)N));
   if (two_block) { status.m = (int32_t)m_c; status.n = (int32_t)tb_n; }  // H.A.m(), H.A.n()
   status.N = N;
   description = Format("%s m=%lld n=%lld N=%d stages=%zu graph=%d\n", two_block ? "ProxADMMTwoBlock" : "ProxADMM",

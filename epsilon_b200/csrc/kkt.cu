@@ -755,7 +755,13 @@ void KktSolver::Init(const std::vector<double>& g_host, const std::vector<double
 
   std::vector<double> dh, da;
   const bool h_diag = (alpha2 == 0.0 || H.blks.empty()) ? (dh.assign(n, 0.0), true) : H.GramDiagonal(&dh);
-  a_diag = A.GramDiagonal(&da);
+  if (a_sharded) {
+    A_sh.Compile();
+    A_rep.Compile();
+    EPS_CHECK(mode == EPS_KKT_AUTO || mode == EPS_KKT_GRAM || mode == EPS_KKT_CG,
+              "row-sharded constraints need kkt mode AUTO, GRAM or CG");
+  }
+  a_diag = !a_sharded && A.GramDiagonal(&da);
   bool a_pos = a_diag;
   if (a_diag) for (double v : da) if (!(v > 0.0)) { a_pos = false; break; }
 
@@ -813,14 +819,16 @@ void KktSolver::Init(const std::vector<double>& g_host, const std::vector<double
   } else if (mode == EPS_KKT_GRAM) {
     DevBuf<double> Mmat(ctx, (size_t)n * n);
     Mmat.zero();
-    if (alpha2 != 0.0) {
-      AccumulateGram(ctx, H, alpha2, Mmat.p, n);
-      if (h_sharded) AllReduceSum(ctx, Mmat.p, n * n);
-    }
-    AccumulateGram(ctx, A, 1.0, Mmat.p, n);
+    // the parts whose rows are sharded first, one all-reduce for them, then the replicated parts
+    if (alpha2 != 0.0 && h_sharded) AccumulateGram(ctx, H, alpha2, Mmat.p, n);
+    if (a_sharded) AccumulateGram(ctx, A_sh, 1.0, Mmat.p, n);
+    if (h_sharded || a_sharded) AllReduceSum(ctx, Mmat.p, n * n);
+    if (alpha2 != 0.0 && !h_sharded) AccumulateGram(ctx, H, alpha2, Mmat.p, n);
+    AccumulateGram(ctx, a_sharded ? A_rep : A, 1.0, Mmat.p, n);
     W.alloc(ctx, (size_t)n * n);
     DenseCholInverseFactor(ctx, Mmat.p, n, (int)n, W.p);
-    description = Format("kkt=GRAM n=%lld factor=%lldx%lld", (long long)n, (long long)n, (long long)n);
+    description = Format("kkt=GRAM n=%lld factor=%lldx%lld%s", (long long)n, (long long)n, (long long)n,
+                         (h_sharded || a_sharded) ? " sharded (Gram all-reduced)" : "");
   } else if (mode == EPS_KKT_CG) {
     if (a_diag) {
       ddiag.alloc(ctx, n);
@@ -842,18 +850,49 @@ void KktSolver::Init(const std::vector<double>& g_host, const std::vector<double
       tail_grid = std::min(tail_grid, ctx->sm_count);
       cg_partials.alloc(ctx, 4 * (size_t)tail_grid);
     }
-    // fused matvec: H is one SELL-packed sparse block over all of x and A'A is diagonal
-    fast_h = a_diag && alpha2 != 0.0 && H.blks.size() == 1 && H.blks[0].map->kind == MK_SPARSE &&
-             H.blks[0].row_off == 0 && H.blks[0].col_off == 0 && H.blks[0].m() == rows_h &&
-             H.blks[0].n() == n && H.blks[0].map->sell.built && H.blks[0].map->sell_t.built;
-    if (fast_h && h_sharded) peer = PeerEnsure(ctx, n);
-    fused_tail = fast_h && (!h_sharded || peer) && tail_grid <= kPeerMaxCtas && !getenv("EPS_NO_FUSED_TAIL");
+    // fused matvec: M = c B'B + diag(d) with ONE SELL-packed sparse block B over all of x.
+    //   (i)  B is the argument of the SUM_SQUARE (H) and A'A is diagonal           -- the lasso
+    //   (ii) B is the data block of the constraints (A), every other block of A and all of H are
+    //        scalar / diagonal                                                      -- logistic regression, SVM
+    auto sell_block = [&](const Blk& b) {
+      return b.map->kind == MK_SPARSE && b.col_off == 0 && b.n() == n && b.map->sell.built && b.map->sell_t.built;
+    };
+    fast_h = a_diag && alpha2 != 0.0 && H.blks.size() == 1 && sell_block(H.blks[0]) && H.blks[0].row_off == 0 &&
+             H.blks[0].m() == rows_h;
+    if (fast_h) {
+      fb = H.blks[0];
+      fb_coef = alpha2;
+      fb_sharded = h_sharded;
+    } else if (h_diag && !h_sharded) {
+      const BlockOp& src = a_sharded ? A_sh : A;
+      int n_sparse = 0;
+      for (auto& b : src.blks) if (!b.diag_like()) n_sparse++;
+      BlockOp rest;
+      rest.ctx = ctx; rest.rows = A.rows; rest.cols = n;
+      for (auto& b : A.blks) if (b.diag_like()) rest.blks.push_back(b);
+      std::vector<double> dr;
+      bool ok = n_sparse == 1 && (!a_sharded || A_sh.blks.size() == 1) && (int)A.blks.size() == (int)rest.blks.size() + 1;
+      if (ok) for (auto& b : src.blks) if (!b.diag_like()) ok = sell_block(b), fb = b;
+      if (ok) for (auto& b : A_rep.blks) ok = ok && b.diag_like();
+      if (ok && rest.GramDiagonal(&dr)) {
+        fast_h = true;
+        fb_coef = 1.0;
+        fb_sharded = a_sharded;
+        da.assign(n, 0.0);
+        for (int64_t j = 0; j < n; j++) da[j] = alpha2 * dh[j] + dr[j];
+        ddiag.alloc(ctx, n);
+        ddiag.upload(da.data(), n);
+      }
+    }
+    if (fast_h) tb1.alloc(ctx, std::max<int64_t>(fb.m(), 1));
+    if (fast_h && fb_sharded) peer = PeerEnsure(ctx, n);
+    fused_tail = fast_h && (!fb_sharded || peer) && tail_grid <= kPeerMaxCtas && !getenv("EPS_NO_FUSED_TAIL");
     if (fused_tail) {
       int per_sm = 0;
       CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, CgFusedTailKernel, kTailBlock, 0));
       EPS_CHECK(per_sm >= 1, "CgFusedTailKernel does not fit an SM");
-      tail_v2 = !getenv("EPS_TAIL_V1") && H.blks[0].map->sell.n_cta <= ctx->sm_count &&
-                H.blks[0].map->sell_t.n_cta <= ctx->sm_count;
+      tail_v2 = !getenv("EPS_TAIL_V1") && fb.map->sell.n_cta <= ctx->sm_count &&
+                fb.map->sell_t.n_cta <= ctx->sm_count;
       if (tail_v2) {
         rhs_prev.alloc(ctx, n);
         cg_bar.alloc(ctx, 4);
@@ -862,7 +901,8 @@ void KktSolver::Init(const std::vector<double>& g_host, const std::vector<double
     }
     CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
     description = Format("kkt=CG n=%lld rows_h=%lld tol=%.1e%s%s%s", (long long)n, (long long)rows_h, cg_tol,
-                         h_sharded ? " sharded" : "", fast_h ? " fused-matvec" : "",
+                         (h_sharded || a_sharded) ? " sharded" : "",
+                         fast_h ? (fb_coef == alpha2 && alpha2 != 0.0 ? " fused-matvec" : " fused-matvec(constraint block)") : "",
                          peer ? " peer-allreduce" : "");
     if (fused_tail) description += tail_v2 ? " fused-tail(one-barrier, pre-phase, residual-carry)" : " fused-tail";
   } else {
@@ -875,7 +915,7 @@ void KktSolver::MatVec(const double* p, double* w, const int* skip) {
     // w = 2a s^2 H'(H p) + d.*p with the diagonal term fused into the reduction of the second
     // pass.  Row-sharded: every rank contributes its rows' part, rank 0 alone adds d.*p, and
     // the all-reduce completes the sum (identical bits on every rank).
-    const Blk& b = H.blks[0];
+    const Blk& b = fb;
     const MapData& M = *b.map;
     SpmvExtra e1, e2;
     e1.skip = skip;
@@ -887,14 +927,14 @@ void KktSolver::MatVec(const double* p, double* w, const int* skip) {
       e2.publish = &peer->x;
       e2.publish_seq = pending_seq = ++peer->seq;
       e2.publish_counter = peer->counter;
-    } else if (!h_sharded || ctx->rank == 0) {
+    } else if (!fb_sharded || ctx->rank == 0) {
       e2.ep_d = ddiag.p;
       e2.ep_p = p;
     }
-    SellApply(ctx, b.trans ? M.sell_t : M.sell, b.scale, p, 0.0, th1.p, b.trans ? KC_SPMV_T : KC_SPMV_N, &e1);
-    SellApply(ctx, b.trans ? M.sell : M.sell_t, alpha2 * b.scale, th1.p, 0.0, w,
+    SellApply(ctx, b.trans ? M.sell_t : M.sell, b.scale, p, 0.0, tb1.p, b.trans ? KC_SPMV_T : KC_SPMV_N, &e1);
+    SellApply(ctx, b.trans ? M.sell : M.sell_t, fb_coef * b.scale, tb1.p, 0.0, w,
               b.trans ? KC_SPMV_N : KC_SPMV_T, &e2);
-    if (h_sharded && !peer) AllReduceSum(ctx, w, n);
+    if (fb_sharded && !peer) AllReduceSum(ctx, w, n);
     return;
   }
   bool have = false;
@@ -907,6 +947,17 @@ void KktSolver::MatVec(const double* p, double* w, const int* skip) {
   if (a_diag) {
     if (have) VecMulAdd(ctx, n, ddiag.p, p, alpha2, w, w);
     else VecMulAdd(ctx, n, ddiag.p, p, 0.0, nullptr, w);
+  } else if (a_sharded) {
+    // sharded rows: this rank's part of A_sh'(A_sh p), summed over the ranks; then the replicated rows
+    A_sh.Apply(p, ta1.p);
+    A_sh.ApplyT(ta1.p, tn2.p);
+    AllReduceSum(ctx, tn2.p, n);
+    if (have) VecAxpby(ctx, n, alpha2, w, 1.0, tn2.p, w);
+    else VecCopy(ctx, n, tn2.p, w);
+    if (!A_rep.blks.empty()) {
+      A_rep.Apply(p, ta1.p);
+      A_rep.ApplyT(ta1.p, w, true);
+    }
   } else {
     if (have) VecScale(ctx, n, alpha2, w, w);
     A.Apply(p, ta1.p);
@@ -1020,7 +1071,7 @@ void KktSolver::Solve(const double* rhs, double* x) {
         if (fused_tail) {
           // first pass with its reduction, second pass as partial planes, then ONE kernel for
           // the plane reduction, the cross-GPU exchange and the CG update
-          const Blk& b = H.blks[0];
+          const Blk& b = fb;
           const MapData& M = *b.map;
           const Sell& S1 = b.trans ? M.sell_t : M.sell;
           const Sell& S2 = b.trans ? M.sell : M.sell_t;
@@ -1028,19 +1079,19 @@ void KktSolver::Solve(const double* rhs, double* x) {
           if (tail_v2) {
             // first pass as planes; their reduction rides in the second pass (pre-phase + grid barrier)
             const double* p1 = SellApplyPlanes(ctx, S1, cg_p.p, b.trans ? KC_SPMV_T : KC_SPMV_N, cg_done.p);
-            planes = SellApplyPlanesAfter(ctx, S2, th1.p, p1, S1.T, b.scale, cg_bar.p + 2,
+            planes = SellApplyPlanesAfter(ctx, S2, tb1.p, p1, S1.T, b.scale, cg_bar.p + 2,
                                           b.trans ? KC_SPMV_N : KC_SPMV_T, cg_done.p);
           } else {
             SpmvExtra e1;
             e1.skip = cg_done.p;
-            SellApply(ctx, S1, b.scale, cg_p.p, 0.0, th1.p, b.trans ? KC_SPMV_T : KC_SPMV_N, &e1);
-            planes = SellApplyPlanes(ctx, S2, th1.p, b.trans ? KC_SPMV_N : KC_SPMV_T, cg_done.p);
+            SellApply(ctx, S1, b.scale, cg_p.p, 0.0, tb1.p, b.trans ? KC_SPMV_T : KC_SPMV_N, &e1);
+            planes = SellApplyPlanes(ctx, S2, tb1.p, b.trans ? KC_SPMV_N : KC_SPMV_T, cg_done.p);
           }
           {
           ProfScope ps(ctx, peer ? KC_ALLREDUCE : KC_VEC, 8.0 * S2.T * n + 72.0 * n);
           int64_t nn = n;
           int T = S2.T;
-          double alpha = alpha2 * b.scale;
+          double alpha = fb_coef * b.scale;
           double* wp = cg_w.p;
           double *pp = cg_p.p, *xp = x, *rp = cg_r.p, *sp = scal.p, *part = cg_partials.p;
           int* dp = cg_done.p;

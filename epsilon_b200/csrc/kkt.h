@@ -20,6 +20,17 @@ struct KktSolver {
   double alpha2 = 0;  // 2*alpha (0: no H term)
   bool h_sharded = false;
   BlockOp H, A;
+  // Row-sharded constraints (multi-GPU): A = A_sh (blocks whose rows this rank holds a shard of: their
+  // products A_sh'(A_sh p) and A_sh'v are summed over the ranks) + A_rep (rows every rank holds in full).
+  bool a_sharded = false;
+  BlockOp A_sh, A_rep;
+  // The one sparse (SELL) block B of the fused CG step: M = fb_coef * s^2 B'B + diag(ddiag).  Either the
+  // argument of a SUM_SQUARE (H, fb_coef = 2a: the lasso) or the data block of the constraints (A,
+  // fb_coef = 1: logistic regression, SVM); fb_sharded: its rows are this rank's shard.
+  Blk fb;
+  double fb_coef = 0;
+  bool fb_sharded = false;
+  DevBuf<double> tb1;    // B p
   DevBuf<double> c0;
   // factors
   DevBuf<double> dinv;   // DIAGONAL: 1/diag(M); WOODBURY: 1/diag(A'A)

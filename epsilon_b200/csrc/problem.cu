@@ -117,6 +117,16 @@ int eps_problem_prox_arg_sharded(eps_problem* p, int prox_index, int arg_index, 
   EPS_API_END
 }
 
+int eps_problem_constraint_sharded(eps_problem* p, int constraint_index, int64_t global_rows) {
+  EPS_API_BEGIN
+  EPS_CHECK(p && constraint_index >= 0 && constraint_index < (int)p->constraints.size(), "constraint index %d",
+            constraint_index);
+  EPS_CHECK(global_rows >= p->constraints[constraint_index].rows, "global rows %lld < local rows %d",
+            (long long)global_rows, p->constraints[constraint_index].rows);
+  p->constraints[constraint_index].global_rows = global_rows;
+  EPS_API_END
+}
+
 int eps_problem_add_term(eps_problem* p, int prox_index, int index, eps_map* map, int var_index,
                          const double* constant) {
   EPS_API_BEGIN

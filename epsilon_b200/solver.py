@@ -163,7 +163,8 @@ class _ProblemBuilder:
     """ProxAffineProblem -> eps_problem (the AffineOperator terms of affine.cc:22-129)."""
 
     def __init__(self, ctx: Context, problem: ProxAffineProblem,
-                 sharded_args: Optional[Dict[Tuple[int, int], int]] = None):
+                 sharded_args: Optional[Dict[Tuple[int, int], int]] = None,
+                 sharded_constraints: Optional[Dict[int, int]] = None):
         self.ctx, self.lib = ctx, ctx.lib
         self.handle = C.c_void_p()
         self.maps: List[LinearMap] = []
@@ -179,6 +180,9 @@ class _ProblemBuilder:
         for c in problem.constraints:
             ci = C.c_int()
             capi.check(self.lib.eps_problem_add_constraint(self.handle, c.rows, C.byref(ci)))
+            if sharded_constraints and ci.value in sharded_constraints:
+                capi.check(self.lib.eps_problem_constraint_sharded(self.handle, ci.value,
+                                                                   int(sharded_constraints[ci.value])))
             for t in c.terms:
                 self._add_term(-1, ci.value, t)
         for f in problem.prox:
@@ -260,13 +264,14 @@ class ProxADMMSolver:
 
     def __init__(self, problem: ProxAffineProblem, params: Optional[dict] = None,
                  ctx: Optional[Context] = None,
-                 sharded_args: Optional[Dict[Tuple[int, int], int]] = None):
+                 sharded_args: Optional[Dict[Tuple[int, int], int]] = None,
+                 sharded_constraints: Optional[Dict[int, int]] = None):
         self._own_ctx = ctx is None
         self.ctx = ctx or Context()
         self.lib = self.ctx.lib
         self.problem = problem
         self.params = make_params(self.lib, **(params or {}))
-        self._builder = _ProblemBuilder(self.ctx, problem, sharded_args)
+        self._builder = _ProblemBuilder(self.ctx, problem, sharded_args, sharded_constraints)
         self.handle = C.c_void_p()
         capi.check(self.lib.eps_solver_create(self._builder.handle, C.byref(self.params),
                                               C.byref(self.handle)))

@@ -179,6 +179,15 @@ int eps_problem_prox_add_arg(eps_problem* p, int prox_index, int rows, int* arg_
  * argument with `global_rows` rows; products H'H p and H'g are all-reduced. */
 int eps_problem_prox_arg_sharded(eps_problem* p, int prox_index, int arg_index,
                                  int64_t global_rows);
+/* Row-sharded CONSTRAINT (multi-GPU, SURVEY section 8e: the "consensus blocks" of the north star): the rows
+ * given to this rank are its slice of a constraint with `global_rows` rows -- for logistic regression or an
+ * SVM the block -diag(y) A x - t = 0 whose row count is the number of samples.  Every rank holds its rows of
+ * the data block, of the constant term, of u and y_i and of the variable that enters the block through a
+ * scalar / diagonal map (t); variables that enter through a general map (x) are replicated.  The
+ * linear-equality prox of the replicated variables sums A_r'(.) over the ranks (fused NVLink exchange per
+ * CG step, or one all-reduce of the Gram matrix), ComputeResiduals all-reduces its partial sums in one
+ * message (prox_admm.cc:141-147,178-217 on row blocks). */
+int eps_problem_constraint_sharded(eps_problem* p, int constraint_index, int64_t global_rows);
 /* Add `map * x[var_index]` (var_index >= 0) or `map * constant` (var_index < 0,
  * `constant` has map.n entries, or `rows` entries when map is NULL) to constraint
  * `constraint_index` (prox_index < 0) or to argument `arg_index` of prox `prox_index`.

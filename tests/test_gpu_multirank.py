@@ -142,3 +142,86 @@ def test_row_sharded_solve_matches_reference_on_every_rank(case, mode, tmp_path)
         assert np.abs(x - gold_x).max() <= 1e-7 * max(1.0, np.abs(gold_x).max())
     # the second solve on the same context repeats the first bit for bit
     assert np.array_equal(r[0]["trace0"], r[0]["trace1"]) and np.array_equal(r[0]["x0"], r[0]["x1"])
+
+
+# ---- row-sharded CONSTRAINTS (eps_problem_constraint_sharded): logistic regression and the SVM ------------------
+SHARD_CASES = {
+    # fixture name -> (generator, shard helper, params)
+    "logreg_l1_2000x200": ("logreg_l1", "logreg_l1_row_shard", dict(m=2000, n=200, density=0.05, seed=4), {"max_iterations": 200}),
+    "hinge_l2_sparse_5000x300": ("hinge_l2", "hinge_l2_row_shard", dict(m=5000, n=300, density=0.02, seed=10), {"max_iterations": 300}),
+    "hinge_l2_1500x100": ("hinge_l2", "hinge_l2_row_shard", dict(m=1500, n=100, seed=5), {"max_iterations": 300}),   # dense data block
+    "logreg_l1_sparse_60000x2000": ("logreg_l1", "logreg_l1_row_shard", dict(m=60000, n=2000, density=0.005, seed=14), {"max_iterations": 200}),
+}
+SHARD_MODES = {
+    "gram": {"kkt_mode": "gram"},                                  # Gram of the row blocks all-reduced, factor replicated
+    "cg_fused": {"kkt_mode": "cg", "_env": {"EPS_SPARSE_FORMAT": "sell"}},   # fused SELL passes + NVLink exchange per CG step
+    "cg_nccl": {"kkt_mode": "cg", "_env": {"EPS_SPARSE_FORMAT": "csr"}},     # generic block path, ncclAllReduce per product
+}
+
+
+def _shard_worker(rank, world, port, case, mode, out_dir):
+    gen, helper, args, params = SHARD_CASES[case]
+    mp_ = dict(SHARD_MODES[mode])
+    os.environ.update(mp_.pop("_env", {}))
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    import torch
+    import torch.distributed as dist
+    torch.cuda.set_device(rank)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from epsilon_b200 import problems
+    from epsilon_b200.solver import Context, ProxADMMSolver
+    ctx = Context(rank)
+    uid = [Context.nccl_unique_id() if rank == 0 else None]
+    dist.broadcast_object_list(uid, src=0)
+    ctx.init_comm(world, rank, uid[0])
+    a = dict(args)
+    m, n = a.pop("m"), a.pop("n")
+    _, info = getattr(problems, gen)(m, n, **a)
+    prob, sharded = getattr(problems, helper)(info, rank, world)
+    with ProxADMMSolver(prob, dict(params, **mp_), ctx=ctx, sharded_constraints=sharded) as s:
+        x = s.solve()
+        st = s.status.as_dict()
+        trace = np.array([[t[k] for k in TRACE_KEYS] for t in s.trace], dtype=np.float64)
+        desc = s.describe()
+    np.savez(os.path.join(out_dir, "rank%d.npz" % rank), desc=np.array(desc), x=x["x"], t=x["t"], trace=trace,
+             mn=np.array([st["m"], st["n"]]), unconverged=st["cg_unconverged"])
+    dist.barrier()
+    ctx.close()
+    dist.destroy_process_group()
+
+
+@pytest.mark.timeout(900)
+@pytest.mark.parametrize("mode", sorted(SHARD_MODES))
+@pytest.mark.parametrize("case", sorted(SHARD_CASES))
+def test_row_sharded_constraints_match_the_reference_fixture(case, mode, tmp_path):
+    """C3 / C5b shapes: the data matrix sits in the CONSTRAINT, so u, y_i and t are m-vectors and the rows of the
+    constraint block are what is sharded.  Every rank must report the reference's trace (the single-process
+    fixture), hold the replicated x bit-identically, and the shards of t must concatenate to the fixture's."""
+    world = min(_gpus(), int(os.environ.get("EPS_TEST_WORLD", "2")))
+    if world < 2:
+        pytest.skip("needs at least 2 GPUs (gpurun --gpus 2)")
+    if mode == "cg_fused" and "sparse" not in case and case != "logreg_l1_2000x200":
+        pytest.skip("dense data block: no SELL path")
+    import make_golden
+    index = json.load(open(os.path.join(GOLDEN, "index.json")))
+    prob, info, params = make_golden.make_problem(case)
+    if make_golden.problem_digest(prob) != index["solve"][case]["digest"]:
+        pytest.skip("generator drift on this host")
+    gold = np.load(os.path.join(GOLDEN, case + ".npz"))
+    import torch.multiprocessing as mp
+    mp.spawn(_shard_worker, args=(world, _free_port(), case, mode, str(tmp_path)), nprocs=world, join=True)
+    r = [np.load(os.path.join(str(tmp_path), "rank%d.npz" % k)) for k in range(world)]
+    desc = str(r[0]["desc"])
+    assert r[0]["mn"].tolist() == gold["mnN"][:2].tolist(), desc        # global A_.m(), A_.n()
+    if mode == "cg_fused":
+        assert "fused-matvec(constraint block)" in desc and "peer-allreduce" in desc and "fused-tail" in desc, desc
+    for k in range(1, world):
+        assert np.array_equal(r[0]["trace"], r[k]["trace"]), (mode, desc)
+        assert np.array_equal(r[0]["x"], r[k]["x"])
+    assert int(r[0]["unconverged"]) == 0
+    trace = r[0]["trace"]
+    assert trace.shape == gold["trace"].shape, (trace.shape, gold["trace"].shape, desc)
+    assert np.array_equal(trace[:, :2], gold["trace"][:, :2])
+    np.testing.assert_allclose(trace[:, 2:], gold["trace"][:, 2:], rtol=1e-7, atol=1e-12)
+    assert np.abs(r[0]["x"] - gold["x"]).max() <= 1e-7 * max(1.0, np.abs(gold["x"]).max())
