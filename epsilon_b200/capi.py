@@ -85,6 +85,7 @@ SIGNATURES = {
     "eps_nccl_unique_id": (C.c_int, [_P]),
     "eps_ctx_init_comm": (C.c_int, [_P, C.c_int, C.c_int, _P]),
     "eps_map_dense": (C.c_int, [_P, C.c_int, C.c_int, _DP, C.POINTER(_P)]),
+    "eps_map_dense_dev": (C.c_int, [_P, C.c_int, C.c_int, _P, C.POINTER(_P)]),
     "eps_map_csc": (C.c_int, [_P, C.c_int, C.c_int, C.c_int64, _IP, _IP, _DP, C.POINTER(_P)]),
     "eps_map_diagonal": (C.c_int, [_P, C.c_int, _DP, C.POINTER(_P)]),
     "eps_map_scalar": (C.c_int, [_P, C.c_int, C.c_double, C.POINTER(_P)]),

@@ -58,13 +58,14 @@ struct DevBuf {
   T* p = nullptr;
   size_t n = 0;
   Ctx* ctx = nullptr;
+  bool borrowed = false;   // memory owned by the caller (eps_map_dense_dev): never freed here
   DevBuf() {}
   DevBuf(Ctx* c, size_t count) { alloc(c, count); }
   DevBuf(const DevBuf&) = delete;
   DevBuf& operator=(const DevBuf&) = delete;
   DevBuf(DevBuf&& o) noexcept { *this = std::move(o); }
   DevBuf& operator=(DevBuf&& o) noexcept {
-    if (this != &o) { release(); p = o.p; n = o.n; ctx = o.ctx; o.p = nullptr; o.n = 0; }
+    if (this != &o) { release(); p = o.p; n = o.n; ctx = o.ctx; borrowed = o.borrowed; o.p = nullptr; o.n = 0; o.borrowed = false; }
     return *this;
   }
   ~DevBuf() { release(); }
@@ -75,8 +76,12 @@ struct DevBuf {
     p = static_cast<T*>(DevAlloc(c, count * sizeof(T)));
   }
   void release() {
-    if (p) DevFree(ctx, p, n * sizeof(T));
-    p = nullptr; n = 0;
+    if (p && !borrowed) DevFree(ctx, p, n * sizeof(T));
+    p = nullptr; n = 0; borrowed = false;
+  }
+  void borrow(Ctx* c, T* ptr, size_t count) {
+    release();
+    ctx = c; p = ptr; n = count; borrowed = true;
   }
   void zero() { if (n) CUDA_CHECK(cudaMemsetAsync(p, 0, n * sizeof(T), ctx->stream)); }
   void upload(const T* host, size_t count) {

@@ -508,6 +508,22 @@ int eps_map_dense(eps_ctx* ctx, int m, int n, const double* colmajor, eps_map** 
   EPS_API_END
 }
 
+int eps_map_dense_dev(eps_ctx* ctx, int m, int n, double* colmajor_dev, eps_map** out) {
+  EPS_API_BEGIN
+  EPS_CHECK(ctx && out && m >= 0 && n >= 0 && (colmajor_dev || (size_t)m * n == 0), "eps_map_dense_dev arguments");
+  cudaPointerAttributes attr;
+  CUDA_CHECK(cudaPointerGetAttributes(&attr, colmajor_dev));
+  EPS_CHECK(attr.type == cudaMemoryTypeDevice && attr.device == ctx->c.device,
+            "eps_map_dense_dev: the matrix must live in the memory of device %d", ctx->c.device);
+  auto d = std::make_shared<MapData>();
+  d->ctx = &ctx->c; d->kind = MK_DENSE; d->m = m; d->n = n;
+  d->dense.borrow(&ctx->c, colmajor_dev, (size_t)m * n);
+  auto* h = new eps_map();
+  h->d = d;
+  *out = h;
+  EPS_API_END
+}
+
 int eps_map_csc(eps_ctx* ctx, int m, int n, int64_t nnz, const int32_t* colptr,
                 const int32_t* rowidx, const double* vals, eps_map** out) {
   EPS_API_BEGIN

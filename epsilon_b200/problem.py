@@ -70,6 +70,9 @@ class LinearMapSpec:
     trans: bool = False  # DENSE only: stored data is the transpose's (shares storage)
     name: str = ""  # data_location stem for the reference
     parameter_id: str = ""  # DENSE only: Constant.parameter_id of the matrix data (a cvxpy Parameter)
+    # DENSE only: the matrix already lives on the device, column-major f64; (pointer, owner object kept alive)
+    device_ptr: Optional[int] = None
+    device_owner: object = None
 
     @staticmethod
     def Dense(a: np.ndarray, name: str = "") -> "LinearMapSpec":

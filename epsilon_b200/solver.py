@@ -87,7 +87,10 @@ class LinearMap:
             self.handle = _handle
             return
         h = C.byref(self.handle)
-        if spec.kind == MAP_DENSE:
+        if spec.kind == MAP_DENSE and spec.device_ptr is not None:
+            self._keep = [spec.device_owner]
+            capi.check(self.lib.eps_map_dense_dev(ctx.handle, spec.m, spec.n, C.c_void_p(spec.device_ptr), h))
+        elif spec.kind == MAP_DENSE:
             a = np.asfortranarray(spec.dense, dtype=np.float64)
             capi.check(self.lib.eps_map_dense(ctx.handle, a.shape[0], a.shape[1], capi.dptr(a), h))
         elif spec.kind == MAP_SPARSE:

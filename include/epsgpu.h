@@ -119,6 +119,10 @@ int eps_ctx_init_comm(eps_ctx* ctx, int n_ranks, int rank, const void* unique_id
 /* DenseMatrixImpl (dense_matrix_impl.cc:11-19): m x n, column-major f64, as decoded
  * by BuildMatrix (src/epsilon/vector/vector_util.cc:247-259). */
 int eps_map_dense(eps_ctx* ctx, int m, int n, const double* colmajor, eps_map** out);
+/* The same for a matrix that is ALREADY resident in the memory of the context's device (column-major f64):
+ * the map borrows the buffer -- no copy; the caller keeps it alive until the map and every problem / solver
+ * built on it are destroyed.  (An 80 GB data matrix produced on the device must not exist twice.) */
+int eps_map_dense_dev(eps_ctx* ctx, int m, int n, double* colmajor_dev, eps_map** out);
 /* SparseMatrixImpl from the wire layout of BuildSparseMatrix (vector_util.cc:261-281):
  * CSC, int32 colptr[n+1], int32 rowidx[nnz], f64 vals[nnz]. */
 int eps_map_csc(eps_ctx* ctx, int m, int n, int64_t nnz, const int32_t* colptr,

@@ -1,14 +1,17 @@
 #!/usr/bin/env python
-"""Per-config measurements on ONE GPU for the BASELINE.json configs other than the headline
-one (bench.py covers config 2).  Prints one JSON line per config: iterations/s of the ADMM
-loop, time-to-tolerance of a whole solve, and CUDA-event time / algorithmic bytes per kernel
-class from a profiled pass, against the measured HBM peak.
+"""Per-config measurements for the BASELINE.json configs other than the headline one (bench.py covers
+config 2).  One JSON line per run: iterations/s of the ADMM loop, time-to-tolerance of a whole solve, and
+CUDA-event time / algorithmic bytes per kernel class from a profiled pass, against the measured HBM peak.
 
+One GPU:
   python tools/bench_configs.py tv1d --n 10000000
   python tools/bench_configs.py logreg --m 2000000 --n 200000 --density 1e-3
-  python tools/bench_configs.py hinge --m 100000 --n 10000
+  python tools/bench_configs.py hinge --m 1000000 --n 10000 --device-gen        # 80 GB matrix made on the GPU
   python tools/bench_configs.py group_lasso --m 50000 --group 50 --K 200
   python tools/bench_configs.py lasso_dense --m 1000 --n 5000
+N GPUs (sample rows of the constraint block sharded, eps_problem_constraint_sharded):
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \\
+      tools/bench_configs.py logreg --rows 2000000 --cols 200000 --density 1e-3
 """
 from __future__ import annotations
 
@@ -24,11 +27,68 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
 
+def hinge_l2_on_device(m, n, rank, world, seed, allreduce_dev, lam=1.0):
+    """hinge_l2 (problems/hinge_l2.py: dense N(0,1) data, unit-norm columns, y = sign(A x0 + noise)) with the data
+    block generated ON THE DEVICE by torch's counter-based (Philox) generator, in the row-sharded compiled form:
+    this rank holds rows [rank*m/world, (rank+1)*m/world).  The 8*m*n-byte matrix never exists on the host and
+    is handed to the library without a copy (eps_map_dense_dev)."""
+    import torch
+    from epsilon_b200.problem import Affine, LinearMapSpec, ProxAffineProblem, ProxFunction, Term, Variable
+    lo, hi = rank * m // world, (rank + 1) * m // world
+    ml = hi - lo
+    dev = torch.device("cuda", torch.cuda.current_device())
+    g = torch.Generator(device=dev)
+    g.manual_seed(seed * 1000 + rank)
+    a = torch.empty((n, ml), dtype=torch.float64, device=dev)       # row j = column j of the column-major ml x n block
+    step = max(1, (1 << 28) // max(ml, 1))
+    sq = torch.empty(n, dtype=torch.float64, device=dev)
+    for j in range(0, n, step):
+        blk = a[j:j + step]
+        blk.normal_(generator=g)
+        sq[j:j + step] = (blk * blk).sum(dim=1)
+    sq = allreduce_dev(sq)
+    inv = 1.0 / torch.sqrt(sq)
+    x0 = np.zeros(n)
+    rng = np.random.default_rng([seed, 10_000])
+    k = max(1, int(round(0.01 * n)))
+    idx = rng.choice(n, size=k, replace=False)
+    x0[idx] = rng.standard_normal(k)
+    x0d = torch.from_numpy(x0).to(dev)
+    z = torch.zeros(ml, dtype=torch.float64, device=dev)
+    for j in range(0, n, step):
+        blk = a[j:j + step]
+        blk *= inv[j:j + step, None]
+        z += x0d[j:j + step] @ blk
+    z += 0.05 * torch.randn(ml, dtype=torch.float64, device=dev, generator=g)
+    y = torch.sign(z)
+    y[y == 0] = 1.0
+    for j in range(0, n, step):
+        a[j:j + step] *= -y[None, :]
+    torch.cuda.synchronize()
+    nda = LinearMapSpec(0, ml, n, name="negDA", device_ptr=a.data_ptr(), device_owner=a)
+    t, x = Variable("t", ml), Variable("x", n)
+    f0 = ProxFunction("SUM_HINGE", args=[Affine(ml, [Term(t)])])
+    f1 = ProxFunction("SUM_SQUARE", alpha=lam, args=[Affine(n, [Term(x)])])
+    c0 = Affine(ml, [Term(np.ones(ml), name="ones"), Term(x, nda), Term(t, LinearMapSpec.Scalar(-1.0, ml))])
+
+    def objective(sol):
+        xv = torch.from_numpy(np.ascontiguousarray(sol["x"])).to(dev)
+        zz = torch.zeros(ml, dtype=torch.float64, device=dev)
+        for j in range(0, n, step):
+            zz += xv[j:j + step] @ a[j:j + step]
+        part = torch.clamp(1.0 + zz, min=0).sum().reshape(1)
+        return float(allreduce_dev(part)[0]) + lam * float(sol["x"] @ sol["x"])
+
+    return ProxAffineProblem([f0, f1], [c0], name="hinge_l2_%dx%d_device" % (m, n)), {
+        "objective": objective, "solution_var": "x", "lam": lam, "sharded_constraints": {0: m}, "keep": a}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("config", choices=["tv1d", "logreg", "hinge", "group_lasso", "lasso_dense", "lasso_sparse", "mv_lasso"])
-    ap.add_argument("--m", type=int, default=0)
-    ap.add_argument("--n", type=int, default=0)
+    # --rows / --cols: spellings torchrun's own parser does not mistake for abbreviations of its options
+    ap.add_argument("--m", "--rows", dest="m", type=int, default=0)
+    ap.add_argument("--n", "--cols", dest="n", type=int, default=0)
     ap.add_argument("--density", type=float, default=1.0)
     ap.add_argument("--group", type=int, default=50)
     ap.add_argument("--K", type=int, default=100)
@@ -37,16 +97,60 @@ def main():
     ap.add_argument("--kkt-mode", default="auto")
     ap.add_argument("--max-iterations", type=int, default=2000)
     ap.add_argument("--no-solve", action="store_true")
+    ap.add_argument("--no-profile", action="store_true")
+    ap.add_argument("--device-gen", action="store_true", help="hinge: generate the dense data block on the GPU")
     a = ap.parse_args()
+    # libraries print banners on fd 1 (NCCL's version line): keep the real stdout for the one JSON line
+    sys.stdout.flush()
+    real_stdout = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    import torch
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("cpu:gloo,cuda:nccl", rank=rank, world_size=world)
 
     from epsilon_b200 import problems
     from epsilon_b200.solver import Context, ProxADMMSolver
 
+    def allreduce(v):
+        if world == 1:
+            return v
+        t = torch.from_numpy(np.ascontiguousarray(v, dtype=np.float64).copy())
+        dist.all_reduce(t)
+        return t.numpy()
+
+    def allreduce_dev(t):
+        if world > 1:
+            dist.all_reduce(t)
+        return t
+
+    def max_over_ranks(v):
+        if world == 1:
+            return v
+        t = torch.tensor([v], dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t[0])
+
     t0 = time.time()
+    sharded_constraints = None
     if a.config == "tv1d":
         prob, info = problems.tv_1d(a.n or 10_000_000, seed=0)
+    elif a.config == "logreg" and (world > 1 or a.density < 1.0 and a.m >= 100_000):
+        per = 8 // world
+        prob, info = problems.logreg_l1_panels(a.m, a.n, a.density, panels=8, my_panels=range(rank * per, (rank + 1) * per),
+                                               seed=0, allreduce=allreduce)
+        sharded_constraints = info["sharded_constraints"] if world > 1 else None
     elif a.config == "logreg":
         prob, info = problems.logreg_l1(a.m, a.n, a.density, seed=0)
+    elif a.config == "hinge" and (a.device_gen or world > 1):
+        prob, info = hinge_l2_on_device(a.m, a.n, rank, world, 0, allreduce_dev)
+        sharded_constraints = info["sharded_constraints"] if world > 1 else None
     elif a.config == "hinge":
         prob, info = problems.hinge_l2(a.m, a.n, a.density, seed=0)
     elif a.config == "group_lasso":
@@ -66,51 +170,71 @@ def main():
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
 
-    ctx = Context(0)
+    ctx = Context(local_rank)
+    if world > 1:
+        uid = [Context.nccl_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        ctx.init_comm(world, rank, uid[0])
     params = {"kkt_mode": a.kkt_mode, "max_iterations": a.max_iterations}
-    out = {"config": a.config, "problem": prob.name, "data_generation_s": round(t_gen, 2)}
+    out = {"config": a.config, "problem": prob.name, "n_gpus": world, "data_generation_s": round(t_gen, 2)}
+    kw = dict(ctx=ctx, sharded_constraints=sharded_constraints)
 
     if not a.no_solve:
+        if world > 1:
+            dist.barrier()
         t0 = time.time()
-        s = ProxADMMSolver(prob, params, ctx=ctx)
+        s = ProxADMMSolver(prob, params, **kw)
         t_init = time.time() - t0
         x = s.solve()
         ctx.synchronize()
-        t_all = time.time() - t0
+        t_all = max_over_ranks(time.time() - t0)
         st = s.status.as_dict()
         out["solve"] = {"state": st["state"], "num_iterations": st["num_iterations"],
-                        "iterations_run": st["iterations_run"], "init_s": round(t_init, 4),
+                        "iterations_run": st["iterations_run"], "init_s": round(max_over_ranks(t_init), 4),
                         "loop_s": st["loop_ms"] / 1e3, "time_to_tol_s": round(t_all, 4),
                         "objective": info["objective"](x), "r_norm": st["r_norm"], "s_norm": st["s_norm"],
-                        "cg_iterations": st["cg_iterations"]}
+                        "cg_iterations": st["cg_iterations"], "cg_unconverged": st["cg_unconverged"],
+                        "m": st["m"], "n": st["n"]}
         out["solver"] = s.describe().strip().split("\n")
         s.close()
 
-    s = ProxADMMSolver(prob, params, ctx=ctx)
+    s = ProxADMMSolver(prob, params, **kw)
     s.iterate(a.warmup)
-    ms = s.iterate(a.steps)
+    if world > 1:
+        dist.barrier()
+    ms = max_over_ranks(s.iterate(a.steps))
     out["iterations_per_s"] = a.steps / (ms / 1e3)
     out["ms_per_iteration"] = ms / a.steps
+    out["cg_iterations_per_step"] = s.residuals()["cg_iterations"] / a.steps
+    if "solver" not in out:
+        out["solver"] = s.describe().strip().split("\n")
     s.close()
 
-    s = ProxADMMSolver(prob, dict(params, profile=1), ctx=ctx)
-    s.iterate(a.warmup)
-    base = s.profile()
-    s.iterate(a.steps)
-    prof = s.profile()
-    classes = {}
-    for k, v in prof.items():
-        b = base.get(k, {"launches": 0, "ms": 0.0, "bytes": 0.0})
-        l, t, by = v["launches"] - b["launches"], v["ms"] - b["ms"], v["bytes"] - b["bytes"]
-        if l > 0:
-            classes[k] = {"launches": l, "ms_per_iteration": t / a.steps, "us_per_launch": 1e3 * t / l,
-                          "GBps": by / (t / 1e3) / 1e9 if t > 0 else None,
-                          "frac_of_measured_hbm_peak": by / (t / 1e3) / 1e9 / peak if t > 0 else None}
-    out["classes"] = classes
+    if not a.no_profile:
+        s = ProxADMMSolver(prob, dict(params, profile=1), **kw)
+        s.iterate(a.warmup)
+        base = s.profile()
+        s.iterate(a.steps)
+        prof = s.profile()
+        classes = {}
+        for k, v in prof.items():
+            b = base.get(k, {"launches": 0, "ms": 0.0, "bytes": 0.0})
+            l, t, by = v["launches"] - b["launches"], v["ms"] - b["ms"], v["bytes"] - b["bytes"]
+            if l > 0:
+                classes[k] = {"launches": l, "ms_per_iteration": t / a.steps, "us_per_launch": 1e3 * t / l,
+                              "GBps": by / (t / 1e3) / 1e9 if t > 0 else None,
+                              "frac_of_measured_hbm_peak": by / (t / 1e3) / 1e9 / peak if t > 0 else None}
+        out["classes"] = classes
+        s.close()
     out["hbm_peak_GBps"] = peak
-    s.close()
+    if world > 1:
+        dist.barrier()
     ctx.close()
-    print(json.dumps(out))
+    if rank == 0:
+        real_stdout.write(json.dumps(out) + "\n")
+        real_stdout.flush()
+    if world > 1:
+        dist.destroy_process_group()
 
 
 if __name__ == "__main__":
