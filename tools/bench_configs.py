@@ -83,6 +83,70 @@ def hinge_l2_on_device(m, n, rank, world, seed, allreduce_dev, lam=1.0):
         "objective": objective, "solution_var": "x", "lam": lam, "sharded_constraints": {0: m}, "keep": a}
 
 
+def group_lasso_on_device(m, gs, K, rank, world, seed, allreduce_dev):
+    """group_lasso (problems/group_lasso.py with K equal groups of `gs`, as BASELINE config 4 asks) with the dense
+    m x n data matrix generated on the device, rows sharded over the ranks (the 500k x 50k matrix is 200 GB: it
+    does not fit one GPU).  Compiled form of epsilon_b200.problems.group_lasso; the SUM_SQUARE argument is the
+    row-sharded one (eps_problem_prox_arg_sharded)."""
+    import scipy.sparse as sp
+    import torch
+    from epsilon_b200.problem import Affine, LinearMapSpec, ProxAffineProblem, ProxFunction, Term, Variable
+    n = gs * K
+    lo, hi = rank * m // world, (rank + 1) * m // world
+    ml = hi - lo
+    dev = torch.device("cuda", torch.cuda.current_device())
+    g = torch.Generator(device=dev)
+    g.manual_seed(seed * 1000 + rank)
+    a = torch.empty((n, ml), dtype=torch.float64, device=dev)
+    step = max(1, (1 << 28) // max(ml, 1))
+    sq = torch.empty(n, dtype=torch.float64, device=dev)
+    for j in range(0, n, step):
+        blk = a[j:j + step]
+        blk.normal_(generator=g)
+        sq[j:j + step] = (blk * blk).sum(dim=1)
+    inv = 1.0 / torch.sqrt(allreduce_dev(sq))
+    rng = np.random.default_rng([seed, 10_000])
+    x0 = np.zeros(n)
+    for k in range(K):
+        if rng.random() < 0.2:
+            x0[k * gs:(k + 1) * gs] = rng.standard_normal(gs)
+    x0d = torch.from_numpy(x0).to(dev)
+    b = torch.zeros(ml, dtype=torch.float64, device=dev)
+    for j in range(0, n, step):
+        blk = a[j:j + step]
+        blk *= inv[j:j + step, None]
+        b += x0d[j:j + step] @ blk
+    b += np.sqrt(0.001) * torch.randn(ml, dtype=torch.float64, device=dev, generator=g)
+    atb = torch.empty(n, dtype=torch.float64, device=dev)
+    for j in range(0, n, step):
+        atb[j:j + step] = a[j:j + step] @ b
+    atb = allreduce_dev(atb).cpu().numpy()
+    lam = 0.1 * max(float(np.linalg.norm(atb[k * gs:(k + 1) * gs])) for k in range(K))
+    torch.cuda.synchronize()
+    x = Variable("x", n)
+    amap = LinearMapSpec(0, ml, n, name="A", device_ptr=a.data_ptr(), device_owner=a)
+    bh = b.cpu().numpy()
+    prox = [ProxFunction("SUM_SQUARE", alpha=0.5, args=[Affine(ml, [Term(x, amap), Term(bh, LinearMapSpec.Scalar(-1.0, ml), name="b")])])]
+    cons = []
+    for k in range(K):
+        tk = Variable("t%04d" % k, gs)
+        prox.append(ProxFunction("NORM_2", alpha=lam, args=[Affine(gs, [Term(tk)])]))
+        sel = sp.csc_matrix((np.ones(gs), (np.arange(gs), np.arange(k * gs, (k + 1) * gs))), shape=(gs, n))
+        cons.append(Affine(gs, [Term(x, LinearMapSpec.Sparse(sel, name="S%d" % k)), Term(tk, LinearMapSpec.Scalar(-1.0, gs))]))
+
+    def objective(sol):
+        xv = torch.from_numpy(np.ascontiguousarray(sol["x"])).to(dev)
+        r = -b.clone()
+        for j in range(0, n, step):
+            r += xv[j:j + step] @ a[j:j + step]
+        part = (r @ r).reshape(1)
+        return 0.5 * float(allreduce_dev(part)[0]) + lam * sum(
+            float(np.linalg.norm(sol["x"][k * gs:(k + 1) * gs])) for k in range(K))
+
+    return ProxAffineProblem(prox, cons, name="group_lasso_%dx%d_device" % (m, n)), {
+        "objective": objective, "solution_var": "x", "lam": lam, "sharded_args": {(0, 0): m}, "keep": a}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("config", choices=["tv1d", "logreg", "hinge", "group_lasso", "lasso_dense", "lasso_sparse", "mv_lasso"])
@@ -98,6 +162,7 @@ def main():
     ap.add_argument("--max-iterations", type=int, default=2000)
     ap.add_argument("--no-solve", action="store_true")
     ap.add_argument("--no-profile", action="store_true")
+    ap.add_argument("--reuse-solver", action="store_true", help="time the iterations on the solver of the solve (one Init)")
     ap.add_argument("--device-gen", action="store_true", help="hinge: generate the dense data block on the GPU")
     a = ap.parse_args()
     # libraries print banners on fd 1 (NCCL's version line): keep the real stdout for the one JSON line
@@ -139,6 +204,7 @@ def main():
 
     t0 = time.time()
     sharded_constraints = None
+    sharded_args = None
     if a.config == "tv1d":
         prob, info = problems.tv_1d(a.n or 10_000_000, seed=0)
     elif a.config == "logreg" and (world > 1 or a.density < 1.0 and a.m >= 100_000):
@@ -153,6 +219,9 @@ def main():
         sharded_constraints = info["sharded_constraints"] if world > 1 else None
     elif a.config == "hinge":
         prob, info = problems.hinge_l2(a.m, a.n, a.density, seed=0)
+    elif a.config == "group_lasso" and (a.device_gen or world > 1):
+        prob, info = group_lasso_on_device(a.m, a.group, a.K, rank, world, 0, allreduce_dev)
+        sharded_args = info["sharded_args"] if world > 1 else None
     elif a.config == "group_lasso":
         prob, info = problems.group_lasso(a.m, a.group, a.K, seed=0)
     elif a.config == "mv_lasso":
@@ -177,7 +246,7 @@ def main():
         ctx.init_comm(world, rank, uid[0])
     params = {"kkt_mode": a.kkt_mode, "max_iterations": a.max_iterations}
     out = {"config": a.config, "problem": prob.name, "n_gpus": world, "data_generation_s": round(t_gen, 2)}
-    kw = dict(ctx=ctx, sharded_constraints=sharded_constraints)
+    kw = dict(ctx=ctx, sharded_constraints=sharded_constraints, sharded_args=sharded_args)
 
     if not a.no_solve:
         if world > 1:
@@ -195,10 +264,12 @@ def main():
                         "objective": info["objective"](x), "r_norm": st["r_norm"], "s_norm": st["s_norm"],
                         "cg_iterations": st["cg_iterations"], "cg_unconverged": st["cg_unconverged"],
                         "m": st["m"], "n": st["n"]}
-        out["solver"] = s.describe().strip().split("\n")
-        s.close()
+        out["solver"] = s.describe().strip().split("\n")[:12]
+        if not a.reuse_solver:
+            s.close()
 
-    s = ProxADMMSolver(prob, params, **kw)
+    if a.no_solve or not a.reuse_solver:
+        s = ProxADMMSolver(prob, params, **kw)
     s.iterate(a.warmup)
     if world > 1:
         dist.barrier()
@@ -207,7 +278,7 @@ def main():
     out["ms_per_iteration"] = ms / a.steps
     out["cg_iterations_per_step"] = s.residuals()["cg_iterations"] / a.steps
     if "solver" not in out:
-        out["solver"] = s.describe().strip().split("\n")
+        out["solver"] = s.describe().strip().split("\n")[:12]
     s.close()
 
     if not a.no_profile:
