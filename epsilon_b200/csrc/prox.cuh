@@ -34,6 +34,10 @@ struct SegPair {
 void ElemProxStep(Ctx* ctx, const ElemSeg* segs_dev, const int64_t* prefix_dev, int nseg,
                   int64_t total, int type, const double* consts, double* u, const double* y_old,
                   double* y_new, double* x);
+// The same for a stage of ONE segment with even offsets: 128-bit accesses, no segment search (host copy of the
+// segment passed by value).
+void ElemProxStepSingle(Ctx* ctx, const ElemSeg& seg, const double* consts, double* u, const double* y_old,
+                        double* y_new, double* x);
 // NORM_2 block soft threshold, one warp (len <= 1024) or one CTA per segment.
 void Norm2ProxStep(Ctx* ctx, const ElemSeg* segs_dev, int nseg, int max_len, const double* consts,
                    double* u, const double* y_old, double* y_new, double* x);

@@ -183,7 +183,112 @@ ElemProxKernel(const ElemSeg* __restrict__ segs, const int64_t* __restrict__ pre
   }
 }
 
+// One prox value (everything after v = Bs*w + g has been formed); LOGISTIC / NEWTON are warp-cooperative: every
+// lane of the warp must make the call.
+template <int TYPE>
+__device__ __forceinline__ double ProxValue(const ElemSeg& sg, const double* __restrict__ consts, int64_t j,
+                                            double v, bool active) {
+  if (TYPE == EPS_PROX_SUM_LOGISTIC) return LogisticProx(v, sg.lam, active);
+  if (TYPE == EPS_PROX_SUM_EXP || TYPE == EPS_PROX_SUM_NEG_ENTR || TYPE == EPS_PROX_SUM_INV_POS)
+    return NewtonProxElem<TYPE>(v, sg.lam, active);
+  if (!active) return 0.0;
+  if (TYPE == EPS_PROX_SUM_NEG_LOG) return NegLogProx(v, sg.lam);
+  if (TYPE == EPS_PROX_NON_NEGATIVE) return fmax(v, 0.0);
+  if (TYPE == EPS_PROX_SUM_QUANTILE) {
+    const double a = sg.q_off >= 0 ? consts[sg.q_off + j] : sg.zone_alpha;
+    const double b = sg.q_off >= 0 ? consts[sg.q_off + sg.len + j] : sg.zone_beta;
+    return ScaledZone(v, sg.lam, 0.0, a, b);
+  }
+  return ScaledZone(v, sg.lam, sg.zone_m, sg.zone_alpha, sg.zone_beta);
+}
+
+// Single-segment stage (the large vectors: t of a logistic regression / SVM, x of a lasso): no segment search, the
+// segment descriptor travels as a kernel argument, and every access is a 128-bit load or store of two consecutive
+// elements (u, y_old [, g] in; x, y_new, u out).  Needs even offsets (16-byte alignment); an odd last element is
+// finished by the first warp of CTA 0.
+constexpr int kVecPairs = 2;   // double2 pairs per thread and pass
+template <int TYPE>
+__global__ void __launch_bounds__(kBlock)
+ElemProxVec2Kernel(ElemSeg sg, const double* __restrict__ consts, double* __restrict__ u,
+                   const double* __restrict__ y_old, double* __restrict__ y_new, double* __restrict__ x) {
+  const int64_t n2 = sg.len / 2;
+  double2* u2 = reinterpret_cast<double2*>(u + sg.u_off);
+  const double2* yo2 = reinterpret_cast<const double2*>(y_old + sg.y_off);
+  double2* yn2 = reinterpret_cast<double2*>(y_new + sg.y_off);
+  double2* x2 = reinterpret_cast<double2*>(x + sg.x_off);
+  const double2* g2 = sg.g_off >= 0 ? reinterpret_cast<const double2*>(consts + sg.g_off) : nullptr;
+  const int64_t stride = (int64_t)gridDim.x * kBlock * kVecPairs;
+  for (int64_t base = (int64_t)blockIdx.x * kBlock * kVecPairs + threadIdx.x; base - threadIdx.x < n2; base += stride) {
+    double2 w[kVecPairs], g[kVecPairs];
+    bool act[kVecPairs];
+#pragma unroll
+    for (int k = 0; k < kVecPairs; k++) {
+      const int64_t p = base + (int64_t)k * kBlock;
+      act[k] = p < n2;
+      w[k] = make_double2(0.0, 0.0);
+      g[k] = make_double2(0.0, 0.0);
+      if (act[k]) {
+        const double2 a = u2[p], b = LdStream2(reinterpret_cast<const double*>(yo2 + p));
+        w[k] = make_double2(a.x + b.x, a.y + b.y);
+        if (g2) g[k] = g2[p];
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < kVecPairs; k++) {
+      const int64_t p = base + (int64_t)k * kBlock;
+      const double xa = ProxValue<TYPE>(sg, consts, 2 * p, sg.Bs * w[k].x + g[k].x, act[k]);
+      const double xb = ProxValue<TYPE>(sg, consts, 2 * p + 1, sg.Bs * w[k].y + g[k].y, act[k]);
+      if (act[k]) {
+        const double2 xv = make_double2(sg.Cs * (xa - g[k].x), sg.Cs * (xb - g[k].y));
+        const double2 yn = make_double2(sg.As * xv.x, sg.As * xv.y);
+        x2[p] = xv;
+        yn2[p] = yn;
+        u2[p] = make_double2(w[k].x - yn.x, w[k].y - yn.y);
+      }
+    }
+  }
+  if ((sg.len & 1) && blockIdx.x == 0 && threadIdx.x < 32) {
+    const int64_t j = sg.len - 1;
+    const bool active = threadIdx.x == 0;
+    double w = 0.0, g = 0.0;
+    if (active) {
+      w = u[sg.u_off + j] + y_old[sg.y_off + j];
+      g = sg.g_off >= 0 ? consts[sg.g_off + j] : 0.0;
+    }
+    const double xo = ProxValue<TYPE>(sg, consts, j, sg.Bs * w + g, active);
+    if (active) {
+      const double xv = sg.Cs * (xo - g);
+      const double yn = sg.As * xv;
+      x[sg.x_off + j] = xv;
+      y_new[sg.y_off + j] = yn;
+      u[sg.u_off + j] = w - yn;
+    }
+  }
+}
+
 }  // namespace
+
+void ElemProxStepSingle(Ctx* ctx, const ElemSeg& sg, const double* consts, double* u, const double* y_old,
+                        double* y_new, double* x) {
+  ProfScope ps(ctx, KC_PROX, 40.0 * sg.len);
+  const int grid = GridFor(sg.len / 2 + 1, kBlock, kVecPairs, ctx->sm_count);
+#define LAUNCHV(T) ElemProxVec2Kernel<T><<<grid, kBlock, 0, ctx->stream>>>(sg, consts, u, y_old, y_new, x)
+  switch (sg.type) {
+    case EPS_PROX_NON_NEGATIVE: LAUNCHV(EPS_PROX_NON_NEGATIVE); break;
+    case EPS_PROX_SUM_QUANTILE: LAUNCHV(EPS_PROX_SUM_QUANTILE); break;
+    case EPS_PROX_SUM_LOGISTIC: LAUNCHV(EPS_PROX_SUM_LOGISTIC); break;
+    case EPS_PROX_SUM_EXP: LAUNCHV(EPS_PROX_SUM_EXP); break;
+    case EPS_PROX_SUM_NEG_ENTR: LAUNCHV(EPS_PROX_SUM_NEG_ENTR); break;
+    case EPS_PROX_SUM_INV_POS: LAUNCHV(EPS_PROX_SUM_INV_POS); break;
+    case EPS_PROX_SUM_NEG_LOG: LAUNCHV(EPS_PROX_SUM_NEG_LOG); break;
+    case EPS_PROX_NORM_1:
+    case EPS_PROX_SUM_HINGE:
+    case EPS_PROX_SUM_DEADZONE: LAUNCHV(EPS_PROX_NORM_1); break;
+    default: throw Error(EPS_ERR_INVALID, Format("prox type %d is not elementwise", sg.type));
+  }
+#undef LAUNCHV
+  ctx->count_launch();
+}
 
 void ElemProxStep(Ctx* ctx, const ElemSeg* segs, const int64_t* prefix, int nseg, int64_t total,
                   int type, const double* consts, double* u, const double* y_old, double* y_new,
