@@ -206,7 +206,8 @@ void ProxADMMGpuSolver::Build(const std::vector<Affine>& exprs) {
     int fi = -1;
     EPS_OK_OR_FATAL(eps_problem_add_prox(prob_, f.prox_function_type(), f.alpha(), f.epigraph(), &fi));
     CHECK_EQ(fi, i);
-    CHECK(!f.has_axis()) << "axis-wise prox functions stay on the CPU path";
+    if (f.has_axis())                                               // vector_prox.cc:150-177
+      EPS_OK_OR_FATAL(eps_problem_prox_axis(prob_, fi, f.axis(), f.arg_size(0).dim(0), f.arg_size(0).dim(1)));
     switch (f.prox_function_type()) {
       case ProxFunction::SUM_DEADZONE:
         EPS_OK_OR_FATAL(eps_problem_prox_zone(prob_, fi, f.scaled_zone_params().m(), nullptr, nullptr, 0));

@@ -106,6 +106,7 @@ SIGNATURES = {
     "eps_problem_prox_soc_dims": (C.c_int, [_P, C.c_int, C.c_int, C.c_int]),
     "eps_problem_prox_mat_dims": (C.c_int, [_P, C.c_int, C.c_int, C.c_int]),
     "eps_problem_prox_zone": (C.c_int, [_P, C.c_int, C.c_double, _DP, _DP, C.c_int]),
+    "eps_problem_prox_axis": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, C.c_int]),
     "eps_problem_prox_add_arg": (C.c_int, [_P, C.c_int, C.c_int, C.POINTER(C.c_int)]),
     "eps_problem_prox_arg_sharded": (C.c_int, [_P, C.c_int, C.c_int, C.c_int64]),
     "eps_problem_constraint_sharded": (C.c_int, [_P, C.c_int, C.c_int64]),

@@ -25,13 +25,13 @@ void eps_solver::RunStages(const double* yo, double* yn) {
         const ElemSeg& sg = ops[st.members[0]].seg;
         static const bool no_vec = getenv("EPS_PROX_SCALAR") != nullptr;
         const bool vec2 = nseg == 1 && !no_vec && ((sg.u_off | sg.y_off | sg.x_off) & 1) == 0 &&
-                          (sg.g_off < 0 || (sg.g_off & 1) == 0) && sg.q_off < 0;
+                          (sg.g_off < 0 || (sg.g_off & 1) == 0) && sg.q_off < 0 && sg.d_off < 0;
         if (vec2) ElemProxStepSingle(ctx, sg, consts.p, u.p, yo, yn, x.p);
         else ElemProxStep(ctx, st.segs.p, st.prefix.p, nseg, st.total, st.type, consts.p, u.p, yo, yn, x.p);
         break;
       }
       case ST_NORM2:
-        Norm2ProxStep(ctx, st.segs.p, nseg, st.max_len, consts.p, u.p, yo, yn, x.p);
+        Norm2ProxStep(ctx, st.segs.p, st.n_segs, st.max_len, consts.p, u.p, yo, yn, x.p);
         break;
       case ST_TV:
         Tv1dProxStep(ctx, ops[st.members[0]].seg, consts.p, u.p, yo, yn, x.p, st.tv_work.p, &st.tv_tag);

@@ -26,6 +26,7 @@ struct ProxOp {
   double a = 0;
   std::unique_ptr<KktSolver> kkt;
   ElemSeg seg;                  // elementwise / block / tv operators
+  std::vector<ElemSeg> axis_segs;   // NORM_2 with has_axis: one segment per column / row (replaces `seg` in the stage)
   // multi-argument / sort-based vector operators (ST_VEC): the general form of the VectorProx
   // scalar reduction, v = (beta/gamma) H A'w + g, x = (1/beta) H'(x' - g)  (vector_prox.cc:59-67,131-137)
   BlockOp Hop;
@@ -55,6 +56,7 @@ struct Stage {
   DevBuf<int64_t> prefix;
   int64_t total = 0;
   int max_len = 0;
+  int n_segs = 0;               // entries of `segs` (more than members when an operator acts axis-wise)
   DevBuf<double> tv_work;
   unsigned tv_tag = 0;          // last round tag of the TV solver's slot maxima (tv1d_par.cu)
 };

@@ -481,16 +481,27 @@ void eps_solver::Init(const eps_problem& original) {
       const BlockOp& H = Hs[i];
       EPS_CHECK(f.args.size() == 1 && op.vars.size() == 1,
                 "prox %d (%s): one argument over one variable expected", i, TypeName(f.type));
-      EPS_CHECK(H.blks.size() == 1 && H.blks[0].map->kind == MK_SCALAR && H.rows == op.n,
-                "prox %d (%s): argument must be a scalar multiple of its variable "
-                "(diagonal / general H is not supported on the device path)", i, TypeName(f.type));
+      EPS_CHECK(H.blks.size() == 1 && H.blks[0].diag_like() && H.rows == op.n,
+                "prox %d (%s): argument must be a scalar or diagonal multiple of its variable "
+                "(a general H is a reference CHECK too, vector_prox.cc:118-120)", i, TypeName(f.type));
       EPS_CHECK(op.simple_scalar,
                 "prox %d (%s): the variable must enter exactly one constraint through a scalar map", i,
                 TypeName(f.type));
-      const double h = H.blks[0].scale * H.blks[0].map->alpha;
+      const bool h_diagonal = H.blks[0].map->kind == MK_DIAGONAL;
+      // diagonal H: the scalar reduction is tried first, as in VectorProx::Init (vector_prox.cc:118-119)
+      bool h_const = true;
+      if (h_diagonal)
+        for (double d : H.blks[0].map->h_diag) h_const = h_const && d == H.blks[0].map->h_diag[0];
+      const double h = H.blks[0].scale * (h_diagonal ? H.blks[0].map->h_diag[0] : H.blks[0].map->alpha);
       const double a = op.a;
-      const double beta = h * h;
-      const double gamma = ((h * a) * a) * h;
+      const bool diag_reduction = h_diagonal && (!h_const || h == 0.0);
+      EPS_CHECK(!diag_reduction || IsElemType(f.type),
+                "prox %d (%s): a diagonally weighted argument needs an elementwise lambda, which this operator "
+                "does not take (VectorProxInput::lambda, vector_prox.cc:185-188)", i, TypeName(f.type));
+      EPS_CHECK(f.axis < 0 || f.type == EPS_PROX_NORM_2,
+                "prox %d (%s): has_axis is supported for NORM_2 only on the device path", i, TypeName(f.type));
+      const double beta = diag_reduction ? 1.0 : h * h;
+      const double gamma = diag_reduction ? 1.0 : ((h * a) * a) * h;
       EPS_CHECK(gamma > 0, "prox %d: H A'A H' = %g", i, gamma);
       ElemSeg& s = op.seg;
       s.u_off = op.span_lo;
@@ -509,6 +520,35 @@ void eps_solver::Init(const eps_problem& original) {
         consts_host.insert(consts_host.end(), g_hosts[i].begin(), g_hosts[i].end());
       }
       s.q_off = -1;
+      s.d_off = -1;
+      s.stride = 1;
+      if (diag_reduction) {
+        // VectorProx::InitDiagonal (vector_prox.cc:72-116) with H = diag(h_i), A = a I:
+        //   beta_i = h_i^2, gamma_i = h_i^2 a^2; where gamma_i == 0: lambda_i = 0, beta_i = gamma_i = delta_i = 1
+        //   B = H diag(beta/gamma) A',  C = diag(1/beta) H',  D = (A'A)^-1 diag(delta) A',  lambda_i = alpha beta_i^2/gamma_i
+        const std::vector<double>& hd = H.blks[0].map->h_diag;
+        const double hs = H.blks[0].scale;
+        s.d_off = (int64_t)consts_host.size();
+        consts_host.resize(consts_host.size() + 4 * (size_t)op.n);
+        double* Bv = consts_host.data() + s.d_off;
+        double* Cv = Bv + op.n;
+        double* Dv = Cv + op.n;
+        double* Lv = Dv + op.n;
+        for (int64_t j = 0; j < op.n; j++) {
+          const double hj = hs * hd[j];
+          double bj = hj * hj, gj = ((hj * a) * a) * hj, dj = 0.0, lj;
+          if (gj != 0.0) {
+            lj = f.alpha * bj * bj / gj;
+          } else {
+            lj = 0.0; bj = 1.0; gj = 1.0; dj = 1.0;
+          }
+          EPS_CHECK(lj >= 0, "lambda = %g < 0", lj);
+          Bv[j] = (hj * (bj / gj)) * a;
+          Cv[j] = (1 / bj) * hj;
+          Dv[j] = (1 / (a * a)) * dj * a;
+          Lv[j] = lj;
+        }
+      }
       s.zone_m = 0; s.zone_alpha = 1; s.zone_beta = 1;
       if (f.type == EPS_PROX_SUM_DEADZONE) s.zone_m = f.zone_m;
       if (f.type == EPS_PROX_SUM_HINGE) s.zone_beta = 0;
@@ -525,9 +565,26 @@ void eps_solver::Init(const eps_problem& original) {
           consts_host.insert(consts_host.end(), f.q_beta.begin(), f.q_beta.end());
         }
       }
-      description += Format("prox %d %s n=%lld rows=[%lld,+%lld) lambda=%.6g B=%g C=%g A=%g\n", i,
+      if (f.axis >= 0) {
+        // has_axis: one NORM_2 segment per column (axis 0) or row (axis 1) of mat(arg, m, n), column-major
+        EPS_CHECK((int64_t)f.ax_m * f.ax_n == op.n, "prox %d: axis dims %d x %d vs %lld entries", i, f.ax_m, f.ax_n,
+                  (long long)op.n);
+        const int k = f.axis == 0 ? f.ax_n : f.ax_m;
+        for (int q = 0; q < k; q++) {
+          ElemSeg t = s;
+          const int64_t first = f.axis == 0 ? (int64_t)q * f.ax_m : q;
+          t.u_off += first; t.y_off += first; t.x_off += first;
+          if (t.g_off >= 0) t.g_off += first;
+          t.len = f.axis == 0 ? f.ax_m : f.ax_n;
+          t.stride = f.axis == 0 ? 1 : f.ax_m;
+          op.axis_segs.push_back(t);
+        }
+      }
+      description += Format("prox %d %s n=%lld rows=[%lld,+%lld) lambda=%.6g B=%g C=%g A=%g%s%s\n", i,
                             TypeName(f.type), (long long)op.n, (long long)op.span_lo,
-                            (long long)op.span_len, s.lam, s.Bs, s.Cs, s.As);
+                            (long long)op.span_len, s.lam, s.Bs, s.Cs, s.As,
+                            diag_reduction ? " (diagonal reduction: per-element B, C, D, lambda)" : "",
+                            f.axis >= 0 ? (f.axis == 0 ? " axis=0 (columns)" : " axis=1 (rows)") : "");
     } else {
       throw Error(EPS_ERR_INVALID, Format("prox %d: type %d (%s) has no device operator", i, f.type, TypeName(f.type)));
     }
@@ -568,7 +625,8 @@ void eps_solver::Init(const eps_problem& original) {
     st.scalar_a = true;
     for (int j : st.members) {
       const ProxOp& op = ops[j];
-      segs.push_back(op.seg);
+      if (op.axis_segs.empty()) segs.push_back(op.seg);
+      else segs.insert(segs.end(), op.axis_segs.begin(), op.axis_segs.end());
       SegPair pr;
       pr.a_off = op.span_lo;
       pr.b_off = op.y_off;
@@ -576,9 +634,11 @@ void eps_solver::Init(const eps_problem& original) {
       pr.coef = op.a * op.a;
       st.pairs_host.push_back(pr);
       prefix.push_back(prefix.back() + op.span_len);
-      st.max_len = std::max<int>(st.max_len, (int)op.span_len);
+      if (op.axis_segs.empty()) st.max_len = std::max<int>(st.max_len, (int)op.span_len);
+      else st.max_len = std::max<int>(st.max_len, op.axis_segs[0].len);
       if (!op.simple_scalar) st.scalar_a = false;
     }
+    st.n_segs = (int)segs.size();
     st.total = prefix.back();
     st.segs.alloc(ctx, segs.size());
     st.segs.upload(segs.data(), segs.size());

@@ -96,6 +96,16 @@ int eps_problem_prox_mat_dims(eps_problem* p, int prox_index, int m, int n) {
   EPS_API_END
 }
 
+int eps_problem_prox_axis(eps_problem* p, int prox_index, int axis, int m, int n) {
+  EPS_API_BEGIN
+  EPS_CHECK(p && prox_index >= 0 && prox_index < (int)p->prox.size() && (axis == 0 || axis == 1) && m > 0 && n > 0,
+            "prox index %d, axis %d over %d x %d", prox_index, axis, m, n);
+  p->prox[prox_index].axis = axis;
+  p->prox[prox_index].ax_m = m;
+  p->prox[prox_index].ax_n = n;
+  EPS_API_END
+}
+
 int eps_problem_prox_add_arg(eps_problem* p, int prox_index, int rows, int* arg_index) {
   EPS_API_BEGIN
   EPS_CHECK(p && prox_index >= 0 && prox_index < (int)p->prox.size() && rows >= 0, "prox index %d", prox_index);

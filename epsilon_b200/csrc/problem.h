@@ -26,6 +26,7 @@ struct ProxFn {
   int sum_largest_k = 0;
   int soc_m = 0, soc_n = 0;
   int mat_m = 0, mat_n = 0;
+  int axis = -1, ax_m = 0, ax_n = 0;   // has_axis / axis / arg_size(0) (vector_prox.cc:150-177)
   std::vector<double> q_alpha, q_beta;
   std::vector<AffineExpr> args;
 };

@@ -18,6 +18,12 @@ struct ElemSeg {
   int64_t x_off;   // offset of x_i in the x arena
   int64_t g_off;   // offset of g in the constant arena, -1 when absent
   int64_t q_off;   // SUM_QUANTILE: alpha at q_off, beta at q_off + len; -1 otherwise
+  // VectorProx::InitDiagonal (vector_prox.cc:72-116): per-element B, C, D, lambda at d_off, d_off + len,
+  // d_off + 2 len, d_off + 3 len of the constant arena; x = C (x' - g) + D w.  -1: the scalar reduction.
+  int64_t d_off;
+  // has_axis (vector_prox.cc:150-177): a NORM_2 segment is one column (stride 1) or one row (stride = rows) of the
+  // column-major matrix argument; element k sits at offset + k * stride
+  int64_t stride;
   int32_t len;
   int32_t type;    // eps_prox_type
   double lam, Bs, Cs, As;

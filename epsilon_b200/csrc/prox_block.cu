@@ -26,9 +26,10 @@ Norm2Kernel(const ElemSeg* __restrict__ segs, int nseg, const double* __restrict
   if (valid) sg = segs[seg_id];
   const int len = valid ? sg.len : 0;
   double ss[1] = {0.0};
+  const int64_t st = valid ? sg.stride : 1;   // 1: contiguous block / column; rows of a matrix argument: its row count
   for (int j = t; j < len; j += GROUP) {
-    const double w = u[sg.u_off + j] + y_old[sg.y_off + j];
-    const double g = sg.g_off >= 0 ? consts[sg.g_off + j] : 0.0;
+    const double w = u[sg.u_off + j * st] + y_old[sg.y_off + j * st];
+    const double g = sg.g_off >= 0 ? consts[sg.g_off + j * st] : 0.0;
     const double v = sg.Bs * w + g;
     ss[0] += v * v;
   }
@@ -47,15 +48,15 @@ Norm2Kernel(const ElemSeg* __restrict__ segs, int nseg, const double* __restrict
   const bool keep = nrm >= sg.lam;
   const double scale = keep ? 1.0 - sg.lam / nrm : 0.0;
   for (int j = t; j < len; j += GROUP) {
-    const double w = u[sg.u_off + j] + y_old[sg.y_off + j];
-    const double g = sg.g_off >= 0 ? consts[sg.g_off + j] : 0.0;
+    const double w = u[sg.u_off + j * st] + y_old[sg.y_off + j * st];
+    const double g = sg.g_off >= 0 ? consts[sg.g_off + j * st] : 0.0;
     const double v = sg.Bs * w + g;
     const double xo = keep ? scale * v : 0.0;
     const double xv = sg.Cs * (xo - g);
     const double yn = sg.As * xv;
-    x[sg.x_off + j] = xv;
-    y_new[sg.y_off + j] = yn;
-    u[sg.u_off + j] = w - yn;
+    x[sg.x_off + j * st] = xv;
+    y_new[sg.y_off + j * st] = yn;
+    u[sg.u_off + j * st] = w - yn;
   }
 }
 

@@ -143,7 +143,7 @@ ElemProxKernel(const ElemSeg* __restrict__ segs, const int64_t* __restrict__ pre
     for (int k = 0; k < kUnroll; k++) {
       const int64_t e = base + (int64_t)k * kBlock;
       const bool active = e < total;
-      double w = 0, v = 0, g = 0, lam = 0, xo = 0;
+      double w = 0, v = 0, g = 0, lam = 0, xo = 0, dcoef = 0;
       int64_t j = 0;
       ElemSeg sg;
       if (active) {
@@ -152,6 +152,13 @@ ElemProxKernel(const ElemSeg* __restrict__ segs, const int64_t* __restrict__ pre
         j = e - prefix[si];
         w = u[sg.u_off + j] + y_old[sg.y_off + j];
         g = sg.g_off >= 0 ? consts[sg.g_off + j] : 0.0;
+        // InitDiagonal (vector_prox.cc:72-116): B, C, D, lambda per element
+        if (sg.d_off >= 0) {
+          sg.Bs = consts[sg.d_off + j];
+          sg.Cs = consts[sg.d_off + sg.len + j];
+          dcoef = consts[sg.d_off + 2 * (int64_t)sg.len + j];
+          sg.lam = consts[sg.d_off + 3 * (int64_t)sg.len + j];
+        }
         v = sg.Bs * w + g;
         lam = sg.lam;
       }
@@ -173,7 +180,8 @@ ElemProxKernel(const ElemSeg* __restrict__ segs, const int64_t* __restrict__ pre
         }
       }
       if (active) {
-        const double xv = sg.Cs * (xo - g);
+        double xv = sg.Cs * (xo - g);
+        if (sg.d_off >= 0) xv = xv + dcoef * w;     // PostProcessOutput: C (x' - g) + D v
         const double yn = sg.As * xv;
         x[sg.x_off + j] = xv;
         y_new[sg.y_off + j] = yn;

@@ -168,6 +168,9 @@ class ProxFunction:
     # matrix functions (LAMBDA_MAX, NEG_LOG_DET, NORM_NUCLEAR, SEMIDEFINITE): (m, n) of the matrix argument
     # mat(x, m, n), column-major (arg_size(0), ortho_invariant.cc:12-16)
     mat_dims: Optional[Tuple[int, int]] = None
+    # has_axis / axis (expression.proto:193-195): apply to every column (0) or row (1) of mat(arg0, *axis_dims)
+    axis: Optional[int] = None
+    axis_dims: Optional[Tuple[int, int]] = None
 
 
 @dataclass

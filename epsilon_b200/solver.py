@@ -209,6 +209,9 @@ class _ProblemBuilder:
             if f.mat_dims is not None:
                 capi.check(self.lib.eps_problem_prox_mat_dims(self.handle, fi.value, int(f.mat_dims[0]),
                                                               int(f.mat_dims[1])))
+            if f.axis is not None:
+                capi.check(self.lib.eps_problem_prox_axis(self.handle, fi.value, int(f.axis), int(f.axis_dims[0]),
+                                                          int(f.axis_dims[1])))
             if f.type == "SUM_LARGEST":
                 capi.check(self.lib.eps_problem_prox_sum_largest(self.handle, fi.value, int(f.sum_largest_k)))
             for ai_, a in enumerate(f.args):

@@ -178,6 +178,10 @@ int eps_problem_prox_soc_dims(eps_problem* p, int prox_index, int m, int n);
 /* Matrix functions (LAMBDA_MAX, NEG_LOG_DET, NORM_NUCLEAR, SEMIDEFINITE): the first argument is
  * mat(x, m, n), column-major; m, n = ProxFunction.arg_size(0).dim (src/epsilon/prox/ortho_invariant.cc:12-16). */
 int eps_problem_prox_mat_dims(eps_problem* p, int prox_index, int m, int n);
+/* ProxFunction.has_axis / axis (expression.proto:193-195; VectorProx::Apply, vector_prox.cc:150-177): the operator
+ * acts on every column (axis 0) or every row (axis 1) of mat(arg, m, n), m, n = arg_size(0).  On the device:
+ * NORM_2 (the row / column group norms of a matrix variable); other types return EPS_ERR_INVALID. */
+int eps_problem_prox_axis(eps_problem* p, int prox_index, int axis, int m, int n);
 int eps_problem_prox_add_arg(eps_problem* p, int prox_index, int rows, int* arg_index);
 /* Row-sharded argument (multi-GPU): the rows given to this rank are its slice of an
  * argument with `global_rows` rows; products H'H p and H'g are all-reduced. */

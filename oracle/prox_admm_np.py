@@ -902,6 +902,19 @@ class _VectorProx:
             return np.maximum(v, 0.0)                                   # non_negative.cc:5-9
         if t == "NORM_2":
             assert self.scalar
+            if getattr(self.f, "axis", None) is not None:
+                # has_axis (vector_prox.cc:150-177): ApplyVector once per column (axis 0) / row (axis 1) of
+                # mat(arg 0, m, n), column-major (ToMatrix, vector_util.cc:202-209)
+                m, n = self.f.axis_dims
+                V = v.reshape((m, n), order="F")
+                X = np.empty_like(V)
+                if self.f.axis == 0:
+                    for c in range(n):
+                        X[:, c] = norm2_block(V[:, c], float(self.lam[0]))
+                else:
+                    for r in range(m):
+                        X[r, :] = norm2_block(np.ascontiguousarray(V[r, :]), float(self.lam[0]))
+                return X.ravel(order="F")
             return norm2_block(v, float(self.lam[0]))
         if t == "SUM_LOGISTIC":
             return newton_logistic(v, self.lam)

@@ -100,8 +100,12 @@ class _RefWriter:
                 pf += " arg_size { dim: %d dim: %d }" % tuple(f.soc_dims)
             elif f.mat_dims is not None and k == 0:
                 pf += " arg_size { dim: %d dim: %d }" % tuple(f.mat_dims)
+            elif getattr(f, "axis", None) is not None and k == 0:
+                pf += " arg_size { dim: %d dim: %d }" % tuple(f.axis_dims)
             else:
                 pf += " arg_size { dim: %d dim: 1 }" % a.rows
+        if getattr(f, "axis", None) is not None:
+            pf += " has_axis: true axis: %d" % int(f.axis)
         if f.type == "SUM_DEADZONE":
             pf += " scaled_zone_params { m: %s }" % repr(float(f.zone_m))
         if f.type == "SUM_LARGEST":

@@ -58,6 +58,10 @@ SOLVE_CASES = {
     "mv_lasso_120x60x4": ("mv_lasso", (120, 60, 4), {"seed": 2}, {}),
     "mv_lasso_sparse_3000x300x5": ("mv_lasso", (3000, 300, 5), {"density": 0.02, "seed": 3}, {}),
     "l1_epigraph_denoise_300": ("l1_epigraph_denoise", (300,), {"seed": 1}, {"max_iterations": 400}),
+    # VectorProx::InitDiagonal (weights with exact zeros) and has_axis (row norms of a matrix variable)
+    "weighted_lasso_200x300": ("weighted_lasso", (200, 300), {"seed": 16}, {"max_iterations": 300}),
+    "weighted_lasso_sparse_4000x400": ("weighted_lasso", (4000, 400), {"density": 0.02, "seed": 17}, {"max_iterations": 300}),
+    "mv_row_group_lasso_60x80x4": ("mv_row_group_lasso", (60, 80, 4), {"seed": 18}, {"max_iterations": 300}),
     "nuclear_denoise_30x12": ("nuclear_denoise", (30, 12), {"seed": 2}, {"max_iterations": 400, "rel_tol": 1e-5, "abs_tol": 1e-6}),
     "covsel_12": ("sparse_inverse_covariance", (12,), {"seed": 3}, {"max_iterations": 600, "rel_tol": 1e-5, "abs_tol": 1e-6}),
 }
@@ -270,6 +274,29 @@ def prox_cases():
                                     {"x": rng4.standard_normal(176), "t": np.array([8.0])})
     out["semidefinite"] = (mat("SEMIDEFINITE", 16, 16), 1.0, {"x": rng4.standard_normal(256)})
     out["semidefinite_64"] = (mat("SEMIDEFINITE", 64, 64), 1.0, {"x": rng4.standard_normal(4096)})
+    # ---- VectorProx::InitDiagonal (diagonal H, zeros included) and has_axis (own generator again) ----
+    rng5 = np.random.default_rng(1357)
+
+    def diag_arg(ptype, n, alpha=1.0, **kw):
+        w = rng5.standard_normal(n)
+        w[rng5.random(n) < 0.15] = 0.0
+        x = Variable("x", n)
+        return ProxFunction(ptype, args=[Affine(n, [Term(x, LinearMapSpec.Diagonal(w, name="w"))])], alpha=alpha, **kw)
+
+    n = 1201
+    out["norm_1_diag"] = (diag_arg("NORM_1", n, alpha=0.8), 1.4, {"x": rng5.standard_normal(n) * 2})
+    out["sum_hinge_diag"] = (diag_arg("SUM_HINGE", n), 0.9, {"x": rng5.standard_normal(n) * 2})
+    out["sum_deadzone_diag"] = (diag_arg("SUM_DEADZONE", n, alpha=1.2, zone_m=0.4), 0.7, {"x": rng5.standard_normal(n) * 2})
+    out["non_negative_diag"] = (diag_arg("NON_NEGATIVE", n), 1.0, {"x": rng5.standard_normal(n)})
+    out["sum_logistic_diag"] = (diag_arg("SUM_LOGISTIC", 400), 1.3, {"x": rng5.standard_normal(400) * 3})
+
+    def axis_norm2(m, k, axis, alpha):
+        x = Variable("x", m * k)
+        return ProxFunction("NORM_2", args=[Affine(m * k, [Term(x)])], alpha=alpha, axis=axis, axis_dims=(m, k))
+
+    out["norm_2_axis0"] = (axis_norm2(37, 11, 0, 2.5), 1.2, {"x": rng5.standard_normal(37 * 11)})
+    out["norm_2_axis1"] = (axis_norm2(37, 11, 1, 1.5), 0.9, {"x": rng5.standard_normal(37 * 11)})
+    out["norm_2_axis1_wide"] = (axis_norm2(5, 1500, 1, 20.0), 1.0, {"x": rng5.standard_normal(5 * 1500)})
     return out
 
 

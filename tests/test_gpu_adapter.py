@@ -39,7 +39,7 @@ def adapter():
 
 CASES = ["lasso_dense_100x500", "lasso_sparse_4000x400", "lasso_sparse_120000x4000", "logreg_l1_2000x200",
          "hinge_l2_sparse_5000x300", "group_lasso_400x10x12", "tv_1d_5000", "mv_lasso_40x100x3",
-         "l1_epigraph_denoise_300", "covsel_12"]
+         "l1_epigraph_denoise_300", "covsel_12", "weighted_lasso_200x300", "mv_row_group_lasso_60x80x4"]
 
 
 @pytest.mark.parametrize("name", CASES)
