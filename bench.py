@@ -390,16 +390,21 @@ def main_ours(args):
     achieved = spmv_bytes / (spmv_ms / 1e3) / 1e9 if spmv_ms > 0 else None
     total_prof_ms = sum(v["ms"] for v in prof.values())
     traffic = None  # dram__bytes_read.sum + dram__bytes_write.sum per launch, ncu --set full (1-GPU shape)
+    traffic_file = "profiles/r02_ncu_full_SellStreamKernel.csv"
     try:
         if world == 1 and args.m == 1_000_000 and args.n == 100_000:
             import csv
-            rd = wr = 0.0
-            for row in csv.reader(open(os.path.join(ROOT, "profiles", "r01_ncu_full_SellStreamKernel.csv"))):
-                if row and row[0] in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
-                    scale = {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0}[row[1]]
-                    v = 0.5 * (float(row[2]) + float(row[3])) * scale   # mean of the A' and A launches
-                    rd, wr = (v, wr) if "read" in row[0] else (rd, v)
-            traffic = rd + wr if rd else None
+            rows = list(csv.reader(open(os.path.join(ROOT, traffic_file))))
+            hdr, units = rows[0], rows[1]
+            scale = {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0}
+            per_launch = []
+            for r in rows[2:]:
+                tot = 0.0
+                for name in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+                    k = hdr.index(name)
+                    tot += float(r[k]) * scale[units[k]]
+                per_launch.append(tot)
+            traffic = float(np.mean(per_launch)) if per_launch else None   # mean of one A' and one A launch
     except Exception:
         traffic = None
     sell = os.environ.get("EPS_SPARSE_FORMAT", "sell") != "csr"
@@ -409,7 +414,7 @@ def main_ours(args):
         "achieved": achieved, "peak": peak,
         "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "6650 GB/s (of fallback)",
         "unit": "GB/s", "frac": achieved / peak if achieved else None, "traffic": traffic,
-        "traffic_source": "profiles/r01_ncu_full_SellStreamKernel.csv (ncu --set full, mean of one A and one A' launch)" if traffic else None,
+        "traffic_source": traffic_file + " (ncu --set full, mean of one A' and one A launch)" if traffic else None,
         "launches": spmv_launches, "ms_per_launch": spmv_ms / max(spmv_launches, 1),
         "algorithmic_bytes_per_launch": spmv_bytes / max(spmv_launches, 1),
         "share_of_step": spmv_ms / total_prof_ms if total_prof_ms else None,

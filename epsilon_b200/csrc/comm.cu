@@ -184,9 +184,23 @@ PeerBuf* PeerEnsure(Ctx* ctx, int64_t n) {
   if (ctx->peer && ctx->peer->ready && ctx->peer->x.n >= n) return ctx->peer;
   EPS_CHECK(!ctx->capturing, "peer buffer growth during graph capture");
   CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
-  if (ctx->peer) { PeerRelease(ctx->peer); delete ctx->peer; ctx->peer = nullptr; }
-  auto* pb = new PeerBuf();
-  ctx->peer = pb;
+  // Growth keeps the PeerBuf OBJECT: live solvers hold its address (KktSolver::peer) and read `x` afresh at every
+  // launch, so they simply see the larger buffers.  Order: every rank closes its mappings of the old blocks, all
+  // ranks meet (one tiny all-reduce), only then is the exported block freed.
+  PeerBuf* pb = ctx->peer;
+  if (pb) {
+    for (int r = 0; r < kMaxRanks; r++)
+      if (pb->mapped[r]) { cudaIpcCloseMemHandle(pb->mapped[r]); pb->mapped[r] = nullptr; }
+    DevBuf<double> meet(ctx, 1);
+    meet.zero();
+    NCCL_CHECK(Api().AllReduce(meet.p, meet.p, 1, ncclFloat64, ncclSum, ctx->comm->comm, ctx->stream));
+    CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+    PeerRelease(pb);
+    pb->x = PeerXchg();
+  } else {
+    pb = new PeerBuf();
+    ctx->peer = pb;
+  }
   PeerSetup(ctx, n, pb);
   return pb->ready ? pb : nullptr;
 }
