@@ -54,6 +54,7 @@ MODES = {
     "sentinel_two_shot": {"EPS_SPARSE_FORMAT": "sell"},                    # fused tail, 8-byte sentinel slots (default)
     "ll_two_shot": {"EPS_SPARSE_FORMAT": "sell", "EPS_PEER_SENTINEL": "0"},   # fused tail, 16-byte flag-in-data packets
     "ll_two_shot_v1": {"EPS_SPARSE_FORMAT": "sell", "EPS_TAIL_V1": "1"},   # first-generation tail (two grid syncs)
+    "sentinel_grown": {"EPS_SPARSE_FORMAT": "sell", "EPS_PEER_CAPACITY": "64"},   # peer buffers grow in place at solver set-up
     "one_shot_flags": {"EPS_SPARSE_FORMAT": "sell", "EPS_PEER_LL": "0"},   # P2P stores + fence + per-CTA flags
     "nccl_fallback": {"EPS_SPARSE_FORMAT": "sell", "EPS_NO_PEER": "1"},    # ncclAllReduce per product
     "csr_nccl": {"EPS_SPARSE_FORMAT": "csr"},                              # generic block path, CSR kernels
@@ -123,7 +124,7 @@ def test_row_sharded_solve_matches_reference_on_every_rank(case, mode, tmp_path)
     mp.spawn(_worker, args=(world, _free_port(), MODES[mode], case, str(tmp_path)), nprocs=world, join=True)
     r = [np.load(os.path.join(str(tmp_path), "rank%d.npz" % k)) for k in range(world)]
     desc = str(r[0]["desc"])
-    if mode in ("sentinel_two_shot", "ll_two_shot", "ll_two_shot_v1", "one_shot_flags"):
+    if mode in ("sentinel_two_shot", "sentinel_grown", "ll_two_shot", "ll_two_shot_v1", "one_shot_flags"):
         assert "peer-allreduce" in desc and "fused-tail" in desc, desc
     if mode == "nccl_fallback":
         assert "sharded" in desc and "peer-allreduce" not in desc, desc
