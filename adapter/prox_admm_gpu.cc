@@ -179,6 +179,10 @@ std::vector<ProxADMMGpuSolver::Affine> ProxADMMGpuSolver::Walk() {
 }
 
 void ProxADMMGpuSolver::Build(const std::vector<Affine>& exprs) {
+  BuildProblem(exprs);
+}
+
+void ProxADMMGpuSolver::BuildProblem(const std::vector<Affine>& exprs) {
   // a live solver whose matrices changed (SetParameterValue on a LinearMap constant): the reference keeps
   // x_, y_, u_ across the re-run of Init (prox_admm.cc:110-120); the old device solver hands its iterate on
   eps_solver* old_solver = solver_;
@@ -238,6 +242,11 @@ void ProxADMMGpuSolver::Build(const std::vector<Affine>& exprs) {
     }
   }
   for (const Affine& e : exprs) AddTerms(e);
+  if (exprs_only_) {   // EvalProx: the problem is all that is needed
+    if (old_solver) eps_solver_destroy(old_solver);
+    if (old_prob) eps_problem_destroy(old_prob);
+    return;
+  }
 
   eps_params p;
   eps_params_default(&p);                                            // SolverParams -> eps_params
@@ -304,6 +313,30 @@ int ProxADMMGpuSolver::OnEpoch(const eps_status* st, void* self_) {
                             st->r_norm, st->epsilon_primal, st->s_norm, st->epsilon_dual));
   }
   return self->HasExternalStop() ? 1 : 0;                             // stop_callback_, solver.h:60-63
+}
+
+BlockVector ProxADMMGpuSolver::EvalProx(double lambda, const BlockVector& v) {
+  CHECK_EQ(0, problem().constraint_size());
+  CHECK_EQ(1, problem().objective().arg_size());
+  exprs_only_ = true;
+  BuildProblem(Walk());
+  exprs_only_ = false;
+  // variables concatenated in the order they were registered (GetVariables: ordered by variable id)
+  std::vector<double> vin, xout;
+  for (const Expression* var : GetVariables(problem())) {
+    const BlockVector::DenseVector vv = v.Get(var->variable().variable_id(), GetDimension(*var));
+    vin.insert(vin.end(), vv.data(), vv.data() + vv.rows());
+  }
+  xout.resize(vin.size());
+  EPS_OK_OR_FATAL(eps_prox_eval(prob_, lambda, vin.data(), xout.data()));
+  BlockVector x;
+  size_t off = 0;
+  for (const Expression* var : GetVariables(problem())) {
+    const int n = GetDimension(*var);
+    x(var->variable().variable_id()) = Eigen::Map<const Eigen::VectorXd>(xout.data() + off, n);
+    off += n;
+  }
+  return x;
 }
 
 BlockVector ProxADMMGpuSolver::Solve() {

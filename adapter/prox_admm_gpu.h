@@ -33,6 +33,9 @@ class ProxADMMGpuSolver final : public Solver {
   ProxADMMGpuSolver(const Problem& problem, const DataMap& data_map, const SolverParams& params);
   ~ProxADMMGpuSolver() override;
   BlockVector Solve() override;
+  // EvalProx (python/epopt/solvemodule.cc:189-242): the problem holds exactly one prox function and no
+  // constraint; returns argmin lambda*f(x) + 1/2 ||x - v||^2 over its variables.
+  BlockVector EvalProx(double lambda, const BlockVector& v);
 
   // every ComputeResiduals result of the last Solve() (the reference keeps only the last one)
   const std::vector<SolverStatus>& epochs() const { return epochs_; }
@@ -50,6 +53,7 @@ class ProxADMMGpuSolver final : public Solver {
   };
   std::vector<Affine> Walk();
   void Build(const std::vector<Affine>& exprs);
+  void BuildProblem(const std::vector<Affine>& exprs);
   bool SameMaps(const std::vector<Affine>& exprs) const;
   void RefreshConstants(const std::vector<Affine>& exprs);
   eps_map* Upload(const linear_map::LinearMap& L);
@@ -63,6 +67,7 @@ class ProxADMMGpuSolver final : public Solver {
   eps_solver* solver_ = nullptr;
   std::map<std::string, int> var_index_;
   std::vector<Affine> built_;       // what the device solver was built from (for SetParameterValue)
+  bool exprs_only_ = false;
   std::vector<SolverStatus> epochs_;
   eps_status device_status_;
 };

@@ -4,7 +4,7 @@
 // uses seven glog macros (LOG, VLOG, CHECK, CHECK_EQ/NE/GE, InitGoogleLogging);
 // building the vendored glog needs cmake-generated headers, so the oracle recipe
 // (oracle/Makefile) puts this directory on the include path instead.  Semantics
-// kept: a failed CHECK / LOG(FATAL) prints the message and aborts (the reference
+// kept: a failed CHECK / LOG(FATAL) prints the message and calls the installed failure function, else aborts (the reference
 // longjmps out of glog's failure function, python/epopt/solvemodule.cc:245-263;
 // stand-alone C++ aborts, which is what the harness wants).
 #ifndef ORACLE_SHIM_GLOG_LOGGING_H
@@ -27,6 +27,13 @@ inline int& ShimVerbosity() {
   return v;
 }
 
+// InstallFailureFunction (glog): called instead of abort() when a CHECK / LOG(FATAL) fires.  The reference's
+// Python binding longjmps out of it (python/epopt/solvemodule.cc:245-248); so does adapter/solvemodule_py3.cc.
+inline void (*&ShimFailureFunction())() {
+  static void (*f)() = nullptr;
+  return f;
+}
+
 class ShimLogMessage {
  public:
   ShimLogMessage(const char* file, int line, int severity)
@@ -38,6 +45,7 @@ class ShimLogMessage {
     std::cerr << stream_.str();
     if (severity_ == FATAL) {
       std::cerr.flush();
+      if (ShimFailureFunction() != nullptr) ShimFailureFunction()();
       std::abort();
     }
   }
@@ -54,7 +62,7 @@ struct ShimVoidify {
 };
 
 inline void InitGoogleLogging(const char*) {}
-inline void InstallFailureFunction(void (*)()) {}
+inline void InstallFailureFunction(void (*f)()) { ShimFailureFunction() = f; }
 
 }  // namespace google
 
