@@ -97,6 +97,7 @@ SIGNATURES = {
     "eps_map_apply_dev": (C.c_int, [_P, _P, _P]),
     "eps_map_time": (C.c_int, [_P, C.c_int, C.POINTER(C.c_float), C.POINTER(C.c_double)]),
     "eps_map_destroy": (None, [_P]),
+    "eps_dense_apply_noalloc": (C.c_int, [_P, C.c_int, C.c_int, _P, _P, _P]),
     "eps_problem_create": (C.c_int, [_P, C.POINTER(_P)]),
     "eps_problem_destroy": (None, [_P]),
     "eps_problem_add_variable": (C.c_int, [_P, C.c_char_p, C.c_int, C.POINTER(C.c_int)]),

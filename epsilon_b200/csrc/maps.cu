@@ -5,6 +5,8 @@
 //   DiagonalMatrixImpl::Apply diagonal_matrix_impl.h:23, ScalarMatrixImpl::Apply scalar_matrix_impl.h:24
 // All arithmetic is fp64 (LinearMapImpl::Scalar = double, linear_map.h:35); indices int32.
 #include <chrono>
+#include <mutex>
+
 #include <cub/cub.cuh>
 
 #include "device.cuh"
@@ -794,3 +796,65 @@ int eps_map_time(eps_map* map, int reps, float* ms_per_apply, double* algorithmi
 void eps_map_destroy(eps_map* map) { delete map; }
 
 }  // extern "C"
+
+// =====================================================================================
+// eps_dense_apply_noalloc: y = A x for a dense column-major A with the split partials in a static
+// device array instead of the context's grown scratch.  No counterpart in the reference; added
+// for callers that cannot allocate (CUDA graph capture, serving loops).
+// Same two kernels, same split arithmetic and the same summation order as DenseGemv(trans = false),
+// so the result is bit-identical to eps_map_apply_dev on an eps_map_dense of the same matrix.
+// =====================================================================================
+namespace {
+
+// Lives in every GPU that loads the library until the process exits (8 MiB).  Shared by all calls:
+// GemvNKernel overwrites every entry SplitReduceKernel reads, so nothing has to start at zero, but two
+// calls that overlap on the GPU (different streams / contexts of one device) race on it.
+static __device__ __align__(256) double g_noalloc_partials[EPS_NOALLOC_SCRATCH_DOUBLES];
+
+constexpr int kNoAllocMaxDevices = 64;
+std::mutex g_noalloc_mu;
+double* g_noalloc_ptr[kNoAllocMaxDevices] = {};   // device address of the array, per device ordinal
+
+// In host code `g_noalloc_partials` is only a handle: the address a kernel can use comes from
+// cudaGetSymbolAddress, asked once per device with that device current.
+double* NoAllocScratch(int device) {
+  EPS_CHECK(device >= 0 && device < kNoAllocMaxDevices, "eps_dense_apply_noalloc: device ordinal %d out of range", device);
+  std::lock_guard<std::mutex> lock(g_noalloc_mu);
+  if (g_noalloc_ptr[device] == nullptr) {
+    void* p = nullptr;
+    CUDA_CHECK(cudaGetSymbolAddress(&p, g_noalloc_partials));
+    EPS_CHECK(p != nullptr, "eps_dense_apply_noalloc: no device address for the static scratch");
+    g_noalloc_ptr[device] = static_cast<double*>(p);
+  }
+  return g_noalloc_ptr[device];
+}
+
+}  // namespace
+
+extern "C" int eps_dense_apply_noalloc(eps_ctx* c, int m, int n, const double* a_colmajor_dev, const double* x_dev,
+                                       double* y_dev) {
+  EPS_API_BEGIN
+  EPS_CHECK(c && a_colmajor_dev && x_dev && y_dev, "eps_dense_apply_noalloc arguments");
+  EPS_CHECK(m > 0 && n > 0, "eps_dense_apply_noalloc: m = %d, n = %d must be positive", m, n);
+  Ctx* ctx = &c->c;
+  CUDA_CHECK(cudaSetDevice(ctx->device));
+  // the split of DenseGemv(trans = false), unchanged
+  const int target = ctx->sm_count * 24;
+  const int rb = (m + kGemvBlock * kGemvNRows - 1) / (kGemvBlock * kGemvNRows);
+  int splits = std::max(1, std::min((n + 63) / 64, target / rb));
+  int cps = (n + splits - 1) / splits;
+  cps = (cps + 7) / 8 * 8;
+  splits = (n + cps - 1) / cps;
+  const size_t need = (size_t)splits * (size_t)m;
+  if (need > (size_t)EPS_NOALLOC_SCRATCH_DOUBLES)
+    throw Error(EPS_ERR_INVALID,
+                Format("eps_dense_apply_noalloc: %d x %d needs %zu partial sums (%d column splits x %d rows), the static "
+                       "scratch holds EPS_NOALLOC_SCRATCH_DOUBLES = %d; use eps_map_dense + eps_map_apply_dev",
+                       m, n, need, splits, m, (int)EPS_NOALLOC_SCRATCH_DOUBLES));
+  double* part = NoAllocScratch(ctx->device);
+  GemvNKernel<<<dim3(rb, splits), kGemvBlock, 0, ctx->stream>>>(a_colmajor_dev, m, m, n, cps, x_dev, part, m, 0);
+  SplitReduceKernel<<<(m + 255) / 256, 256, 0, ctx->stream>>>(m, splits, part, m, 1.0, 0.0, y_dev);
+  ctx->count_launch(2);
+  CUDA_CHECK(cudaGetLastError());
+  EPS_API_END
+}

@@ -150,6 +150,20 @@ int eps_map_apply_dev(eps_map* map, const double* x_dev, double* y_dev);
  * returns the mean milliseconds per launch and the algorithmic bytes one launch moves. */
 int eps_map_time(eps_map* map, int reps, float* ms_per_apply, double* algorithmic_bytes);
 void eps_map_destroy(eps_map* map);
+/* y = A x for a dense column-major m x n matrix already on the device, WITHOUT any allocation: no
+ * cudaMalloc / cudaFree / pool call, so it can be issued under CUDA graph capture or from a loop that
+ * must not allocate.  No counterpart in the reference.
+ * The kernels and the summation order are those of eps_map_apply_dev on an eps_map_dense (bit-identical
+ * result); their column-split partial sums live in one static device array of
+ * EPS_NOALLOC_SCRATCH_DOUBLES doubles (8 MiB, held by every GPU that loads the library until exit)
+ * instead of the context's grown scratch.  EPS_ERR_INVALID when splits * m exceeds it, where
+ * splits <= min(ceil(n / 64), 24 * SMs / ceil(m / 512)); m * ceil(n / 64) <= EPS_NOALLOC_SCRATCH_DOUBLES
+ * always fits.  All calls share the array (it keeps the last call's partials; every entry read is
+ * written first, nothing needs clearing): calls that overlap on one GPU -- two streams, two contexts --
+ * race; calls on one stream are ordered.  Runs on the context's stream; a, x, y are device pointers. */
+#define EPS_NOALLOC_SCRATCH_DOUBLES (1 << 20)
+int eps_dense_apply_noalloc(eps_ctx* ctx, int m, int n, const double* a_colmajor_dev, const double* x_dev,
+                            double* y_dev);
 
 /* ---- prox-affine problem: what ProxADMMSolver::Init assembles ------------------
  *   minimize sum_i f_i(H_i x + g_i)   s.t.  sum_j A_j x_j + b = 0
