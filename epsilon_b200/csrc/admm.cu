@@ -34,7 +34,7 @@ void eps_solver::RunStages(const double* yo, double* yn) {
         Norm2ProxStep(ctx, st.segs.p, st.n_segs, st.max_len, consts.p, u.p, yo, yn, x.p);
         break;
       case ST_TV:
-        Tv1dProxStep(ctx, ops[st.members[0]].seg, consts.p, u.p, yo, yn, x.p, st.tv_work.p, &st.tv_tag);
+        Tv1dProxStep(ctx, ops[st.members[0]].seg, consts.p, u.p, yo, yn, x.p, st.tv_work.p, st.tv_tag);
         break;
       case ST_VEC: {
         // general VectorProx reduction around a multi-argument operator (vector_prox.cc:131-137)

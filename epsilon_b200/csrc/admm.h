@@ -58,7 +58,7 @@ struct Stage {
   int max_len = 0;
   int n_segs = 0;               // entries of `segs` (more than members when an operator acts axis-wise)
   DevBuf<double> tv_work;
-  unsigned tv_tag = 0;          // last round tag of the TV solver's slot maxima (tv1d_par.cu)
+  unsigned tv_tag[2] = {0, 0};  // TV solver (tv1d_par.cu): last round tag of its slot maxima, rounds of the last call
 };
 
 }  // namespace eps

@@ -774,7 +774,7 @@ void eps_solver::ResetVariables() {
   x.zero();
   ybuf[0].zero();
   ybuf[1].zero();
-  for (auto& stp : stages) { stp->tv_work.zero(); stp->tv_tag = 0; }  // cold active set for the TV solver
+  for (auto& stp : stages) { stp->tv_work.zero(); stp->tv_tag[0] = stp->tv_tag[1] = 0; }  // cold active set for the TV solver
   parity = 0;
   iter = 0;
   started = false;

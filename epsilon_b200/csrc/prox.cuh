@@ -30,6 +30,17 @@ struct ElemSeg {
   double zone_m, zone_alpha, zone_beta;  // scaled_zone.cc:34-76
 };
 
+// TOTAL_VARIATION_1D: the pre / post maps of VectorProx handed to the solver so that it fuses them into its own
+// first and last pass (tv1d_par.cu)
+struct TvFuse {
+  ElemSeg seg;
+  const double* consts;
+  double* u;
+  const double* y_old;
+  double* y_new;
+  double* x;
+};
+
 struct SegPair {
   int64_t a_off, b_off;
   int32_t len;
@@ -50,7 +61,7 @@ void Norm2ProxStep(Ctx* ctx, const ElemSeg* segs_dev, int nseg, int max_len, con
 // TOTAL_VARIATION_1D for one segment (host copy of the segment passed by value).
 void Tv1dProxStep(Ctx* ctx, const ElemSeg& seg, const double* consts, double* u, const double* y_old,
                   double* y_new, double* x, double* work /* Tv1dWorkDoubles(len) */,
-                  unsigned* tag_state /* host word kept with `work`: round tags of the slot maxima */);
+                  unsigned* tag_state /* two host words kept with `work`: round tag of the slot maxima, rounds of the last call */);
 size_t Tv1dWorkDoubles(int64_t len);
 
 // dst[a_off + j] += c1*src1[b_off + j] + c2*src2[b_off + j]   (src2 may be null)

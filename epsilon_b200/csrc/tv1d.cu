@@ -42,8 +42,8 @@ TvPostKernel(ElemSeg sg, const double* __restrict__ consts, const double* __rest
 
 // tv1d_par.cu
 size_t Tv1dParallelBytes(int64_t n);
-int Tv1dParallelSolve(Ctx* ctx, int n, const double* v, double lam, double* beta, char* scratch,
-                      int* h_changed, unsigned* tag_state);
+int Tv1dParallelSolve(Ctx* ctx, int n, double* v, double lam, double* beta, char* scratch,
+                      int* h_flag, unsigned* host_state, const TvFuse* fuse);
 
 // work layout (doubles): v[n] | beta[n] | scratch of the parallel solver (whose first part, the active set,
 // persists between calls: warm start)
@@ -59,25 +59,23 @@ void Tv1dProxStep(Ctx* ctx, const ElemSeg& seg, const double* consts, double* u,
   double* beta = v + n;
   char* par = reinterpret_cast<char*>(work + 2 * (size_t)n);
   par += (256 - (reinterpret_cast<uintptr_t>(par) & 255)) & 255;
-  const int grid = GridFor(n, 256, 2, ctx->sm_count);
-  {
-    ProfScope ps(ctx, KC_VEC, 32.0 * n);
-    TvPreKernel<<<grid, 256, 0, ctx->stream>>>(seg, consts, u, y_old, v);
-    ctx->count_launch();
-  }
   if (n == 1 || seg.lam == 0.0) {
     // no boundary / no penalty: the prox is the identity (tf_dp returns its input for lam = 0 as well)
-    VecCopy(ctx, n, v, beta);
-  } else {
-    EPS_CHECK(!ctx->capturing, "the TV solver cannot be captured in a CUDA graph");
-    const int rounds = Tv1dParallelSolve(ctx, n, v, seg.lam, beta, par, PinnedFlag(ctx), tag_state);
-    if (rounds < 0)
-      throw Error(EPS_ERR_NUMERIC, Format("TOTAL_VARIATION_1D: the active-set rounds did not settle (n = %d, lambda = %g)",
-                                          n, seg.lam));
+    const int grid = GridFor(n, 256, 2, ctx->sm_count);
+    ProfScope ps(ctx, KC_VEC, 72.0 * n);
+    TvPreKernel<<<grid, 256, 0, ctx->stream>>>(seg, consts, u, y_old, v);
+    TvPostKernel<<<grid, 256, 0, ctx->stream>>>(seg, consts, v, u, y_new, x);
+    ctx->count_launch(2);
+    return;
   }
-  ProfScope ps(ctx, KC_VEC, 40.0 * n);
-  TvPostKernel<<<grid, 256, 0, ctx->stream>>>(seg, consts, beta, u, y_new, x);
-  ctx->count_launch();
+  // the pre-map (w = u + y_old, v = B w + g) and the post-map (x = C (beta - g), y = A x, u -= y) run inside the
+  // solver's first and last pass
+  EPS_CHECK(!ctx->capturing, "the TV solver cannot be captured in a CUDA graph");
+  const TvFuse fuse{seg, consts, u, y_old, y_new, x};
+  const int rounds = Tv1dParallelSolve(ctx, n, v, seg.lam, beta, par, PinnedFlag(ctx), tag_state, &fuse);
+  if (rounds < 0)
+    throw Error(EPS_ERR_NUMERIC, Format("TOTAL_VARIATION_1D: the active-set rounds did not settle (n = %d, lambda = %g)",
+                                        n, seg.lam));
 }
 
 }  // namespace eps
