@@ -59,7 +59,9 @@ void eps_solver::RunStages(const double* yo, double* yn) {
         ProxOp& op = ops[st.members[0]];
         double* us = u.p + op.span_lo;
         double* xi = x.p + op.x_off;
-        if (op.simple_scalar) {
+        if (op.simple_scalar && op.kkt->mode == EPS_KKT_DIAGONAL && !op.kkt->inner) {
+          KktScalarDiagStep(ctx, op.n, op.a, op.kkt->c0.p, op.kkt->dinv.p, us, yo + op.y_off, yn + op.y_off, xi);
+        } else if (op.simple_scalar) {
           KktScalarPre(ctx, op.n, op.a, op.kkt->c0.p, us, yo + op.y_off, rhs_n.p);
           op.kkt->Solve(rhs_n.p, xi);
           KktScalarPost(ctx, op.n, op.a, xi, us, yn + op.y_off);

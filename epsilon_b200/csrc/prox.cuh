@@ -78,6 +78,9 @@ void SegSumSq(Ctx* ctx, const SegPair* pairs_dev, const SegPair* pairs_host, int
 void KktScalarPre(Ctx* ctx, int64_t n, double a, const double* c0, double* u, const double* y_old,
                   double* rhs);
 void KktScalarPost(Ctx* ctx, int64_t n, double a, const double* x, double* u, double* y_new);
+// the three steps above with a DIAGONAL solve (x = dinv .* rhs) between them, fused
+void KktScalarDiagStep(Ctx* ctx, int64_t n, double a, const double* c0, const double* dinv, double* u,
+                       const double* y_old, double* y_new, double* x);
 // Two-block consensus ADMM (prox_admm_two_block.cc:111-113,135-146), one pass:
 //   z = mask .* (v - t)   (t = H'y of the projection; mask may be null)
 //   u += x - z

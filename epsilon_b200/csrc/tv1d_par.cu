@@ -117,12 +117,17 @@ struct TileShared {
 };
 
 // lb / rb / a of the tile that starts at boundary t0, given the carries of the tile.  All kTvpBlock threads.
-__device__ __forceinline__ void TileScans(TileShared& sh, int t0, int m, const int8_t* __restrict__ act, int cl, int cr) {
+// The 8 flags this thread owns in tile T (blocked order)
+__device__ __forceinline__ unsigned long long TileFlags(const int8_t* __restrict__ act, int T) {
+  static_assert(kItems == 8, "one 8-byte load per thread");
+  return *reinterpret_cast<const unsigned long long*>(act + (size_t)T * kTile + threadIdx.x * kItems);
+}
+
+__device__ __forceinline__ void TileScans(TileShared& sh, int t0, int m, unsigned long long flags, int cl, int cr) {
   const int t = threadIdx.x, lane = t & 31, w = t >> 5;
   const int base = t * kItems;
   union { unsigned long long q; int8_t b[kItems]; } ld;
-  static_assert(kItems == 8, "one 8-byte load per thread");
-  ld.q = *reinterpret_cast<const unsigned long long*>(act + t0 + base);
+  ld.q = flags;
   int f[kItems], r[kItems];
   int run = -1;
 #pragma unroll
@@ -257,7 +262,8 @@ __device__ __forceinline__ int HeadSlot(int lb, int t0) { return max(lb + 1 - t0
 
 template <typename SignFn>
 __device__ __forceinline__ void TileGroupValues(const TileShared& sh, double* __restrict__ bval, int t0, int n, int m,
-                                                int cl, double lam, const DD* __restrict__ R, SignFn sign) {
+                                                int cl, double lam, const DD* __restrict__ R, SignFn sign,
+                                                int8_t* __restrict__ zlsign = nullptr /* sign of the dual left of the group */) {
 #pragma unroll 2
   for (int jj = 0; jj < kItems; jj++) {
     const int i = jj * kTvpBlock + threadIdx.x;
@@ -272,6 +278,7 @@ __device__ __forceinline__ void TileGroupValues(const TileShared& sh, double* __
     g.zl = lb >= 0 ? lam * sign(lb) : 0.0;
     g.zr = rb < m ? lam * sign(rb) : 0.0;
     bval[i] = GroupValue(g, R);
+    if (zlsign != nullptr) zlsign[i] = lb >= 0 ? (int8_t)sign(lb) : (int8_t)0;
   }
   __syncthreads();
 }
@@ -279,23 +286,47 @@ __device__ __forceinline__ void TileGroupValues(const TileShared& sh, double* __
 // Round, part 1 (dirty tiles): z on every free boundary and per group the largest violation of each sign
 // (warp-aggregated atomicMax on the slot of the group's first element; the bit pattern of a positive double
 // orders like the value); on every active boundary the jump across it times its sign.
-__global__ void __launch_bounds__(kTvpBlock, 4)
+__global__ void __launch_bounds__(kTvpBlock, 3)
 TvpViolationKernel(TvState S, int n, double lam, unsigned tag) {
   __shared__ TileShared sh;
   __shared__ double bval[kTile];
+  __shared__ int8_t zlsign[kTile];
   if (S.ctl[1] != 0) return;
   const int cnt = S.ctl[2];
   const int m = n - 1;
   const int lane = threadIdx.x & 31;
   const DD* __restrict__ R = S.R;
-  for (int idx = blockIdx.x; idx < cnt; idx += gridDim.x) {
-    const int T = S.list[idx];
+  // software pipeline over the tiles of this CTA: the flags and carries of the NEXT tile are requested while the
+  // current one is processed, and the coalesced R[k + 1] stream of a tile is requested before its scans
+  int idx = blockIdx.x;
+  int T = 0, cl = 0, cr = 0;
+  unsigned long long flags = 0;
+  if (idx < cnt) {
+    T = S.list[idx];
+    flags = TileFlags(S.act, T);
+    cl = S.carry_l[T];
+    cr = S.carry_r[T];
+  }
+  for (; idx < cnt; idx += gridDim.x) {
     const int t0 = T * kTile;
-    const int cl = S.carry_l[T], cr = S.carry_r[T];
-    TileScans(sh, t0, m, S.act, cl, cr);
+    DD rk[kItems];
+#pragma unroll
+    for (int jj = 0; jj < kItems; jj++) {
+      const int k = t0 + jj * kTvpBlock + threadIdx.x;
+      rk[jj] = k < m ? R[k + 1] : DD{0.0, 0.0};
+    }
+    int Tn = 0, cln = 0, crn = 0;
+    unsigned long long flagsn = 0;
+    if (idx + gridDim.x < cnt) {
+      Tn = S.list[idx + gridDim.x];
+      flagsn = TileFlags(S.act, Tn);
+      cln = S.carry_l[Tn];
+      crn = S.carry_r[Tn];
+    }
+    TileScans(sh, t0, m, flags, cl, cr);
     // sign of an active boundary: from the tile when it lies inside
     auto sign = [&](int b) -> double { return (double)((unsigned)(b - t0) < (unsigned)kTile ? sh.a[b - t0] : S.act[b]); };
-    TileGroupValues(sh, bval, t0, n, m, cl, lam, R, sign);
+    TileGroupValues(sh, bval, t0, n, m, cl, lam, R, sign, zlsign);
     double zz[kItems];
     bool cand = false;
 #pragma unroll
@@ -305,13 +336,25 @@ TvpViolationKernel(TvState S, int n, double lam, unsigned tag) {
       int gid = -1 - k;  // unique when not a candidate
       double vp = 0.0, vn = 0.0;
       zz[jj] = 0.0;
-      if (k < m) {
-        const int a = sh.a[i];
+      const int a = k < m ? (int)sh.a[i] : 1;
+      if (__all_sync(kFull, a == 0)) {
+        // the common case, kept free of divergence: the whole warp sits on free boundaries
+        const int lb = sh.lb[Pad(i)];
+        const int s0 = lb + 1;
+        const int slot = HeadSlot(lb, t0);
+        const DD rs = R[s0];
+        const double zk = lam * (double)zlsign[slot] + (double)(k - s0 + 1) * bval[slot] - ((rk[jj].hi - rs.hi) + (rk[jj].lo - rs.lo));
+        zz[jj] = zk;
+        vp = zk - lam;
+        vn = -lam - zk;
+        gid = s0;
+      } else if (k < m) {
         if (a == 0) {
           const int lb = sh.lb[Pad(i)];
           const int s0 = lb + 1;
-          const double zl = lb >= 0 ? lam * sign(lb) : 0.0;
-          const double zk = zl + (double)(k - s0 + 1) * bval[HeadSlot(lb, t0)] - DDDiff(R, k + 1, s0);
+          const int slot = HeadSlot(lb, t0);
+          const DD rs = R[s0];
+          const double zk = lam * (double)zlsign[slot] + (double)(k - s0 + 1) * bval[slot] - ((rk[jj].hi - rs.hi) + (rk[jj].lo - rs.lo));
           zz[jj] = zk;
           vp = zk - lam;
           vn = -lam - zk;
@@ -366,6 +409,7 @@ TvpViolationKernel(TvState S, int n, double lam, unsigned tag) {
         if (k < m) S.z[k] = zz[jj];
       }
     }
+    T = Tn; flags = flagsn; cl = cln; cr = crn;
   }
 }
 
@@ -401,7 +445,7 @@ TvpUpdateKernel(TvState S, int n, double lam, int round, unsigned tag) {
       for (int j = 0; j < kItems; j++) zk[j] = t0 + base + j < m ? S.z[t0 + base + j] : 0.0;
     }
     const int cl = S.carry_l[T], cr = S.carry_r[T];
-    TileScans(sh, t0, m, S.act, cl, cr);
+    TileScans(sh, t0, m, a.q, cl, cr);
     int last = -1, first = m;
     bool wrote = false;
 #pragma unroll
@@ -469,20 +513,45 @@ TvpUpdateKernel(TvState S, int n, double lam, int round, unsigned tag) {
 // beta of every sample, from the settled active set.  POST: the VectorProx post-map and the dual update are
 // applied here (x = C (beta - g), y = A x, u -= y; tv1d.cu TvPostKernel) and beta itself is never stored.
 template <bool POST>
-__global__ void __launch_bounds__(kTvpBlock, 5)
+__global__ void __launch_bounds__(kTvpBlock, 4)
 TvpValuesKernel(TvState S, int n, int ntiles, double lam, double* __restrict__ beta, ElemSeg sg,
                 const double* __restrict__ consts, double* __restrict__ u, double* __restrict__ y_new,
                 double* __restrict__ x) {
   __shared__ TileShared sh;
   __shared__ double bval[kTile];
   const int m = n - 1;
-  for (int T = blockIdx.x; T < ntiles; T += gridDim.x) {
+  // software pipeline as in TvpViolationKernel: next tile's flags / carries, and this tile's u (and g) stream,
+  // are in flight while the scans run
+  int T = blockIdx.x, cl = 0, cr = 0;
+  unsigned long long flags = 0;
+  if (T < ntiles) {
+    flags = TileFlags(S.act, T);
+    cl = S.carry_l[T];
+    cr = S.carry_r[T];
+  }
+  for (; T < ntiles; T += gridDim.x) {
     const int t0 = T * kTile;
-    const int cl = S.carry_l[T], cr = S.carry_r[T];
-    TileScans(sh, t0, m, S.act, cl, cr);
+    double uu[kItems], gg[kItems];
+    if (POST) {
+#pragma unroll
+      for (int jj = 0; jj < kItems; jj++) {
+        const int i = t0 + jj * kTvpBlock + threadIdx.x;
+        uu[jj] = i < n ? u[sg.u_off + i] : 0.0;
+        gg[jj] = (i < n && sg.g_off >= 0) ? consts[sg.g_off + i] : 0.0;
+      }
+    }
+    const int Tn = T + gridDim.x;
+    int cln = 0, crn = 0;
+    unsigned long long flagsn = 0;
+    if (Tn < ntiles) {
+      flagsn = TileFlags(S.act, Tn);
+      cln = S.carry_l[Tn];
+      crn = S.carry_r[Tn];
+    }
+    TileScans(sh, t0, m, flags, cl, cr);
     auto sign = [&](int b) -> double { return (double)((unsigned)(b - t0) < (unsigned)kTile ? sh.a[b - t0] : S.act[b]); };
     TileGroupValues(sh, bval, t0, n, m, cl, lam, S.R, sign);
-#pragma unroll 4
+#pragma unroll
     for (int jj = 0; jj < kItems; jj++) {
       const int ii = jj * kTvpBlock + threadIdx.x;
       const int i = t0 + ii;
@@ -490,17 +559,17 @@ TvpValuesKernel(TvState S, int n, int ntiles, double lam, double* __restrict__ b
       const int lb = ii > 0 ? sh.lb[Pad(ii - 1)] : cl;   // last active boundary < i
       const double bv = bval[HeadSlot(lb, t0)];
       if (POST) {
-        const double gc = sg.g_off >= 0 ? consts[sg.g_off + i] : 0.0;
-        const double xv = sg.Cs * (bv - gc);
+        const double xv = sg.Cs * (bv - gg[jj]);
         const double yn = sg.As * xv;
         x[sg.x_off + i] = xv;
         y_new[sg.y_off + i] = yn;
-        u[sg.u_off + i] = u[sg.u_off + i] - yn;
+        u[sg.u_off + i] = uu[jj] - yn;
       } else {
         beta[i] = bv;
       }
     }
     __syncthreads();
+    flags = flagsn; cl = cln; cr = crn;
   }
 }
 
