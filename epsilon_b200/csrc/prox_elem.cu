@@ -36,19 +36,92 @@ __device__ __forceinline__ double ScaledZone(double x, double lam, double M, dou
   return x > 0 ? M : -M;
 }
 
-// Solve x - v + lam*sigma(x) = 0 (newton.cc:10-16 ProxResidual with Logistic::gradf),
-// damped Newton from x = v with the reference's backtracking constants (newton.cc:63-77).
+// Solve f(x) = x - v + lam*sigma(x) = 0 (newton.cc:10-16 ProxResidual with Logistic::gradf) to working precision.
+//
+// The reference runs a damped Newton from x = v (newton.cc:47-91); in fp64 on the device that is ~7 evaluations of
+// exp and ~14 divisions per element, and the kernel sat at 17 % of the HBM roofline on the fp64 pipe.  Three stages:
+//   1. fp32, cheap (MUFU ex2 / rcp): an UNDAMPED Newton that cannot overshoot.  f is increasing, convex on x <= 0
+//      and concave on x >= 0, and the root has the sign of v - lam/2; started on the side where the tangent
+//      under-shoots (f >= 0 in the convex half, f <= 0 in the concave half) Newton converges monotonically.
+//      Leaves x0 with |x0 - x*| ~ 1e-7 (1 + |x*|).
+//   2. fp64: ONE exp and two divisions at x0, then a Newton step and a chord step in which sigma at the stepped
+//      point comes from its Taylor expansion around x0 (the step d is ~1e-6, so the d^3 remainder is below 1e-17).
+//   3. accepted when both steps are as small as quadratic convergence predicts; otherwise -- a stage-1 start that
+//      did not converge in its 12 steps (huge lam: Newton walks an exp tail one unit per step) -- the lanes fall
+//      into the damped Newton of the reference (backtracking constants of newton.cc:63-77) from where they stand.
 // All lanes of the warp iterate together and leave when every lane has converged.
+// single MUFU instructions (the __frcp_rn / __fdividef / __expf intrinsics carry range and rounding fix-ups that
+// tripled the instruction count of the fp32 stage; none of it matters for a starting point)
+__device__ __forceinline__ float RcpApprox(float y) {
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(y));
+  return r;
+}
+__device__ __forceinline__ float Ex2Approx(float y) {
+  float r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(y));
+  return r;
+}
+
+// 1 / y for 1 <= y < 1e38 from the fp32 reciprocal and STEPS Newton refinements (relative error 1e-7 -> 1e-14 ->
+// below 1 ulp): 2 conversions + 2 fused multiply-adds per step instead of the ~30 instructions of an IEEE division.
+template <int STEPS>
+__device__ __forceinline__ double RcpSeeded(double y) {
+  double r = (double)RcpApprox((float)y);
+#pragma unroll
+  for (int i = 0; i < STEPS; i++) r = fma(r, fma(-y, r, 1.0), r);
+  return r;
+}
+
 __device__ __forceinline__ double LogisticProx(double v, double lam, bool active) {
-  double x = v;
   auto sigma = [](double t) {
     if (t >= 0) { double e = exp(-t); return 1.0 / (1.0 + e); }
     double e = exp(t);
     return e / (1.0 + e);
   };
+  double x = v;
+  bool done = !active;
+  if (active && lam > 0.0 && fabs(v) < 1e30 && lam < 1e30) {
+    // ---- stage 1
+    const float vf = (float)v, lf = (float)lam;
+    // valid starts: x = v (root < 0) / x = v - lam (root > 0), and the root of the tangent model at 0,
+    // sigma ~ 1/2 + x/4, which lies on the right side by convexity; the closer of the two
+    const float xlin = (vf - 0.5f * lf) * RcpApprox(1.0f + 0.25f * lf);
+    float xf = v < 0.5 * lam ? fminf(vf, xlin) : fmaxf(vf - lf, xlin);
+#pragma unroll 1
+    for (int it = 0; it < 12; it++) {
+      const float e = Ex2Approx(-1.4426950408889634f * fabsf(xf));
+      const float r = RcpApprox(1.0f + e);
+      const float sg = xf >= 0.0f ? r : e * r;
+      const float dx = (xf - vf + lf * sg) * RcpApprox(1.0f + lf * (e * r * r));
+      xf -= dx;
+      // warp-uniform exit: a converged lane sits on its fixed point while the others finish
+      if (__all_sync(kFull, fabsf(dx) <= 2e-7f * (1.0f + fabsf(xf)))) break;
+    }
+    // ---- stage 2
+    const double x0 = (double)xf;
+    const double e = exp(-fabs(x0));
+    const double r = RcpSeeded<2>(1.0 + e);
+    const double s0 = x0 >= 0.0 ? r : e * r;
+    const double h0 = e * r * r;                               // sigma' = sigma (1 - sigma), without the cancellation
+    const double inv = RcpSeeded<1>(fma(lam, h0, 1.0));        // 1 / f'(x0) to 1e-14, kept for the second (chord)
+    const double d0 = -(fma(lam, s0, x0 - v)) * inv;           // step: f' moves by ~lam sigma'' d0 / f' ~ 1e-6 relative
+    const double x1 = x0 + d0;
+    const double s1 = fma(h0 * d0, fma(0.5 * d0, fma(-2.0, s0, 1.0), 1.0), s0);
+    const double d1 = -(fma(lam, s1, x1 - v)) * inv;
+    // ---- stage 3: the third derivative of sigma is below 4e-18 beyond |x| = 40, there the expansion is exact
+    // for any step
+    const bool small0 = fabs(d0) <= 7.6e-6 || (fabs(x0) > 40.0 && fabs(d0) <= 1.0);
+    if (small0 && fabs(d1) <= 1e-3 * fabs(d0) + 1e-300) {
+      x = x1 + d1;
+      done = true;
+    } else if (small0 || fabs(x1 - v) <= lam) {
+      x = x1;                                                  // still a better start than v
+    }
+  }
+  if (__all_sync(kFull, done)) return x;
   double s = sigma(x);
   double g = x - v + lam * s;
-  bool done = !active;
   for (int it = 0; it < 100; it++) {
     if (__all_sync(kFull, done)) break;
     if (!done) {
