@@ -190,6 +190,34 @@ def test_logistic_extreme_inputs_are_finite(ctx):
     assert x[-1] == pytest.approx(1e4 - 2.0, abs=1e-9) and x[-2] == pytest.approx(798.0, abs=1e-9)
 
 
+@pytest.mark.parametrize("lam", [1e-3, 0.5, 7.0, 300.0, 1e5, 3e8])
+def test_logistic_prox_wide_range_vs_high_precision_root(ctx, lam):
+    """The three-stage SUM_LOGISTIC kernel (fp32 monotone Newton, one fp64 exp + Taylor-carried steps, damped
+    Newton of newton.cc:47-91 as the fallback) against the root of x - v + lam*sigma(x) found independently by
+    bisection in extended precision.  Large lam makes part of every warp take the fallback."""
+    rng = np.random.default_rng(int(lam * 1000) % 9973)
+    v = np.concatenate([rng.standard_normal(6000) * 3, rng.uniform(-80, 80, 3000), rng.standard_normal(1000) * 1e3,
+                        np.array([0.0, 0.5 * lam, -0.5 * lam, lam, 1e-300, -1e-300])])
+    x = eval_prox(_simple("SUM_LOGISTIC", v.size), lam, {"x": v}, ctx=ctx)["x"]
+    vl, ll = v.astype(np.longdouble), np.longdouble(lam)
+    lo, hi = vl - ll, vl.copy()
+    for _ in range(160):
+        mid = (lo + hi) / 2
+        e = np.exp(-np.abs(mid))
+        s = np.where(mid >= 0, 1 / (1 + e), e / (1 + e))
+        pos = mid - vl + ll * s > 0
+        hi = np.where(pos, mid, hi)
+        lo = np.where(pos, lo, mid)
+    root = ((lo + hi) / 2).astype(np.float64)
+    assert np.all(np.isfinite(x))
+    # conditioning: the residual x - v + lam*sigma(x) cancels terms of size |v| + lam*sigma in fp64 (for the
+    # reference as well), which moves the computed root by that rounding over f' = 1 + lam*sigma'
+    e = np.exp(-np.abs(root))
+    sg = np.where(root >= 0, 1 / (1 + e), e / (1 + e))
+    cond = 8 * np.finfo(np.float64).eps * (np.abs(v) + lam * sg) / (1 + lam * sg * (1 - sg))
+    assert np.all(np.abs(x - root) <= 5e-14 * np.maximum(1.0, np.abs(root)) + cond)
+
+
 @pytest.mark.parametrize("n", [1, 2, 3, 1000, 65537, 1 << 20])
 def test_tv1d_vs_oracle(ctx, n):
     rng = np.random.default_rng(n)
