@@ -307,15 +307,21 @@ def main_ours(args):
             with ProxADMMSolver(prob, params, ctx=ctx, sharded_args=sharded) as s0:
                 s0.solve()
             ctx.synchronize()
-        barrier()
-        t0 = time.time()
-        s = ProxADMMSolver(prob, params, ctx=ctx, sharded_args=sharded)
-        t_built = time.time()
-        x = s.solve()
-        ctx.synchronize()
-        t_done = time.time()
-        t_e2e = max_over_ranks(t_done - t0)
-        t_construct, t_solve = max_over_ranks(t_built - t0), max_over_ranks(t_done - t_built)
+        # three timed whole solves (each one uploads the host matrix again); the MEDIAN one is reported, all three
+        # are listed: a single sample moved by +-10 % between boxes with the host's page-locked copy rate
+        runs = []
+        for rep in range(3):
+            if rep:
+                s.close()
+            barrier()
+            t0 = time.time()
+            s = ProxADMMSolver(prob, params, ctx=ctx, sharded_args=sharded)
+            t_built = time.time()
+            x = s.solve()
+            ctx.synchronize()
+            t_done = time.time()
+            runs.append((max_over_ranks(t_done - t0), max_over_ranks(t_built - t0), max_over_ranks(t_done - t_built)))
+        t_e2e, t_construct, t_solve = sorted(runs)[1]
         st = s.status.as_dict()
         iters = st["iterations_run"]
         obj = info["objective"](x)
@@ -330,6 +336,7 @@ def main_ours(args):
         e2e = {"value": iters / t_e2e, "unit": "iterations/s",
                "h2d_bytes_per_step": h2d_bytes / iters, "d2h_bytes_per_step": 8 * 2 * args.n / iters,
                "warmup_solves": 2, "host_buffers": "pinned (cudaHostAlloc)",
+               "timed_solves_s": [round(r[0], 6) for r in runs], "reported": "median of 3 timed solves",
                "time_to_tol_s": t_e2e, "init_s": st["init_ms"] / 1e3, "loop_s": st["loop_ms"] / 1e3,
                # max over ranks: upload + on-device transposition + SELL build + Init | iterations + download of x
                "construct_s": t_construct, "solve_s": t_solve,
