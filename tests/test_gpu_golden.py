@@ -218,6 +218,20 @@ def test_logistic_prox_wide_range_vs_high_precision_root(ctx, lam):
     assert np.all(np.abs(x - root) <= 5e-14 * np.maximum(1.0, np.abs(root)) + cond)
 
 
+@pytest.mark.parametrize("lam", [1e-3, 0.4, 40.0, 1e4])
+@pytest.mark.parametrize("n", [2047, 2048, 2049, 4096, 4097, 6145, 100003])
+def test_tv1d_tile_edges_and_group_regimes_vs_oracle(ctx, n, lam):
+    """The tiled active-set solver (tv1d_par.cu: tiles of 2048 boundaries, carries between tiles, dirty-tile lists)
+    at lengths around the tile size, from 'every boundary active' (tiny lambda) to 'one group across all tiles'
+    (huge lambda), against the dynamic program (oracle/tv1d_dp.c = glmgen tf_dp)."""
+    rng = np.random.default_rng(n + int(lam * 1000))
+    v = np.repeat(rng.standard_normal(n // 300 + 1) * 2, 300)[:n] + 0.5 * rng.standard_normal(n)
+    f = _simple("TOTAL_VARIATION_1D", n, alpha=1.0)
+    x = eval_prox(f, lam, {"x": v}, ctx=ctx)["x"]
+    ref = onp.eval_prox(f, lam, {"x": v})["x"]
+    assert np.abs(x - ref).max() <= 1e-11 * max(1.0, np.abs(ref).max())
+
+
 @pytest.mark.parametrize("n", [1, 2, 3, 1000, 65537, 1 << 20])
 def test_tv1d_vs_oracle(ctx, n):
     rng = np.random.default_rng(n)
