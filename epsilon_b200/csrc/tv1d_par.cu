@@ -522,9 +522,11 @@ template <bool POST>
 __global__ void __launch_bounds__(kTvpBlock, 4)
 TvpValuesKernel(TvState S, int n, int ntiles, double lam, double* __restrict__ beta, ElemSeg sg,
                 const double* __restrict__ consts, double* __restrict__ u, double* __restrict__ y_new,
-                double* __restrict__ x) {
+                double* __restrict__ x, int speculative) {
   __shared__ TileShared sh;
   __shared__ double bval[kTile];
+  // queued behind a batch of rounds before the host knows whether they settled: a no-op if they did not
+  if (speculative && S.ctl[1] == 0) return;
   const int m = n - 1;
   // software pipeline as in TvpViolationKernel: next tile's flags / carries, and this tile's u (and g) stream,
   // are in flight while the scans run
@@ -836,6 +838,15 @@ int Tv1dParallelSolve(Ctx* ctx, int n, double* v, double lam, double* beta, char
       *tag_state = 0;
     }
   }
+  auto launch_values = [&](int speculative) {
+    if (fuse)
+      TvpValuesKernel<true><<<grid_for(3), kTvpBlock, 0, st>>>(S, n, nt, lam, nullptr, fuse->seg, fuse->consts, fuse->u,
+                                                                fuse->y_new, fuse->x, speculative);
+    else
+      TvpValuesKernel<false><<<grid_for(3), kTvpBlock, 0, st>>>(S, n, nt, lam, beta, ElemSeg{}, nullptr, nullptr, nullptr,
+                                                                 nullptr, speculative);
+    ctx->count_launch();
+  };
   int rounds = -1;
   if (m > 0) {
     // Rounds are queued in batches and judged on the device; a settled solve turns the rest of its batch into
@@ -845,18 +856,32 @@ int Tv1dParallelSolve(Ctx* ctx, int n, double* v, double lam, double* beta, char
     int r = 0;
     int batch = host_state[1] == 0 ? 4 : std::min<int>(24, std::max<int>(2, (int)host_state[1] + 1));
     static const bool trace = getenv("EPS_TV_TRACE") != nullptr;
+    // The values pass is queued right behind each batch, before the host has read the verdict (it returns at once
+    // when the rounds did not settle): the host's round trip for the flag overlaps with it instead of idling the GPU.
+    static cudaEvent_t evs[64] = {};
+    cudaEvent_t& ev = evs[ctx->device & 63];
+    if (ev == nullptr) CUDA_CHECK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    bool first_batch = true;
     while (r < kMaxRounds && rounds < 0) {
-      ProfScope ps(ctx, KC_TV, r == 0 ? 34.0 * n : 0.0);
-      for (int b = 0; b < batch; b++, r++) {
-        const unsigned tag = ++(*tag_state);
-        TvpCarryKernel<<<1, kCarryBlock, 0, st>>>(S, nt, m, r, r == 0);
-        TvpViolationKernel<<<grid_for(1), kTvpBlock, 0, st>>>(S, n, lam, tag);
-        TvpUpdateKernel<<<grid_for(2), kTvpBlock, 0, st>>>(S, n, lam, r, tag);
+      {
+        ProfScope ps(ctx, KC_TV, r == 0 ? 34.0 * n : 0.0);
+        for (int b = 0; b < batch; b++, r++) {
+          const unsigned tag = ++(*tag_state);
+          TvpCarryKernel<<<1, kCarryBlock, 0, st>>>(S, nt, m, r, r == 0);
+          TvpViolationKernel<<<grid_for(1), kTvpBlock, 0, st>>>(S, n, lam, tag);
+          TvpUpdateKernel<<<grid_for(2), kTvpBlock, 0, st>>>(S, n, lam, r, tag);
+        }
+        TvpCheckKernel<<<1, 1, 0, st>>>(S, r);
+        ctx->count_launch(3 * batch + 1);
       }
-      TvpCheckKernel<<<1, 1, 0, st>>>(S, r);
-      ctx->count_launch(3 * batch + 1);
       CUDA_CHECK(cudaMemcpyAsync(h_flag, S.ctl + 1, sizeof(int), cudaMemcpyDeviceToHost, st));
-      CUDA_CHECK(cudaStreamSynchronize(st));
+      CUDA_CHECK(cudaEventRecord(ev, st));
+      {
+        ProfScope ps(ctx, KC_TV, first_batch ? (fuse ? 57.0 : 25.0) * n : 0.0);
+        launch_values(1);
+      }
+      first_batch = false;
+      CUDA_CHECK(cudaEventSynchronize(ev));
       if (*h_flag != 0) rounds = *h_flag - 1;   // index of the round that changed nothing
       if (trace) fprintf(stderr, "[tv] n=%d queued=%d settled_after=%d\n", n, r, *h_flag);
       batch = std::min(24, batch * 2);
@@ -865,16 +890,8 @@ int Tv1dParallelSolve(Ctx* ctx, int n, double* v, double lam, double* beta, char
     host_state[1] = (unsigned)(rounds + 1);
   } else {
     rounds = 0;
-  }
-  {
     ProfScope ps(ctx, KC_TV, (fuse ? 57.0 : 25.0) * n);
-    if (fuse)
-      TvpValuesKernel<true><<<grid_for(3), kTvpBlock, 0, st>>>(S, n, nt, lam, nullptr, fuse->seg, fuse->consts, fuse->u,
-                                                                fuse->y_new, fuse->x);
-    else
-      TvpValuesKernel<false><<<grid_for(3), kTvpBlock, 0, st>>>(S, n, nt, lam, beta, ElemSeg{}, nullptr, nullptr, nullptr,
-                                                                 nullptr);
-    ctx->count_launch();
+    launch_values(0);
   }
   return rounds;
 }
