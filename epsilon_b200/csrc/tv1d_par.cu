@@ -34,7 +34,9 @@
 //   * the active set is updated in place: decisions need only z (written by the violation pass, which also does
 //     the jump test of the active boundaries) and the group maxima.
 //   * no host round trip per round: rounds are queued in batches; every kernel returns at once when a previous
-//     round settled (ctl[1] != 0), and the host reads one int per batch.
+//     round settled (ctl[1] != 0), and the host reads one int per batch.  The values pass is queued behind the
+//     batch before the host has that int (it returns at once if the rounds did not settle), so the host's round
+//     trip overlaps with it.
 //   * the double-double prefix sums are three plain passes of our own (tile sums, one CTA scanning them, tiles
 //     scanned with their offset) instead of cub::DeviceScan on a 16-byte type with a user operator (337 us at
 //     n = 1e7, 0.7 TB/s).
