@@ -46,7 +46,8 @@ __device__ __forceinline__ double ScaledZone(double x, double lam, double M, dou
 //      Leaves x0 with |x0 - x*| ~ 1e-7 (1 + |x*|).
 //   2. fp64: ONE exp and two divisions at x0, then a Newton step and a chord step in which sigma at the stepped
 //      point comes from its Taylor expansion around x0 (the step d is ~1e-6, so the d^3 remainder is below 1e-17).
-//   3. accepted when both steps are as small as quadratic convergence predicts; otherwise -- a stage-1 start that
+//   3. accepted when the cubic remainder of the two steps is below rounding and the second step is as small as
+//      quadratic convergence predicts; otherwise -- a stage-1 start that
 //      did not converge in its 12 steps (huge lam: Newton walks an exp tail one unit per step) -- the lanes fall
 //      into the damped Newton of the reference (backtracking constants of newton.cc:63-77) from where they stand.
 // All lanes of the warp iterate together and leave when every lane has converged.
@@ -109,9 +110,11 @@ __device__ __forceinline__ double LogisticProx(double v, double lam, bool active
     const double x1 = x0 + d0;
     const double s1 = fma(h0 * d0, fma(0.5 * d0, fma(-2.0, s0, 1.0), 1.0), s0);
     const double d1 = -(fma(lam, s1, x1 - v)) * inv;
-    // ---- stage 3: the third derivative of sigma is below 4e-18 beyond |x| = 40, there the expansion is exact
-    // for any step
-    const bool small0 = fabs(d0) <= 7.6e-6 || (fabs(x0) > 40.0 && fabs(d0) <= 1.0);
+    // ---- stage 3: what the two steps leave behind is the Taylor remainder of sigma (its third derivative is
+    // bounded by sigma' ~ h0 over the step) and the cube of the Newton error, both <= ~lam h0 |d0|^3 / (1 + lam h0)
+    // in x.  Held below 1e-16 max(1, |x0|); where sigma is saturated (h0 -> 0) any |d0| <= 1 passes.
+    const bool small0 = fabs(d0) <= 1.0 &&
+                        lam * h0 * fabs(d0 * d0 * d0) <= 1e-16 * fmax(1.0, fabs(x0)) * fma(lam, h0, 1.0);
     if (small0 && fabs(d1) <= 1e-3 * fabs(d0) + 1e-300) {
       x = x1 + d1;
       done = true;

@@ -190,7 +190,7 @@ def test_logistic_extreme_inputs_are_finite(ctx):
     assert x[-1] == pytest.approx(1e4 - 2.0, abs=1e-9) and x[-2] == pytest.approx(798.0, abs=1e-9)
 
 
-@pytest.mark.parametrize("lam", [1e-3, 0.5, 7.0, 300.0, 1e5, 3e8])
+@pytest.mark.parametrize("lam", [1e-3, 0.5, 7.0, 300.0, 1e5, 3e8, 1e14, 1e20])
 def test_logistic_prox_wide_range_vs_high_precision_root(ctx, lam):
     """The three-stage SUM_LOGISTIC kernel (fp32 monotone Newton, one fp64 exp + Taylor-carried steps, damped
     Newton of newton.cc:47-91 as the fallback) against the root of x - v + lam*sigma(x) found independently by
